@@ -1,0 +1,959 @@
+// elementwise.cu -- HBM-bound kernels of the BinaryNet train step: fused preprocessing,
+// first-layer (K=9) float conv, BatchNorm statistics / apply+sign / backward, 2x2 max-pool with
+// first-max tie rule, softmax cross-entropy, weight sign/layout preparation, Adam + latent clip.
+// All tensors are NHWC with channels innermost; every thread moves 16-byte vectors along C.
+#include <cuda_bf16.h>
+
+#include "zkb_host.h"
+
+namespace zkb {
+
+__device__ __forceinline__ uint16_t pm1_bf16(bool nonneg) { return nonneg ? 0x3F80u : 0xBF80u; }
+
+__device__ __forceinline__ uint16_t f32_to_bf16_rn(float f) {
+  return __bfloat16_as_ushort(__float2bfloat16_rn(f));
+}
+__device__ __forceinline__ float bf16_to_f32(uint16_t h) {
+  return __uint_as_float(static_cast<uint32_t>(h) << 16);
+}
+
+// Counter-based per-sample randomness shared with oracle/augment.py (splitmix64 finaliser).
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+// ------------------------------------------------------------------------------------------
+// Preprocessing: gather + centre zero-pad + random crop + random flip + u8 -> f32 (x/127.5 - 1).
+// One thread produces 4 consecutive output floats of one row (OW*C % 4 == 0).
+// ------------------------------------------------------------------------------------------
+struct PreParams {
+  const uint8_t* images;    // [n_pool, IH, IW, C]
+  const long long* labels;  // [n_pool] or null
+  const int* index;         // [B] sample ids, or null (identity)
+  const int8_t* aug;        // [B,3] (ox, oy, flip) or null -> derive from (seed, step, sample)
+  float* out;               // [B, OH, OW, C]
+  int* labels_out;          // [B] or null
+  float* onehot;            // [B, num_classes] or null
+  int B, IH, IW, C, OH, OW, pad_size, training, binarize, num_classes;
+  unsigned long long seed, step;
+};
+
+__device__ __forceinline__ void sample_aug(const PreParams& p, int b, int& ox, int& oy, int& flip) {
+  if (!p.training) {
+    ox = oy = flip = 0;
+    return;
+  }
+  if (p.aug) {
+    ox = p.aug[3 * b];
+    oy = p.aug[3 * b + 1];
+    flip = p.aug[3 * b + 2];
+    return;
+  }
+  const uint64_t r = mix64(mix64(p.seed ^ (p.step * 0xD1342543DE82EF95ull)) + static_cast<uint64_t>(b));
+  const int rx = p.pad_size - p.OW + 1;
+  const int ry = p.pad_size - p.OH + 1;
+  ox = static_cast<int>((r & 0xFFFFu) % static_cast<uint32_t>(rx));
+  oy = static_cast<int>(((r >> 16) & 0xFFFFu) % static_cast<uint32_t>(ry));
+  flip = static_cast<int>((r >> 32) & 1u);
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const PreParams p) {
+  const int row_elems = p.OW * p.C;
+  const int vec_per_img = p.OH * row_elems / 4;
+  const long long total = static_cast<long long>(p.B) * vec_per_img;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i / vec_per_img);
+    const int v = static_cast<int>(i - static_cast<long long>(b) * vec_per_img);
+    const int e0 = v * 4;
+    const int oh = e0 / row_elems;
+    const int re = e0 - oh * row_elems;
+    int ox, oy, flip;
+    sample_aug(p, b, ox, oy, flip);
+    const int src = p.index ? p.index[b] : b;
+    // Training: pad to pad_size (centred), crop OHxOW at (oy, ox).  Eval: centre crop/pad to OHxOW.
+    const int target = p.training ? p.pad_size : 0;
+    const int padded_h = p.training ? target : p.OH;
+    const int padded_w = p.training ? target : p.OW;
+    // offset of the source image inside the padded canvas (negative when cropping)
+    const int off_h = (padded_h - p.IH) >= 0 ? (padded_h - p.IH) / 2 : -((p.IH - padded_h) / 2);
+    const int off_w = (padded_w - p.IW) >= 0 ? (padded_w - p.IW) / 2 : -((p.IW - padded_w) / 2);
+    const uint8_t* img = p.images + static_cast<long long>(src) * p.IH * p.IW * p.C;
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e = re + j;
+      int ow = e / p.C;
+      const int c = e - ow * p.C;
+      if (flip) ow = p.OW - 1 - ow;
+      const int ih = oh + oy - off_h;
+      const int iw = ow + ox - off_w;
+      uint8_t px = 0;
+      if (ih >= 0 && ih < p.IH && iw >= 0 && iw < p.IW) px = img[(ih * p.IW + iw) * p.C + c];
+      float f = static_cast<float>(px) / 127.5f - 1.0f;
+      if (p.binarize) f = f >= 0.0f ? 1.0f : -1.0f;
+      o[j] = f;
+    }
+    *reinterpret_cast<float4*>(p.out + i * 4) = make_float4(o[0], o[1], o[2], o[3]);
+    if (v == 0) {
+      const long long lab = p.labels ? p.labels[src] : 0;
+      if (p.labels_out) p.labels_out[b] = static_cast<int>(lab);
+      if (p.onehot)
+        for (int k = 0; k < p.num_classes; ++k)
+          p.onehot[static_cast<long long>(b) * p.num_classes + k] = (k == lab) ? 1.0f : 0.0f;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// First layer: float image (*) sign(W), 'valid', Cin small (K = ks*ks*Cin <= 32).  Output-write bound.
+// ------------------------------------------------------------------------------------------
+template <int KMAX>
+__global__ void __launch_bounds__(256)
+conv_first_fwd_kernel(const float* __restrict__ x, const float* __restrict__ wq,  // [K][Cout]
+                      float* __restrict__ y, int B, int H, int W, int Cin, int Cout, int ks) {
+  extern __shared__ float s_w[];  // [K][Cout]
+  const int K = ks * ks * Cin;
+  for (int i = threadIdx.x; i < K * Cout; i += blockDim.x) s_w[i] = wq[i];
+  __syncthreads();
+  const int OH = H - ks + 1, OW = W - ks + 1;
+  const int cvec = Cout / 4;
+  const long long total = static_cast<long long>(B) * OH * OW * cvec;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % cvec);
+    const long long pix = i / cvec;
+    const int ow = static_cast<int>(pix % OW);
+    const long long t = pix / OW;
+    const int oh = static_cast<int>(t % OH);
+    const int b = static_cast<int>(t / OH);
+    float xv[KMAX];
+    int k = 0;
+    for (int kh = 0; kh < ks; ++kh)
+      for (int kw = 0; kw < ks; ++kw)
+        for (int ci = 0; ci < Cin; ++ci, ++k)
+          xv[k] = __ldg(x + ((static_cast<long long>(b) * H + oh + kh) * W + ow + kw) * Cin + ci);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (k = 0; k < K; ++k) {
+      const float4 w = *reinterpret_cast<const float4*>(s_w + k * Cout + cv * 4);
+      acc.x = fmaf(xv[k], w.x, acc.x);
+      acc.y = fmaf(xv[k], w.y, acc.y);
+      acc.z = fmaf(xv[k], w.z, acc.z);
+      acc.w = fmaf(xv[k], w.w, acc.w);
+    }
+    *reinterpret_cast<float4*>(y + pix * Cout + cv * 4) = acc;
+  }
+}
+
+// dW[k][co] = sum_pix x[pix + tap(k)] * dy[pix][co].  Block = Cout threads x RG row-groups.
+template <int KMAX>
+__global__ void __launch_bounds__(512)
+conv_first_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                        float* __restrict__ dw, int B, int H, int W, int Cin, int Cout, int ks) {
+  const int K = ks * ks * Cin;
+  const int OH = H - ks + 1, OW = W - ks + 1;
+  const long long pixels = static_cast<long long>(B) * OH * OW;
+  const int co = threadIdx.x % Cout;
+  const int rg = threadIdx.x / Cout;
+  const int nrg = blockDim.x / Cout;
+  float acc[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) acc[k] = 0.f;
+  for (long long pix = static_cast<long long>(blockIdx.x) * nrg + rg; pix < pixels;
+       pix += static_cast<long long>(gridDim.x) * nrg) {
+    const int ow = static_cast<int>(pix % OW);
+    const long long t = pix / OW;
+    const int oh = static_cast<int>(t % OH);
+    const int b = static_cast<int>(t / OH);
+    const float g = dy[pix * Cout + co];
+    int k = 0;
+    for (int kh = 0; kh < ks; ++kh)
+      for (int kw = 0; kw < ks; ++kw)
+        for (int ci = 0; ci < Cin; ++ci, ++k)
+          acc[k] = fmaf(__ldg(x + ((static_cast<long long>(b) * H + oh + kh) * W + ow + kw) * Cin + ci),
+                        g, acc[k]);
+  }
+  for (int k = 0; k < K; ++k) atomicAdd(dw + k * Cout + co, acc[k]);
+}
+
+// ------------------------------------------------------------------------------------------
+// BatchNorm statistics: per-channel sum and sum of squares over rows (double accumulators in
+// global memory; exact for the integer-valued conv outputs).
+// ------------------------------------------------------------------------------------------
+template <typename T>
+struct Vec16;
+template <>
+struct Vec16<float> {
+  static constexpr int N = 4;
+  float v[4];
+  __device__ __forceinline__ void load(const float* p) {
+    const float4 t = *reinterpret_cast<const float4*>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+  __device__ __forceinline__ float get(int i) const { return v[i]; }
+};
+template <>
+struct Vec16<int16_t> {
+  static constexpr int N = 8;
+  int16_t v[8];
+  __device__ __forceinline__ void load(const int16_t* p) {
+    const uint4 t = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = static_cast<int16_t>(w[i] & 0xFFFFu);
+      v[2 * i + 1] = static_cast<int16_t>(w[i] >> 16);
+    }
+  }
+  __device__ __forceinline__ float get(int i) const { return static_cast<float>(v[i]); }
+};
+
+// Reduce per-thread partials (VEC channels each) across the row-lanes of a block and add the
+// block totals to the global double accumulators acc0[C], acc1[C].
+template <int VEC>
+__device__ __forceinline__ void block_channel_reduce(const double (&a0)[VEC], const double (&a1)[VEC],
+                                                     int tpr, int C, double* acc0, double* acc1) {
+  extern __shared__ double s_red[];  // [2][blockDim.x * VEC]
+  const int lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr;
+  const int rl = threadIdx.x / tpr;
+  double* s0 = s_red;
+  double* s1 = s_red + static_cast<size_t>(blockDim.x) * VEC;
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    s0[(rl * tpr + cl) * VEC + j] = a0[j];
+    s1[(rl * tpr + cl) * VEC + j] = a1[j];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    double t0 = 0.0, t1 = 0.0;
+    for (int r = 0; r < lanes; ++r) {
+      t0 += s0[r * tpr * VEC + c];
+      t1 += s1[r * tpr * VEC + c];
+    }
+    atomicAdd(acc0 + c, t0);
+    atomicAdd(acc1 + c, t1);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+bn_stats_kernel(const T* __restrict__ x, long long rows, int C, double* __restrict__ sum,
+                double* __restrict__ sumsq) {
+  constexpr int VEC = Vec16<T>::N;
+  const int tpr = C / VEC;
+  const int lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr;
+  const int rl = threadIdx.x / tpr;
+  double a0[VEC], a1[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) a0[j] = a1[j] = 0.0;
+  if (rl < lanes) {
+    float f0[VEC], f1[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) f0[j] = f1[j] = 0.f;
+    int n = 0;
+    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
+         r += static_cast<long long>(gridDim.x) * lanes) {
+      Vec16<T> v;
+      v.load(x + r * C + cl * VEC);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        const float t = v.get(j);
+        f0[j] += t;
+        f1[j] = fmaf(t, t, f1[j]);
+      }
+      // flush float partials to double every 32 rows (keeps integer inputs exact: 32*4608^2 < 2^30)
+      if (++n == 32) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          a0[j] += f0[j]; a1[j] += f1[j];
+          f0[j] = f1[j] = 0.f;
+        }
+        n = 0;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
+  }
+  block_channel_reduce<VEC>(a0, a1, tpr, C, sum, sumsq);
+}
+
+// Per channel: mean, rstd (for normalisation, biased variance), moving-stat update.
+__global__ void bn_finalize_kernel(const double* __restrict__ sum, const double* __restrict__ sumsq,
+                                   double count, float eps, float momentum, int bessel, int C,
+                                   float* __restrict__ mean_out, float* __restrict__ rstd_out,
+                                   float* __restrict__ moving_mean, float* __restrict__ moving_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double m = sum[c] / count;
+  double var = sumsq[c] / count - m * m;
+  if (var < 0.0) var = 0.0;
+  const float meanf = static_cast<float>(m);
+  const float varf = static_cast<float>(var);
+  mean_out[c] = meanf;
+  rstd_out[c] = rsqrtf(varf + eps);
+  if (moving_mean) {
+    const float uv = (bessel && count > 1.0) ? static_cast<float>(var * (count / (count - 1.0))) : varf;
+    moving_mean[c] = moving_mean[c] * momentum + meanf * (1.0f - momentum);
+    moving_var[c] = moving_var[c] * momentum + uv * (1.0f - momentum);
+  }
+}
+
+// a = (x - mean) * rstd + beta ; s = sign(a) with sign(0) = +1, written as bf16 +-1.
+template <typename T>
+__global__ void __launch_bounds__(256)
+bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, const float* __restrict__ beta,
+                     uint16_t* __restrict__ s_out, float* __restrict__ a_out) {
+  constexpr int VEC = Vec16<T>::N;
+  const int tpr = C / VEC;
+  const long long total = rows * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cl = static_cast<int>(i % tpr);
+    const long long r = i / tpr;
+    Vec16<T> v;
+    v.load(x + r * C + cl * VEC);
+    uint16_t s[VEC];
+    float a[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      const int c = cl * VEC + j;
+      a[j] = (v.get(j) - mean[c]) * rstd[c] + beta[c];
+      s[j] = pm1_bf16(a[j] >= 0.0f);
+    }
+    if (s_out) {
+      uint16_t* o = s_out + r * C + cl * VEC;
+      if (VEC == 8) {
+        *reinterpret_cast<uint4*>(o) =
+            make_uint4(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16),
+                       s[4 % VEC] | (uint32_t(s[5 % VEC]) << 16), s[6 % VEC] | (uint32_t(s[7 % VEC]) << 16));
+      } else {
+        *reinterpret_cast<uint2*>(o) =
+            make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
+      }
+    }
+    if (a_out) {
+      float* o = a_out + r * C + cl * VEC;
+#pragma unroll
+      for (int j = 0; j < VEC; j += 4)
+        *reinterpret_cast<float4*>(o + j) = make_float4(a[j], a[j + 1], a[j + 2], a[j + 3]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// 2x2/2 'valid' max-pool on integer conv outputs, first maximum in row-major window order wins
+// (strict > replacement), fused with the BatchNorm statistics of the pooled map.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+maxpool2_i16_kernel(const int16_t* __restrict__ y, int B, int H, int W, int C,
+                    int16_t* __restrict__ p_out, uint8_t* __restrict__ arg_out,
+                    double* __restrict__ sum, double* __restrict__ sumsq) {
+  constexpr int VEC = 8;
+  const int tpr = C / VEC;
+  const int lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr;
+  const int rl = threadIdx.x / tpr;
+  const int PH = H / 2, PW = W / 2;
+  const long long rows = static_cast<long long>(B) * PH * PW;
+  double a0[VEC], a1[VEC];
+  float f0[VEC], f1[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { a0[j] = a1[j] = 0.0; f0[j] = f1[j] = 0.f; }
+  int n = 0;
+  if (rl < lanes) {
+    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
+         r += static_cast<long long>(gridDim.x) * lanes) {
+      const int pw = static_cast<int>(r % PW);
+      const long long t = r / PW;
+      const int ph = static_cast<int>(t % PH);
+      const int b = static_cast<int>(t / PH);
+      const int16_t* base = y + ((static_cast<long long>(b) * H + 2 * ph) * W + 2 * pw) * C + cl * VEC;
+      Vec16<int16_t> v00, v01, v10, v11;
+      v00.load(base);
+      v01.load(base + C);
+      v10.load(base + static_cast<long long>(W) * C);
+      v11.load(base + static_cast<long long>(W) * C + C);
+      int16_t m[VEC];
+      uint8_t am[VEC];
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        int16_t best = v00.v[j];
+        uint8_t k = 0;
+        if (v01.v[j] > best) { best = v01.v[j]; k = 1; }
+        if (v10.v[j] > best) { best = v10.v[j]; k = 2; }
+        if (v11.v[j] > best) { best = v11.v[j]; k = 3; }
+        m[j] = best;
+        am[j] = k;
+        const float tf = static_cast<float>(best);
+        f0[j] += tf;
+        f1[j] = fmaf(tf, tf, f1[j]);
+      }
+      uint32_t w[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        w[e] = (static_cast<uint32_t>(static_cast<uint16_t>(m[2 * e]))) |
+               (static_cast<uint32_t>(static_cast<uint16_t>(m[2 * e + 1])) << 16);
+      *reinterpret_cast<uint4*>(p_out + r * C + cl * VEC) = make_uint4(w[0], w[1], w[2], w[3]);
+      const uint32_t alo = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+      const uint32_t ahi = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+      *reinterpret_cast<uint2*>(arg_out + r * C + cl * VEC) = make_uint2(alo, ahi);
+      if (++n == 32) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
+        n = 0;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
+  block_channel_reduce<VEC>(a0, a1, tpr, C, sum, sumsq);
+}
+
+// ------------------------------------------------------------------------------------------
+// softmax + sparse categorical cross-entropy (mean over batch) and its gradient w.r.t. logits.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+softmax_ce_kernel(const float* __restrict__ logits, int ld, const int* __restrict__ labels, int B,
+                  int NC, float inv_global_batch, float* __restrict__ dlogits,
+                  double* __restrict__ loss_sum, int* __restrict__ correct) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  float loss = 0.f;
+  int ok = 0;
+  if (b < B) {
+    const float* z = logits + static_cast<long long>(b) * ld;
+    float mx = z[0];
+    int am = 0;
+    for (int k = 1; k < NC; ++k)
+      if (z[k] > mx) { mx = z[k]; am = k; }
+    float se = 0.f;
+    for (int k = 0; k < NC; ++k) se += expf(z[k] - mx);
+    const float lse = logf(se) + mx;
+    const int lab = labels[b];
+    loss = lse - z[lab];
+    ok = (am == lab);
+    if (dlogits) {
+      float* d = dlogits + static_cast<long long>(b) * ld;
+      for (int k = 0; k < ld; ++k) {
+        float g = 0.f;
+        if (k < NC) g = (expf(z[k] - lse) - (k == lab ? 1.f : 0.f)) * inv_global_batch;
+        d[k] = g;
+      }
+    }
+  }
+  // block reduce
+  __shared__ float s_loss[8];
+  __shared__ int s_ok[8];
+  for (int o = 16; o > 0; o >>= 1) {
+    loss += __shfl_down_sync(0xffffffffu, loss, o);
+    ok += __shfl_down_sync(0xffffffffu, ok, o);
+  }
+  if ((threadIdx.x & 31) == 0) { s_loss[threadIdx.x >> 5] = loss; s_ok[threadIdx.x >> 5] = ok; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tl = 0.0;
+    int tk = 0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) { tl += s_loss[w]; tk += s_ok[w]; }
+    atomicAdd(loss_sum, tl);
+    atomicAdd(correct, tk);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// BatchNorm backward.  g is the gradient w.r.t. sign(a) (ste != 0: masked by |a| <= 1) or w.r.t.
+// a itself (ste == 0, last layer).  Pass 1: per-channel sum(da), sum(da * xhat).
+// ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long long rows, int C,
+                     const float* __restrict__ mean, const float* __restrict__ rstd,
+                     const float* __restrict__ beta, int ste, double* __restrict__ sum_da,
+                     double* __restrict__ sum_dax) {
+  constexpr int VEC = 4;  // g is f32: 4 channels per 16 B
+  const int tpr = C / VEC;
+  const int lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr;
+  const int rl = threadIdx.x / tpr;
+  double a0[VEC], a1[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) a0[j] = a1[j] = 0.0;
+  if (rl < lanes) {
+    float mu[VEC], rs[VEC], be[VEC], f0[VEC], f1[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j]; be[j] = beta[cl * VEC + j];
+      f0[j] = f1[j] = 0.f;
+    }
+    int n = 0;
+    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
+         r += static_cast<long long>(gridDim.x) * lanes) {
+      const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
+      const float gg[4] = {gv.x, gv.y, gv.z, gv.w};
+      const T* xp = x + r * C + cl * VEC;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        const float xh = (static_cast<float>(xp[j]) - mu[j]) * rs[j];
+        const float a = xh + be[j];
+        const float da = (ste && fabsf(a) > 1.0f) ? 0.f : gg[j];
+        f0[j] += da;
+        f1[j] = fmaf(da, xh, f1[j]);
+      }
+      if (++n == 64) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
+        n = 0;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
+  }
+  block_channel_reduce<VEC>(a0, a1, tpr, C, sum_da, sum_dax);
+}
+
+// Per channel: dbeta = sum(da) into the gradient arena; means for the apply pass.
+__global__ void bn_bwd_finalize_kernel(const double* __restrict__ sum_da,
+                                       const double* __restrict__ sum_dax, double count, int C,
+                                       float* __restrict__ dbeta, float* __restrict__ mean_da,
+                                       float* __restrict__ mean_dax) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  if (dbeta) dbeta[c] = static_cast<float>(sum_da[c]);
+  mean_da[c] = static_cast<float>(sum_da[c] / count);
+  mean_dax[c] = static_cast<float>(sum_dax[c] / count);
+}
+
+// Pass 2: dx = rstd * (da - mean(da) - xhat * mean(da*xhat)), emitted as
+//   out_mode 0: f32 [rows][C]
+//   out_mode 1: bf16 hi/lo split [rows][C]
+//   out_mode 2: bf16 hi/lo split scattered through the 2x2 max-pool argmax into [B,H,W,C]
+//               (x, g and arg are pooled maps [B,H/2,W/2,C]; the three losers get zeros).
+template <typename T>
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long long rows, int C,
+                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ beta, const float* __restrict__ mean_da,
+                    const float* __restrict__ mean_dax, int ste, int out_mode,
+                    float* __restrict__ out_f32, uint16_t* __restrict__ out_hi,
+                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W) {
+  constexpr int VEC = 4;
+  const int tpr = C / VEC;
+  const long long total = rows * tpr;
+  const int PH = H / 2, PW = W / 2;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cl = static_cast<int>(i % tpr);
+    const long long r = i / tpr;
+    const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
+    const float gg[4] = {gv.x, gv.y, gv.z, gv.w};
+    const T* xp = x + r * C + cl * VEC;
+    float dx[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      const int c = cl * VEC + j;
+      const float xh = (static_cast<float>(xp[j]) - mean[c]) * rstd[c];
+      const float a = xh + beta[c];
+      const float da = (ste && fabsf(a) > 1.0f) ? 0.f : gg[j];
+      dx[j] = rstd[c] * (da - mean_da[c] - xh * mean_dax[c]);
+    }
+    if (out_mode == 0) {
+      *reinterpret_cast<float4*>(out_f32 + r * C + cl * VEC) = make_float4(dx[0], dx[1], dx[2], dx[3]);
+      continue;
+    }
+    uint16_t hi[VEC], lo[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      hi[j] = f32_to_bf16_rn(dx[j]);
+      lo[j] = f32_to_bf16_rn(dx[j] - bf16_to_f32(hi[j]));
+    }
+    if (out_mode == 1) {
+      *reinterpret_cast<uint2*>(out_hi + r * C + cl * VEC) =
+          make_uint2(hi[0] | (uint32_t(hi[1]) << 16), hi[2] | (uint32_t(hi[3]) << 16));
+      *reinterpret_cast<uint2*>(out_lo + r * C + cl * VEC) =
+          make_uint2(lo[0] | (uint32_t(lo[1]) << 16), lo[2] | (uint32_t(lo[3]) << 16));
+    } else {
+      const int pw = static_cast<int>(r % PW);
+      const long long t = r / PW;
+      const int ph = static_cast<int>(t % PH);
+      const long long b = t / PH;
+      const uint32_t a4 = *reinterpret_cast<const uint32_t*>(arg + r * C + cl * VEC);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const long long pos =
+            ((b * H + 2 * ph + (k >> 1)) * W + 2 * pw + (k & 1)) * static_cast<long long>(C) + cl * VEC;
+        uint16_t h[VEC], l[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          const bool win = ((a4 >> (8 * j)) & 0xFFu) == static_cast<uint32_t>(k);
+          h[j] = win ? hi[j] : 0;
+          l[j] = win ? lo[j] : 0;
+        }
+        *reinterpret_cast<uint2*>(out_hi + pos) =
+            make_uint2(h[0] | (uint32_t(h[1]) << 16), h[2] | (uint32_t(h[3]) << 16));
+        *reinterpret_cast<uint2*>(out_lo + pos) =
+            make_uint2(l[0] | (uint32_t(l[1]) << 16), l[2] | (uint32_t(l[3]) << 16));
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Weight preparation: sign(W) in the layouts the GEMM engines read.
+// ------------------------------------------------------------------------------------------
+// conv: W f32 [ks,ks,Cin,Cout] (HWIO) -> fwd [Cout][tap][Cin], dgrad [Cin][tap_flipped][Cout] (bf16)
+__global__ void __launch_bounds__(256)
+prep_conv_weights_kernel(const float* __restrict__ w, int ks, int Cin, int Cout,
+                         uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad) {
+  const int taps = ks * ks;
+  const long long total = static_cast<long long>(taps) * Cin * Cout;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int co = static_cast<int>(i % Cout);
+    const long long t = i / Cout;
+    const int ci = static_cast<int>(t % Cin);
+    const int tap = static_cast<int>(t / Cin);
+    const uint16_t s = pm1_bf16(w[i] >= 0.0f);
+    w_fwd[(static_cast<long long>(co) * taps + tap) * Cin + ci] = s;
+    const int kh = tap / ks, kw = tap % ks;
+    const int ftap = (ks - 1 - kh) * ks + (ks - 1 - kw);
+    w_dgrad[(static_cast<long long>(ci) * taps + ftap) * Cout + co] = s;
+  }
+}
+
+// dense: W f32 [K][N] -> fwd [Npad][K] (rows >= N zero), dgrad [K][Npad] (cols >= N zero)
+__global__ void __launch_bounds__(256)
+prep_dense_weights_kernel(const float* __restrict__ w, int K, int N, int Npad,
+                          uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad) {
+  const long long total = static_cast<long long>(K) * Npad;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int n = static_cast<int>(i % Npad);
+    const int k = static_cast<int>(i / Npad);
+    const uint16_t s = (n < N) ? pm1_bf16(w[static_cast<long long>(k) * N + n] >= 0.0f) : 0;
+    w_fwd[static_cast<long long>(n) * K + k] = s;
+    w_dgrad[i] = s;
+  }
+}
+
+// generic elementwise sign to f32 (first-layer kernel, consumed by the SIMT conv)
+__global__ void __launch_bounds__(256)
+sign_f32_kernel(const float* __restrict__ w, float* __restrict__ out, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    out[i] = w[i] >= 0.0f ? 1.0f : -1.0f;
+}
+
+// ------------------------------------------------------------------------------------------
+// Adam (Keras "epsilon-hat" form, bias correction folded into lr_t on the host) followed by the
+// latent-weight clip to [-1, 1] for kernels (Larq weight_clip); the STE mask of the kernel
+// quantizer (|w| <= 1) is applied to the incoming gradient.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+adam_clip_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m,
+                 float* __restrict__ v, long long n, float lr_t, float b1, float b2, float eps,
+                 float gscale, int is_kernel) {
+  const long long nv = n / 4;
+  const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = tid; i < nv; i += stride) {
+    float4 w4 = reinterpret_cast<float4*>(w)[i];
+    const float4 g4 = reinterpret_cast<const float4*>(g)[i];
+    float4 m4 = reinterpret_cast<float4*>(m)[i];
+    float4 v4 = reinterpret_cast<float4*>(v)[i];
+    float* wp = &w4.x; const float* gp = &g4.x; float* mp = &m4.x; float* vp = &v4.x;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float gg = gp[j] * gscale;
+      if (is_kernel && fabsf(wp[j]) > 1.0f) gg = 0.f;
+      mp[j] = b1 * mp[j] + (1.0f - b1) * gg;
+      vp[j] = b2 * vp[j] + (1.0f - b2) * gg * gg;
+      float nw = wp[j] - lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+      if (is_kernel) nw = fminf(fmaxf(nw, -1.0f), 1.0f);
+      wp[j] = nw;
+    }
+    reinterpret_cast<float4*>(w)[i] = w4;
+    reinterpret_cast<float4*>(m)[i] = m4;
+    reinterpret_cast<float4*>(v)[i] = v4;
+  }
+  for (long long i = nv * 4 + tid; i < n; i += stride) {
+    float gg = g[i] * gscale;
+    if (is_kernel && fabsf(w[i]) > 1.0f) gg = 0.f;
+    m[i] = b1 * m[i] + (1.0f - b1) * gg;
+    v[i] = b2 * v[i] + (1.0f - b2) * gg * gg;
+    float nw = w[i] - lr_t * m[i] / (sqrtf(v[i]) + eps);
+    if (is_kernel) nw = fminf(fmaxf(nw, -1.0f), 1.0f);
+    w[i] = nw;
+  }
+}
+
+}  // namespace zkb
+
+// ============================================================================================
+// C ABI (documented in include/zkb200.h)
+// ============================================================================================
+using namespace zkb;
+
+static int grid_for(long long work_items, int block, int max_waves = 8) {
+  const long long cap = static_cast<long long>(zkb_sm_count()) * max_waves;
+  long long g = (work_items + block - 1) / block;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return static_cast<int>(g);
+}
+
+#define ZKB_ALIGNED16(p) ((reinterpret_cast<uintptr_t>(p) & 15) == 0)
+
+ZKB_API int zkb_preprocess_u8(const uint8_t* images, const long long* labels, const int* index,
+                              const int8_t* aug, float* out, int* labels_out, float* onehot, int B,
+                              int IH, int IW, int C, int OH, int OW, int pad_size, int training,
+                              int binarize, int num_classes, unsigned long long seed,
+                              unsigned long long step, void* stream) {
+  ZKB_REQUIRE(images && out, "preprocess: null pointer");
+  ZKB_REQUIRE(B >= 0 && IH > 0 && IW > 0 && C > 0 && OH > 0 && OW > 0, "preprocess: bad shape");
+  if (B == 0) return ZKB_OK;
+  ZKB_REQUIRE((OW * C) % 4 == 0, "preprocess: OW*C=%d must be a multiple of 4", OW * C);
+  ZKB_REQUIRE(ZKB_ALIGNED16(out), "preprocess: out must be 16-byte aligned");
+  if (training)
+    ZKB_REQUIRE(pad_size >= OH && pad_size >= OW, "preprocess: pad_size %d < crop size", pad_size);
+  ZKB_REQUIRE(!onehot || (labels && num_classes > 0), "preprocess: one-hot needs labels");
+  PreParams p{images, labels, index, aug, out, labels_out, onehot, B, IH, IW, C, OH, OW,
+              pad_size, training, binarize, num_classes, seed, step};
+  const long long work = static_cast<long long>(B) * OH * OW * C / 4;
+  preprocess_kernel<<<grid_for(work, 256, 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  ZKB_LAUNCH_CHECK("preprocess_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_fwd(const float* x, const float* wq_k_co, float* y, int B, int H, int W,
+                               int Cin, int Cout, int ksize, void* stream) {
+  ZKB_REQUIRE(x && wq_k_co && y, "conv_first_fwd: null pointer");
+  const int K = ksize * ksize * Cin;
+  ZKB_REQUIRE(K <= 32, "conv_first_fwd: ksize^2*Cin=%d exceeds 32", K);
+  ZKB_REQUIRE(Cout % 4 == 0 && ZKB_ALIGNED16(y), "conv_first_fwd: Cout %% 4 and 16-byte output");
+  ZKB_REQUIRE(H >= ksize && W >= ksize, "conv_first_fwd: image smaller than the kernel");
+  if (B == 0) return ZKB_OK;
+  const long long work = static_cast<long long>(B) * (H - ksize + 1) * (W - ksize + 1) * (Cout / 4);
+  conv_first_fwd_kernel<32><<<grid_for(work, 256, 16), 256, K * Cout * sizeof(float),
+                              static_cast<cudaStream_t>(stream)>>>(x, wq_k_co, y, B, H, W, Cin, Cout,
+                                                                   ksize);
+  ZKB_LAUNCH_CHECK("conv_first_fwd_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_wgrad(const float* x, const float* dy, float* dw_k_co, int B, int H,
+                                 int W, int Cin, int Cout, int ksize, void* stream) {
+  ZKB_REQUIRE(x && dy && dw_k_co, "conv_first_wgrad: null pointer");
+  const int K = ksize * ksize * Cin;
+  ZKB_REQUIRE(K <= 32, "conv_first_wgrad: ksize^2*Cin=%d exceeds 32", K);
+  ZKB_REQUIRE(Cout <= 512 && 512 % Cout == 0, "conv_first_wgrad: Cout must divide 512");
+  if (B == 0) return ZKB_OK;
+  const long long pixels = static_cast<long long>(B) * (H - ksize + 1) * (W - ksize + 1);
+  const int nrg = 512 / Cout;
+  long long g = (pixels + nrg * 64 - 1) / (nrg * 64);
+  const long long cap = static_cast<long long>(zkb_sm_count()) * 4;
+  if (g > cap) g = cap;
+  conv_first_wgrad_kernel<32><<<static_cast<int>(g), 512, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, dy, dw_k_co, B, H, W, Cin, Cout, ksize);
+  ZKB_LAUNCH_CHECK("conv_first_wgrad_kernel");
+  return ZKB_OK;
+}
+
+static int check_rows_c(const char* who, const void* x, long long rows, int C, int vec) {
+  ZKB_REQUIRE(x, "%s: null pointer", who);
+  ZKB_REQUIRE(rows >= 0 && C > 0, "%s: bad shape", who);
+  ZKB_REQUIRE(C % vec == 0 && C / vec <= 256 && 256 % (C / vec) == 0,
+              "%s: C=%d must be a multiple of %d with C/%d dividing 256", who, C, vec, vec);
+  ZKB_REQUIRE(ZKB_ALIGNED16(x), "%s: tensor must be 16-byte aligned", who);
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum,
+                         double* sumsq, void* stream) {
+  const int vec = x_is_i16 ? 8 : 4;
+  int rc = check_rows_c("bn_stats", x, rows, C, vec);
+  if (rc) return rc;
+  ZKB_REQUIRE(sum && sumsq, "bn_stats: null accumulator");
+  if (rows == 0) return ZKB_OK;
+  const int lanes = 256 / (C / vec);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 4);
+  const size_t smem = 2 * 256 * vec * sizeof(double);
+  if (x_is_i16)
+    bn_stats_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const int16_t*>(x), rows, C, sum, sumsq);
+  else
+    bn_stats_kernel<float><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const float*>(x), rows, C, sum, sumsq);
+  ZKB_LAUNCH_CHECK("bn_stats_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_finalize(const double* sum, const double* sumsq, double count, float eps,
+                            float momentum, int bessel, int C, float* mean, float* rstd,
+                            float* moving_mean, float* moving_var, void* stream) {
+  ZKB_REQUIRE(sum && sumsq && mean && rstd, "bn_finalize: null pointer");
+  ZKB_REQUIRE(count > 0 && C > 0, "bn_finalize: bad count / C");
+  ZKB_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr),
+              "bn_finalize: moving_mean and moving_var go together");
+  bn_finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      sum, sumsq, count, eps, momentum, bessel, C, mean, rstd, moving_mean, moving_var);
+  ZKB_LAUNCH_CHECK("bn_finalize_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C, const float* mean,
+                              const float* rstd, const float* beta, void* s_out_bf16, float* a_out,
+                              void* stream) {
+  const int vec = x_is_i16 ? 8 : 4;
+  int rc = check_rows_c("bn_apply_sign", x, rows, C, vec);
+  if (rc) return rc;
+  ZKB_REQUIRE(mean && rstd && beta, "bn_apply_sign: null statistics");
+  ZKB_REQUIRE(s_out_bf16 || a_out, "bn_apply_sign: no output requested");
+  if (rows == 0) return ZKB_OK;
+  const int grid = grid_for(rows * (C / vec), 256, 16);
+  if (x_is_i16)
+    bn_apply_sign_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const int16_t*>(x), rows, C, mean, rstd, beta,
+        static_cast<uint16_t*>(s_out_bf16), a_out);
+  else
+    bn_apply_sign_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const float*>(x), rows, C, mean, rstd, beta, static_cast<uint16_t*>(s_out_bf16),
+        a_out);
+  ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_out, uint8_t* arg_out,
+                             double* sum, double* sumsq, void* stream) {
+  int rc = check_rows_c("maxpool2_i16", y, static_cast<long long>(B) * H * W, C, 8);
+  if (rc) return rc;
+  ZKB_REQUIRE(p_out && arg_out && sum && sumsq, "maxpool2_i16: null output");
+  ZKB_REQUIRE(H >= 2 && W >= 2, "maxpool2_i16: map smaller than the window");
+  if (B == 0) return ZKB_OK;
+  const long long rows = static_cast<long long>(B) * (H / 2) * (W / 2);
+  const int lanes = 256 / (C / 8);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, 4);
+  const size_t smem = 2 * 256 * 8 * sizeof(double);
+  maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);
+  ZKB_LAUNCH_CHECK("maxpool2_i16_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_softmax_ce(const float* logits, int ld, const int* labels, int B, int num_classes,
+                           float inv_global_batch, float* dlogits, double* loss_sum, int* correct,
+                           void* stream) {
+  ZKB_REQUIRE(logits && labels && loss_sum && correct, "softmax_ce: null pointer");
+  ZKB_REQUIRE(num_classes > 0 && ld >= num_classes, "softmax_ce: ld < num_classes");
+  if (B == 0) return ZKB_OK;
+  softmax_ce_kernel<<<(B + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      logits, ld, labels, B, num_classes, inv_global_batch, dlogits, loss_sum, correct);
+  ZKB_LAUNCH_CHECK("softmax_ce_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                              const float* mean, const float* rstd, const float* beta, int ste,
+                              double* sum_da, double* sum_dax, void* stream) {
+  int rc = check_rows_c("bn_bwd_reduce", g, rows, C, 4);
+  if (rc) return rc;
+  ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax, "bn_bwd_reduce: null pointer");
+  if (rows == 0) return ZKB_OK;
+  const int lanes = 256 / (C / 4);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 4);
+  const size_t smem = 2 * 256 * 4 * sizeof(double);
+  if (x_is_i16)
+    bn_bwd_reduce_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+        g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, ste, sum_da, sum_dax);
+  else
+    bn_bwd_reduce_kernel<float><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+        g, static_cast<const float*>(x), rows, C, mean, rstd, beta, ste, sum_da, sum_dax);
+  ZKB_LAUNCH_CHECK("bn_bwd_reduce_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_bwd_finalize(const double* sum_da, const double* sum_dax, double count, int C,
+                                float* dbeta, float* mean_da, float* mean_dax, void* stream) {
+  ZKB_REQUIRE(sum_da && sum_dax && mean_da && mean_dax, "bn_bwd_finalize: null pointer");
+  ZKB_REQUIRE(count > 0 && C > 0, "bn_bwd_finalize: bad count / C");
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      sum_da, sum_dax, count, C, dbeta, mean_da, mean_dax);
+  ZKB_LAUNCH_CHECK("bn_bwd_finalize_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                             const float* mean, const float* rstd, const float* beta,
+                             const float* mean_da, const float* mean_dax, int ste, int out_mode,
+                             float* out_f32, void* out_hi, void* out_lo, const uint8_t* arg, int H,
+                             int W, void* stream) {
+  int rc = check_rows_c("bn_bwd_apply", g, rows, C, 4);
+  if (rc) return rc;
+  ZKB_REQUIRE(x && mean && rstd && beta && mean_da && mean_dax, "bn_bwd_apply: null pointer");
+  ZKB_REQUIRE(out_mode >= 0 && out_mode <= 2, "bn_bwd_apply: out_mode must be 0, 1 or 2");
+  if (out_mode == 0) ZKB_REQUIRE(out_f32, "bn_bwd_apply: out_f32 is null");
+  if (out_mode >= 1) ZKB_REQUIRE(out_hi && out_lo, "bn_bwd_apply: hi/lo outputs are null");
+  if (out_mode == 2) {
+    ZKB_REQUIRE(arg && H >= 2 && W >= 2, "bn_bwd_apply: pool scatter needs argmax and H, W");
+    ZKB_REQUIRE(rows % (static_cast<long long>(H / 2) * (W / 2)) == 0,
+                "bn_bwd_apply: rows is not a multiple of the pooled map size");
+  }
+  if (rows == 0) return ZKB_OK;
+  const int grid = grid_for(rows * (C / 4), 256, 16);
+  if (x_is_i16)
+    bn_bwd_apply_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, mean_da, mean_dax, ste,
+        out_mode, out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W);
+  else
+    bn_bwd_apply_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        g, static_cast<const float*>(x), rows, C, mean, rstd, beta, mean_da, mean_dax, ste,
+        out_mode, out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W);
+  ZKB_LAUNCH_CHECK("bn_bwd_apply_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_prep_conv_weights(const float* w_hwio, int ksize, int Cin, int Cout, void* w_fwd,
+                                  void* w_dgrad, void* stream) {
+  ZKB_REQUIRE(w_hwio && w_fwd && w_dgrad, "prep_conv_weights: null pointer");
+  const long long total = static_cast<long long>(ksize) * ksize * Cin * Cout;
+  prep_conv_weights_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w_hwio, ksize, Cin, Cout, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad));
+  ZKB_LAUNCH_CHECK("prep_conv_weights_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_prep_dense_weights(const float* w_k_n, int K, int N, int Npad, void* w_fwd,
+                                   void* w_dgrad, void* stream) {
+  ZKB_REQUIRE(w_k_n && w_fwd && w_dgrad, "prep_dense_weights: null pointer");
+  ZKB_REQUIRE(Npad >= N, "prep_dense_weights: Npad < N");
+  const long long total = static_cast<long long>(K) * Npad;
+  prep_dense_weights_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w_k_n, K, N, Npad, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad));
+  ZKB_LAUNCH_CHECK("prep_dense_weights_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_sign_f32(const float* w, float* out, long long n, void* stream) {
+  ZKB_REQUIRE(w && out && n >= 0, "sign_f32: bad arguments");
+  if (n == 0) return ZKB_OK;
+  sign_f32_kernel<<<grid_for(n, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(w, out, n);
+  ZKB_LAUNCH_CHECK("sign_f32_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, float lr_t,
+                          float beta1, float beta2, float eps, float grad_scale, int is_kernel,
+                          void* stream) {
+  ZKB_REQUIRE(w && g && m && v && n >= 0, "adam_clip: bad arguments");
+  ZKB_REQUIRE(ZKB_ALIGNED16(w) && ZKB_ALIGNED16(g) && ZKB_ALIGNED16(m) && ZKB_ALIGNED16(v),
+              "adam_clip: arenas must be 16-byte aligned");
+  if (n == 0) return ZKB_OK;
+  adam_clip_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      w, g, m, v, n, lr_t, beta1, beta2, eps, grad_scale, is_kernel);
+  ZKB_LAUNCH_CHECK("adam_clip_kernel");
+  return ZKB_OK;
+}
