@@ -311,17 +311,24 @@ def adam_clip_step(params, grads, m, v, step: int, lr: float = 5e-3, dtype=np.fl
 
     m <- b1 m + (1-b1) g ; v <- b2 v + (1-b2) g^2 ; w <- w - lr_t m / (sqrt(v) + eps) with
     lr_t = lr sqrt(1-b2^t)/(1-b1^t) ; kernels are then clipped to [-1, 1].
+    With dtype=np.float32 every constant and operation is rounded to fp32 in the order of TF's
+    ApplyAdam CPU functor (alpha = lr*sqrt(1-b2^t)/(1-b1^t); m += (g-m)(1-b1); v += (g*g-v)(1-b2);
+    var -= m*alpha/(sqrt(v)+eps)); with np.float64 it is the exact-arithmetic reference.
     """
-    lr_t = lr * np.sqrt(1.0 - ADAM_B2 ** step) / (1.0 - ADAM_B1 ** step)
+    f = dtype
+    b1, b2, eps = f(ADAM_B1), f(ADAM_B2), f(ADAM_EPS)
+    lr_t = f(lr) * np.sqrt(f(1) - b2 ** f(step), dtype=f) / (f(1) - b1 ** f(step))
     new_p, new_m, new_v = {}, {}, {}
     for k in params:
         g = grads[k].astype(dtype)
         w = params[k].astype(dtype)
         if k.startswith("kernel"):
             g = g * (np.abs(w) <= 1)          # ste_sign kernel quantizer mask (always 1 after clip)
-        mm = ADAM_B1 * m[k].astype(dtype) + (1 - ADAM_B1) * g
-        vv = ADAM_B2 * v[k].astype(dtype) + (1 - ADAM_B2) * g * g
-        w = w - lr_t * mm / (np.sqrt(vv) + ADAM_EPS)
+        mm = m[k].astype(dtype)
+        vv = v[k].astype(dtype)
+        mm = mm + (g - mm) * (f(1) - b1)
+        vv = vv + (g * g - vv) * (f(1) - b2)
+        w = w - (mm * lr_t) / (np.sqrt(vv) + eps)
         if k.startswith("kernel"):
             w = np.clip(w, -1.0, 1.0)
         new_p[k], new_m[k], new_v[k] = w.astype(np.float32), mm.astype(np.float32), vv.astype(np.float32)

@@ -130,7 +130,7 @@ def dense_wgrad(M, K, N):
     x = pm1(M, K, seed=12)
     hi, lo = split(dy)
     dw = torch.zeros(K, N, dtype=torch.float32, device=dev)
-    zn.call("zkb_bdense_wgrad", zn.ptr(x.to(torch.bfloat16).contiguous()), zn.ptr(hi), zn.ptr(lo), zn.ptr(dw), N, M, K, N, 0)
+    zn.call("zkb_bdense_wgrad", zn.ptr(x.to(torch.bfloat16).contiguous()), zn.ptr(hi), zn.ptr(lo), zn.ptr(dw), N, M, K, N, N, 0)
     torch.cuda.synchronize()
     return report(f"dense_wgrad M={M} K={K} N={N}", dw, x.double().t() @ dy.double())
 

@@ -1,0 +1,22 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def native_lib():
+    """Build (if stale) and load libzkb200.so; the GPU tests call through this C ABI."""
+    from zookeeper_b200.build import build_native
+    from zookeeper_b200 import native
+
+    build_native()
+    return native.load()

@@ -1,0 +1,147 @@
+"""Parity of the CUDA train step against the CPU oracle.
+
+Bit-exact: preprocessing output, integer conv / dense outputs (through the sign chain).
+Tolerance (north_star): loss, gradients and updated weights within 1e-4 relative; the norm used is
+the Frobenius norm per tensor (a per-element ratio is meaningless where g ~ 0).
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-4
+
+
+def _rel(a, b):
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30)
+
+
+def _setup(B, seed=1234, input_shape=(28, 28, 1), filters=128, dense=1024, nc=10):
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    layers_o = O.binarynet_layers(input_shape, filters, dense, nc)
+    params = O.glorot_uniform_params(layers_o, 0)
+    rng = np.random.default_rng(seed)
+    img = rng.integers(0, 256, (B,) + tuple(input_shape), dtype=np.uint8)
+    lab = rng.integers(0, nc, (B,)).astype(np.int64)
+    eng = BinaryNetEngine(binarynet_layers(input_shape, filters, dense, nc), input_shape, B, nc)
+    eng.load_params(params)
+    return O, layers_o, params, img, lab, eng
+
+
+@pytest.mark.parametrize("B", [8, 37])
+def test_train_step_matches_oracle(native_lib, B):
+    O, layers_o, params, img, lab, eng = _setup(B)
+    aug = O.augmentation_params(1234, 0, B, 32, 28, 28)
+    x = O.preprocess(img, (28, 28), True, 32, aug)
+    ref = O.forward_backward(params, layers_o, x, lab, torch.float64, keep_acts=True)
+
+    d_img = torch.as_tensor(img).cuda()
+    d_lab = torch.as_tensor(lab).cuda()
+    eng.train_step(d_img, d_lab, None, pad_size=32, aug=torch.as_tensor(aug).cuda(), apply_update=False)
+    torch.cuda.synchronize()
+
+    # preprocessing: bit-exact
+    assert np.array_equal(eng.x0.cpu().numpy(), x)
+    assert np.array_equal(eng.labels.cpu().numpy(), lab.astype(np.int32))
+    # first conv (float): close; binary layers: exact integers given identical sign inputs
+    y0 = eng.L[0].y.cpu().numpy()
+    assert _rel(y0, ref.acts["y0"]) < 1e-6
+    for i in range(1, 9):
+        L = eng.L[i]
+        y = L.y.cpu().numpy().astype(np.int64)[..., : L.spec.cout]
+        yr = np.rint(ref.acts[f"y{i}"]).astype(np.int64)
+        assert np.array_equal(y, yr), f"layer {i}: integer conv/dense output differs"
+        if L.spec.pool:
+            assert np.array_equal(L.p.cpu().numpy().astype(np.int64), np.rint(ref.acts[f"p{i}"]).astype(np.int64))
+    assert abs(eng.last_loss() - ref.loss) <= REL_TOL * abs(ref.loss)
+    assert eng.last_accuracy() == pytest.approx(ref.accuracy)
+    assert _rel(eng.logits(), ref.logits) < REL_TOL
+    g = eng.get_grads()
+    for k, v in ref.grads.items():
+        assert _rel(g[k], v) < REL_TOL, f"grad {k}: rel {_rel(g[k], v):.3g}"
+
+    # moving statistics
+    mv = O.update_moving_stats(O.init_moving_stats(layers_o), layers_o, ref.batch_stats)
+    got = eng.get_moving()
+    for k, v in mv.items():
+        assert _rel(got[k], v) < 1e-5, k
+
+    # optimizer kernel in isolation: oracle Adam (fp32 operation order of TF's ApplyAdam) fed with
+    # the ENGINE's gradients must reproduce the engine's weights to fp32 rounding
+    m0 = {k: np.zeros_like(v) for k, v in params.items()}
+    eng_grads = eng.get_grads()
+    exp32, _, _ = O.adam_clip_step(params, eng_grads, m0, m0, 1, dtype=np.float32)
+    exp64, _, _ = O.adam_clip_step(params, ref.grads, m0, m0, 1, dtype=np.float64)
+    eng._begin()
+    eng.optimizer_step()
+    torch.cuda.synchronize()
+    gp = eng.get_params()
+    for k in params:
+        assert _rel(gp[k], exp32[k]) < 2e-6, f"adam kernel {k}: {_rel(gp[k], exp32[k]):.3g}"
+        if k.startswith("kernel"):
+            # end to end (oracle gradients, exact arithmetic): updated latent weights within 1e-4
+            assert _rel(gp[k], exp64[k]) < REL_TOL, f"param {k}: {_rel(gp[k], exp64[k]):.3g}"
+            assert np.abs(gp[k]).max() <= 1.0
+        else:
+            # beta starts at 0, so the new value IS the step lr*g/(|g|+eps'): elementwise it is as
+            # ill-conditioned as g/|g| where g ~ 0; bound the median and the bulk instead
+            err = np.abs(gp[k] - exp64[k]) / 5e-3
+            assert np.median(err) < 1e-4 and (err > 1e-2).mean() < 0.05, f"beta step {k}"
+
+
+def test_second_step_from_engine_state(native_lib):
+    """Step 2 (Adam t = 2, non-zero moments, re-prepared sign weights, in-kernel augmentation RNG).
+
+    Binarised training is chaotic across steps: a weight with |w| < lr whose gradient is ~0 may
+    flip sign after step 1 in one fp implementation and not in the other, and the loss then
+    differs at the 1e-2 level.  Parity per step is therefore checked by re-seeding the oracle with
+    the ENGINE's state after step 1 and comparing everything step 2 produces."""
+    B = 16
+    O, layers_o, params, img, lab, eng = _setup(B, seed=7)
+    d_img, d_lab = torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda()
+    eng.train_step(d_img, d_lab, None, pad_size=32, seed=99)   # step 1, in-kernel counter RNG
+    torch.cuda.synchronize()
+    aug0 = O.augmentation_params(99, 0, B, 32, 28, 28)
+    assert np.array_equal(eng.x0.cpu().numpy(), O.preprocess(img, (28, 28), True, 32, aug0))
+    p1 = eng.get_params()
+    m1, v1 = eng.get_adam_state()
+
+    aug1 = O.augmentation_params(99, 1, B, 32, 28, 28)
+    x1 = O.preprocess(img, (28, 28), True, 32, aug1)
+    ref = O.forward_backward(p1, layers_o, x1, lab, torch.float64)
+    eng.train_step(d_img, d_lab, None, pad_size=32, seed=99)   # step 2
+    torch.cuda.synchronize()
+    assert np.array_equal(eng.x0.cpu().numpy(), x1), "in-kernel augmentation differs from oracle RNG"
+    assert abs(eng.last_loss() - ref.loss) <= REL_TOL * abs(ref.loss)
+    g = eng.get_grads()
+    for k, v in ref.grads.items():
+        assert _rel(g[k], v) < REL_TOL, f"grad {k}: rel {_rel(g[k], v):.3g}"
+    exp32, _, _ = O.adam_clip_step(p1, g, m1, v1, 2, dtype=np.float32)
+    exp64, _, _ = O.adam_clip_step(p1, ref.grads, m1, v1, 2, dtype=np.float64)
+    gp = eng.get_params()
+    for k in p1:
+        assert _rel(gp[k], exp32[k]) < 2e-6, f"adam kernel {k}"
+        if k.startswith("kernel"):
+            assert _rel(gp[k], exp64[k]) < REL_TOL, f"param {k}"
+
+
+def test_eval_step_matches_oracle(native_lib):
+    B = 16
+    O, layers_o, params, img, lab, eng = _setup(B, seed=11)
+    rng = np.random.default_rng(5)
+    moving = {}
+    for i, l in enumerate(layers_o):
+        moving[f"moving_mean{i}"] = rng.normal(0, 2.0, l.cout).astype(np.float32)
+        moving[f"moving_var{i}"] = rng.uniform(50.0, 500.0, l.cout).astype(np.float32)
+    eng.load_params(params, moving)
+    x = O.preprocess(img, (28, 28), False)
+    ref = O.predict(params, moving, layers_o, x)
+    eng.eval_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda())
+    torch.cuda.synchronize()
+    assert np.array_equal(eng.x0.cpu().numpy(), x)
+    assert _rel(eng.logits(), ref) < 1e-4

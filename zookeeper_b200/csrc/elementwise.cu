@@ -112,15 +112,15 @@ preprocess_kernel(const PreParams p) {
 // ------------------------------------------------------------------------------------------
 // First layer: float image (*) sign(W), 'valid', Cin small (K = ks*ks*Cin <= 32).  Output-write bound.
 // ------------------------------------------------------------------------------------------
-template <int KMAX>
+template <int KS, int CIN>
 __global__ void __launch_bounds__(256)
 conv_first_fwd_kernel(const float* __restrict__ x, const float* __restrict__ wq,  // [K][Cout]
-                      float* __restrict__ y, int B, int H, int W, int Cin, int Cout, int ks) {
+                      float* __restrict__ y, int B, int H, int W, int Cout) {
   extern __shared__ float s_w[];  // [K][Cout]
-  const int K = ks * ks * Cin;
+  constexpr int K = KS * KS * CIN;
   for (int i = threadIdx.x; i < K * Cout; i += blockDim.x) s_w[i] = wq[i];
   __syncthreads();
-  const int OH = H - ks + 1, OW = W - ks + 1;
+  const int OH = H - KS + 1, OW = W - KS + 1;
   const int cvec = Cout / 4;
   const long long total = static_cast<long long>(B) * OH * OW * cvec;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -131,14 +131,18 @@ conv_first_fwd_kernel(const float* __restrict__ x, const float* __restrict__ wq,
     const long long t = pix / OW;
     const int oh = static_cast<int>(t % OH);
     const int b = static_cast<int>(t / OH);
-    float xv[KMAX];
-    int k = 0;
-    for (int kh = 0; kh < ks; ++kh)
-      for (int kw = 0; kw < ks; ++kw)
-        for (int ci = 0; ci < Cin; ++ci, ++k)
-          xv[k] = __ldg(x + ((static_cast<long long>(b) * H + oh + kh) * W + ow + kw) * Cin + ci);
+    float xv[K];
+#pragma unroll
+    for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < KS; ++kw)
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci)
+          xv[(kh * KS + kw) * CIN + ci] =
+              __ldg(x + ((static_cast<long long>(b) * H + oh + kh) * W + ow + kw) * CIN + ci);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (k = 0; k < K; ++k) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
       const float4 w = *reinterpret_cast<const float4*>(s_w + k * Cout + cv * 4);
       acc.x = fmaf(xv[k], w.x, acc.x);
       acc.y = fmaf(xv[k], w.y, acc.y);
@@ -149,20 +153,20 @@ conv_first_fwd_kernel(const float* __restrict__ x, const float* __restrict__ wq,
   }
 }
 
-// dW[k][co] = sum_pix x[pix + tap(k)] * dy[pix][co].  Block = Cout threads x RG row-groups.
-template <int KMAX>
+// dW[k][co] = sum_pix x[pix + tap(k)] * dy[pix][co].  Block = Cout threads x row-groups.
+template <int KS, int CIN>
 __global__ void __launch_bounds__(512)
 conv_first_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                        float* __restrict__ dw, int B, int H, int W, int Cin, int Cout, int ks) {
-  const int K = ks * ks * Cin;
-  const int OH = H - ks + 1, OW = W - ks + 1;
+                        float* __restrict__ dw, int B, int H, int W, int Cout) {
+  constexpr int K = KS * KS * CIN;
+  const int OH = H - KS + 1, OW = W - KS + 1;
   const long long pixels = static_cast<long long>(B) * OH * OW;
   const int co = threadIdx.x % Cout;
   const int rg = threadIdx.x / Cout;
   const int nrg = blockDim.x / Cout;
-  float acc[KMAX];
+  float acc[K];
 #pragma unroll
-  for (int k = 0; k < KMAX; ++k) acc[k] = 0.f;
+  for (int k = 0; k < K; ++k) acc[k] = 0.f;
   for (long long pix = static_cast<long long>(blockIdx.x) * nrg + rg; pix < pixels;
        pix += static_cast<long long>(gridDim.x) * nrg) {
     const int ow = static_cast<int>(pix % OW);
@@ -170,13 +174,17 @@ conv_first_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ d
     const int oh = static_cast<int>(t % OH);
     const int b = static_cast<int>(t / OH);
     const float g = dy[pix * Cout + co];
-    int k = 0;
-    for (int kh = 0; kh < ks; ++kh)
-      for (int kw = 0; kw < ks; ++kw)
-        for (int ci = 0; ci < Cin; ++ci, ++k)
-          acc[k] = fmaf(__ldg(x + ((static_cast<long long>(b) * H + oh + kh) * W + ow + kw) * Cin + ci),
-                        g, acc[k]);
+#pragma unroll
+    for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < KS; ++kw)
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci)
+          acc[(kh * KS + kw) * CIN + ci] = fmaf(
+              __ldg(x + ((static_cast<long long>(b) * H + oh + kh) * W + ow + kw) * CIN + ci), g,
+              acc[(kh * KS + kw) * CIN + ci]);
   }
+#pragma unroll
   for (int k = 0; k < K; ++k) atomicAdd(dw + k * Cout + co, acc[k]);
 }
 
@@ -670,9 +678,10 @@ adam_clip_kernel(float* __restrict__ w, const float* __restrict__ g, float* __re
     for (int j = 0; j < 4; ++j) {
       float gg = gp[j] * gscale;
       if (is_kernel && fabsf(wp[j]) > 1.0f) gg = 0.f;
-      mp[j] = b1 * mp[j] + (1.0f - b1) * gg;
-      vp[j] = b2 * vp[j] + (1.0f - b2) * gg * gg;
-      float nw = wp[j] - lr_t * mp[j] / (sqrtf(vp[j]) + eps);
+      // same operation order as TF's ApplyAdam functor (fp32): m += (g-m)(1-b1), v += (g^2-v)(1-b2)
+      mp[j] += (gg - mp[j]) * (1.0f - b1);
+      vp[j] += (gg * gg - vp[j]) * (1.0f - b2);
+      float nw = wp[j] - (mp[j] * lr_t) / (sqrtf(vp[j]) + eps);
       if (is_kernel) nw = fminf(fmaxf(nw, -1.0f), 1.0f);
       wp[j] = nw;
     }
@@ -683,9 +692,9 @@ adam_clip_kernel(float* __restrict__ w, const float* __restrict__ g, float* __re
   for (long long i = nv * 4 + tid; i < n; i += stride) {
     float gg = g[i] * gscale;
     if (is_kernel && fabsf(w[i]) > 1.0f) gg = 0.f;
-    m[i] = b1 * m[i] + (1.0f - b1) * gg;
-    v[i] = b2 * v[i] + (1.0f - b2) * gg * gg;
-    float nw = w[i] - lr_t * m[i] / (sqrtf(v[i]) + eps);
+    m[i] += (gg - m[i]) * (1.0f - b1);
+    v[i] += (gg * gg - v[i]) * (1.0f - b2);
+    float nw = w[i] - (m[i] * lr_t) / (sqrtf(v[i]) + eps);
     if (is_kernel) nw = fminf(fmaxf(nw, -1.0f), 1.0f);
     w[i] = nw;
   }
@@ -732,15 +741,20 @@ ZKB_API int zkb_preprocess_u8(const uint8_t* images, const long long* labels, co
 ZKB_API int zkb_conv_first_fwd(const float* x, const float* wq_k_co, float* y, int B, int H, int W,
                                int Cin, int Cout, int ksize, void* stream) {
   ZKB_REQUIRE(x && wq_k_co && y, "conv_first_fwd: null pointer");
-  const int K = ksize * ksize * Cin;
-  ZKB_REQUIRE(K <= 32, "conv_first_fwd: ksize^2*Cin=%d exceeds 32", K);
+  ZKB_REQUIRE(ksize == 3 && (Cin == 1 || Cin == 3),
+              "conv_first_fwd: only 3x3 kernels over 1 or 3 input channels are built");
   ZKB_REQUIRE(Cout % 4 == 0 && ZKB_ALIGNED16(y), "conv_first_fwd: Cout %% 4 and 16-byte output");
   ZKB_REQUIRE(H >= ksize && W >= ksize, "conv_first_fwd: image smaller than the kernel");
   if (B == 0) return ZKB_OK;
+  const int K = ksize * ksize * Cin;
   const long long work = static_cast<long long>(B) * (H - ksize + 1) * (W - ksize + 1) * (Cout / 4);
-  conv_first_fwd_kernel<32><<<grid_for(work, 256, 16), 256, K * Cout * sizeof(float),
-                              static_cast<cudaStream_t>(stream)>>>(x, wq_k_co, y, B, H, W, Cin, Cout,
-                                                                   ksize);
+  const int grid = grid_for(work, 256, 16);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = static_cast<size_t>(K) * Cout * sizeof(float);
+  if (Cin == 1)
+    conv_first_fwd_kernel<3, 1><<<grid, 256, smem, st>>>(x, wq_k_co, y, B, H, W, Cout);
+  else
+    conv_first_fwd_kernel<3, 3><<<grid, 256, smem, st>>>(x, wq_k_co, y, B, H, W, Cout);
   ZKB_LAUNCH_CHECK("conv_first_fwd_kernel");
   return ZKB_OK;
 }
@@ -748,8 +762,8 @@ ZKB_API int zkb_conv_first_fwd(const float* x, const float* wq_k_co, float* y, i
 ZKB_API int zkb_conv_first_wgrad(const float* x, const float* dy, float* dw_k_co, int B, int H,
                                  int W, int Cin, int Cout, int ksize, void* stream) {
   ZKB_REQUIRE(x && dy && dw_k_co, "conv_first_wgrad: null pointer");
-  const int K = ksize * ksize * Cin;
-  ZKB_REQUIRE(K <= 32, "conv_first_wgrad: ksize^2*Cin=%d exceeds 32", K);
+  ZKB_REQUIRE(ksize == 3 && (Cin == 1 || Cin == 3),
+              "conv_first_wgrad: only 3x3 kernels over 1 or 3 input channels are built");
   ZKB_REQUIRE(Cout <= 512 && 512 % Cout == 0, "conv_first_wgrad: Cout must divide 512");
   if (B == 0) return ZKB_OK;
   const long long pixels = static_cast<long long>(B) * (H - ksize + 1) * (W - ksize + 1);
@@ -757,8 +771,11 @@ ZKB_API int zkb_conv_first_wgrad(const float* x, const float* dy, float* dw_k_co
   long long g = (pixels + nrg * 64 - 1) / (nrg * 64);
   const long long cap = static_cast<long long>(zkb_sm_count()) * 4;
   if (g > cap) g = cap;
-  conv_first_wgrad_kernel<32><<<static_cast<int>(g), 512, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, dy, dw_k_co, B, H, W, Cin, Cout, ksize);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (Cin == 1)
+    conv_first_wgrad_kernel<3, 1><<<static_cast<int>(g), 512, 0, st>>>(x, dy, dw_k_co, B, H, W, Cout);
+  else
+    conv_first_wgrad_kernel<3, 3><<<static_cast<int>(g), 512, 0, st>>>(x, dy, dw_k_co, B, H, W, Cout);
   ZKB_LAUNCH_CHECK("conv_first_wgrad_kernel");
   return ZKB_OK;
 }

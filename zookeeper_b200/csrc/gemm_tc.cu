@@ -240,7 +240,8 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
 // --------------------------------------------------------------------------------------------
 struct WGemmParams {
   int Ma;       // rows of D per tap (reduced operand A has Ma channels), multiple of 128
-  int N;        // columns of D
+  int N;        // columns of the B operand (multiple of 64)
+  int n_valid;  // columns of D actually written (<= N)
   long long P;  // reduction length (pixels / batch rows)
   int b_terms;  // 1 or 2
   int block_n;  // 64, 128 or 256
@@ -391,7 +392,7 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (row_in_tap < p.Ma) {
           float* o = p.out + orow * p.ldo + col0;
           for (int j = 0; j < 32; ++j)
-            if (col0 + j < p.N) atomicAdd(o + j, __uint_as_float(r[j]));
+            if (col0 + j < p.n_valid) atomicAdd(o + j, __uint_as_float(r[j]));
         }
       }
     }
@@ -484,12 +485,8 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   if (rc) return rc;
 
   const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + sizeof(SharedCtl) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    ZKB_CUDA(cudaFuncSetAttribute(kgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  227 * 1024));
-    attr_set = true;
-  }
+  ZKB_CUDA(cudaFuncSetAttribute(kgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                227 * 1024));
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = zkb_sm_count();
   const int grid = tiles < sms ? tiles : sms;
@@ -501,17 +498,18 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
 // A: bf16 [P][Ma] (plain) or NHWC activation [NB,H,W,Ma] viewed through tap (im2col).
 // B_hi/B_lo: bf16 [P][N].  out f32 [(taps*Ma)][ldo], accumulated into (caller zeroes it).
 static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float* out,
-                        long long ldo, int Ma, int N, long long P, int im2col, int NB, int H, int W,
-                        int ksize, int pad, cudaStream_t stream) {
+                        long long ldo, int Ma, int N, int n_valid, long long P, int im2col, int NB,
+                        int H, int W, int ksize, int pad, cudaStream_t stream) {
   ZKB_REQUIRE(A && B_hi && out, "wgemm: null pointer");
   ZKB_REQUIRE(Ma > 0 && N > 0 && P > 0, "wgemm: empty problem");
   ZKB_REQUIRE(Ma % 128 == 0, "wgemm: Ma=%d must be a multiple of 128", Ma);
   ZKB_REQUIRE(N % 64 == 0, "wgemm: N=%d must be a multiple of 64", N);
   ZKB_REQUIRE(P < (1ll << 31) - 256, "wgemm: P too large");
-  ZKB_REQUIRE(ldo >= N, "wgemm: ldo < N");
+  ZKB_REQUIRE(n_valid > 0 && n_valid <= N && ldo >= n_valid, "wgemm: bad n_valid / ldo");
   WGemmParams p{};
   p.Ma = Ma;
   p.N = N;
+  p.n_valid = n_valid;
   p.P = P;
   p.b_terms = B_lo ? 2 : 1;
   p.block_n = (N % 128 == 0) ? 128 : 64;
@@ -559,12 +557,8 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
     if (rc) return rc;
   }
   const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + sizeof(SharedCtlW) + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    ZKB_CUDA(cudaFuncSetAttribute(wgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  227 * 1024));
-    attr_set = true;
-  }
+  ZKB_CUDA(cudaFuncSetAttribute(wgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                227 * 1024));
   const int grid = out_tiles * p.splits;
   wgemm_bf16_kernel<<<grid, 192, smem, stream>>>(tmA, tmB0, tmB1, p);
   ZKB_LAUNCH_CHECK("wgemm_bf16_kernel");
@@ -606,13 +600,14 @@ ZKB_API int zkb_bconv2d_wgrad(const void* act_pm1, const void* dy_hi, const void
                               float* dw_hwio, int NB, int H, int W, int Cin, int Cout, int ksize,
                               void* stream) {
   ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_wgrad: ksize must be odd");
-  return launch_wgemm(act_pm1, dy_hi, dy_lo, dw_hwio, Cout, Cin, Cout,
+  return launch_wgemm(act_pm1, dy_hi, dy_lo, dw_hwio, Cout, Cin, Cout, Cout,
                       static_cast<long long>(NB) * H * W, 1, NB, H, W, ksize, ksize / 2,
                       static_cast<cudaStream_t>(stream));
 }
 
 ZKB_API int zkb_bdense_wgrad(const void* act_pm1, const void* dy_hi, const void* dy_lo,
-                             float* dw_k_n, long long ldw, int rows, int K, int N, void* stream) {
-  return launch_wgemm(act_pm1, dy_hi, dy_lo, dw_k_n, ldw, K, N, rows, 0, 0, 0, 0, 1, 0,
+                             float* dw_k_n, long long ldw, int rows, int K, int N, int n_out,
+                             void* stream) {
+  return launch_wgemm(act_pm1, dy_hi, dy_lo, dw_k_n, ldw, K, N, n_out, rows, 0, 0, 0, 0, 1, 0,
                       static_cast<cudaStream_t>(stream));
 }

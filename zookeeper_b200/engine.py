@@ -1,0 +1,503 @@
+"""BinaryNet train-step engine: Python host code driving libzkb200.so through ctypes.
+
+This is what replaces ``tf.keras.Sequential.fit`` for the model built by the reference's
+``BinaryNet.build`` (examples/larq_experiment.py:51-103) compiled with
+``sparse_categorical_crossentropy`` + ``Adam`` (:117-122, :141-153).  PyTorch is used for device
+memory, streams and ``torch.distributed`` only; every arithmetic step is a hand-written sm_100a
+kernel behind the C ABI (no CPU / PyTorch fallback: a missing library raises).
+
+Data layout (all NHWC, channels innermost, resident in HBM for the whole run):
+  x0        f32  [B,H,W,Cin]            preprocessed images
+  y_i       f32 (first layer) / int16   pre-BatchNorm conv / dense output (exact integers)
+  p_i, arg  int16 / u8                  2x2 max-pooled map and winning window slot
+  s_i       bf16 (+-1)                  sign(BatchNorm(.)) -- operand of the next binary GEMM
+  ds_i      f32                         gradient w.r.t. s_i (output of the next layer's dgrad)
+  dy_i      bf16 hi + bf16 lo           gradient w.r.t. y_i, split so that tensor-core products
+                                        with the exact +-1 operand keep ~16 mantissa bits
+Parameters, gradients and Adam moments live in flat f32 arenas: [all kernels | all betas(padded)].
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import native as zn
+
+BN_EPS = 1e-3
+BN_MOMENTUM = 0.99
+NPAD = 64  # dense output widths below 64 are padded to 64 columns inside the engine
+
+
+@dataclass
+class LayerSpec:
+    """One QuantConv2D / QuantDense + (MaxPool2D) + BatchNormalization block."""
+
+    kind: str            # "conv" | "dense"
+    cin: int
+    cout: int
+    ksize: int = 3
+    padding: str = "same"
+    quant_input: bool = True
+    pool: bool = False
+
+
+def binarynet_layers(input_shape=(28, 28, 1), filters=128, dense_units=1024, num_classes=10,
+                     kernel_size=3) -> List[LayerSpec]:
+    """Topology of ``BinaryNet.build`` (examples/larq_experiment.py:59-103)."""
+    if isinstance(kernel_size, (tuple, list)):
+        if kernel_size[0] != kernel_size[1]:
+            raise ValueError("only square kernels are supported")
+        kernel_size = kernel_size[0]
+    h, w, c = input_shape
+    f = filters
+    layers = [
+        LayerSpec("conv", c, f, kernel_size, "valid", quant_input=False),
+        LayerSpec("conv", f, f, kernel_size, "same", pool=True),
+        LayerSpec("conv", f, 2 * f, kernel_size, "same"),
+        LayerSpec("conv", 2 * f, 2 * f, kernel_size, "same", pool=True),
+        LayerSpec("conv", 2 * f, 4 * f, kernel_size, "same"),
+        LayerSpec("conv", 4 * f, 4 * f, kernel_size, "same", pool=True),
+    ]
+    h, w = h - kernel_size + 1, w - kernel_size + 1
+    for _ in range(3):
+        h, w = h // 2, w // 2
+    layers += [
+        LayerSpec("dense", h * w * 4 * f, dense_units),
+        LayerSpec("dense", dense_units, dense_units),
+        LayerSpec("dense", dense_units, num_classes),
+    ]
+    return layers
+
+
+def _round_up(x: int, m: int) -> int:
+    return (x + m - 1) // m * m
+
+
+class _Layer:
+    """Device buffers of one block."""
+
+    pass
+
+
+class BinaryNetEngine:
+    """Holds parameters, optimizer state and activations of a BinaryNet on one GPU and runs
+    train / eval steps.  With ``world_size > 1`` (one process per GPU) gradients are summed with
+    an NCCL all-reduce over the flat gradient arena; BatchNorm statistics are per replica unless
+    ``sync_bn`` is set, in which case the per-channel sums are all-reduced as well."""
+
+    def __init__(self, layers: Sequence[LayerSpec], input_shape: Tuple[int, int, int], batch_size: int,
+                 num_classes: int, learning_rate: float = 5e-3, device: Optional[torch.device] = None,
+                 process_group=None, sync_bn: bool = False, beta_1: float = 0.9, beta_2: float = 0.999,
+                 epsilon: float = 1e-7):
+        zn.load()  # fail loudly now if the CUDA library is missing
+        if not torch.cuda.is_available():
+            raise RuntimeError("BinaryNetEngine needs a CUDA device (B200); there is no CPU fallback")
+        self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        self.layers = list(layers)
+        self.input_shape = tuple(input_shape)
+        self.B = int(batch_size)
+        self.num_classes = int(num_classes)
+        self.lr, self.b1, self.b2, self.eps = float(learning_rate), beta_1, beta_2, epsilon
+        self.pg = process_group
+        self.world = 1
+        if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
+            self.world = torch.distributed.get_world_size(process_group)
+        self.sync_bn = bool(sync_bn) and self.world > 1
+        self.step_count = 0
+        self.launches_per_step = 0
+        self.watch = None      # None | True | set of entry-point names to time with CUDA events
+        self.watched = []      # (name, layer tag, start event, end event)
+        self._tag = ""
+        self._validate()
+        self._allocate()
+
+    # ------------------------------------------------------------------ set-up
+    def _validate(self):
+        ls = self.layers
+        if not ls or ls[0].kind != "conv" or ls[0].quant_input or ls[0].padding != "valid" or ls[0].pool:
+            raise ValueError("first layer must be an unquantised-input 'valid' conv without pooling")
+        if ls[0].ksize != 3 or ls[0].cin not in (1, 3):
+            raise ValueError("first layer: 3x3 kernel over 1 or 3 input channels")
+        for l in ls[1:]:
+            if not l.quant_input:
+                raise ValueError("only the first layer may skip the input quantizer")
+            if l.kind == "conv" and (l.padding != "same" or l.ksize % 2 != 1):
+                raise ValueError("binary convs must be odd-sized 'same' convs")
+            if l.cin % 128 != 0:
+                raise ValueError(f"binary layer input width {l.cin} must be a multiple of 128")
+        if ls[-1].kind != "dense" or ls[-1].cout != self.num_classes:
+            raise ValueError("last layer must be a dense layer with num_classes units")
+        if ls[-1].pool:
+            raise ValueError("pooling after a dense layer")
+
+    def _allocate(self):
+        dev, B = self.device, self.B
+        H, W, C = self.input_shape
+        f32, i16, bf16, u8 = torch.float32, torch.int16, torch.bfloat16, torch.uint8
+        # ---- parameter arenas
+        k_sizes, b_sizes = [], []
+        for l in self.layers:
+            k_sizes.append(l.ksize * l.ksize * l.cin * l.cout if l.kind == "conv" else l.cin * l.cout)
+            b_sizes.append(self._cpad(l))
+        self.k_off = np.concatenate([[0], np.cumsum([_round_up(s, 4) for s in k_sizes])]).astype(np.int64)
+        self.b_off = np.concatenate([[0], np.cumsum(b_sizes)]).astype(np.int64)
+        self.n_kernel = int(self.k_off[-1])
+        self.n_beta = int(self.b_off[-1])
+        n = self.n_kernel + self.n_beta
+        self.params = torch.zeros(n, dtype=f32, device=dev)
+        self.grads = torch.zeros(n, dtype=f32, device=dev)
+        self.adam_m = torch.zeros(n, dtype=f32, device=dev)
+        self.adam_v = torch.zeros(n, dtype=f32, device=dev)
+        self.moving_mean = torch.zeros(self.n_beta, dtype=f32, device=dev)
+        self.moving_var = torch.ones(self.n_beta, dtype=f32, device=dev)
+        # per-step accumulators (zeroed by one memset): fwd sums, bwd sums, loss, correct
+        self.acc = torch.zeros(4 * self.n_beta + 2, dtype=torch.float64, device=dev)
+        self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.stat = torch.zeros(4 * self.n_beta, dtype=f32, device=dev)  # mean, rstd, mean_da, mean_dax
+        self.x0 = torch.zeros(B, H, W, C, dtype=f32, device=dev)
+        self.labels = torch.zeros(B, dtype=torch.int32, device=dev)
+        self.L: List[_Layer] = []
+        h, w = H, W
+        for i, l in enumerate(self.layers):
+            L = _Layer()
+            L.spec, L.idx = l, i
+            L.cp = self._cpad(l)
+            ksz = k_sizes[i]
+            L.kernel = self.params[self.k_off[i]: self.k_off[i] + ksz]
+            L.dkernel = self.grads[self.k_off[i]: self.k_off[i] + ksz]
+            bo = self.n_kernel + int(self.b_off[i])
+            L.beta = self.params[bo: bo + L.cp]
+            L.dbeta = self.grads[bo: bo + L.cp]
+            so = int(self.b_off[i])
+            nb = self.n_beta
+            L.sum, L.sumsq = self.acc[so: so + L.cp], self.acc[nb + so: nb + so + L.cp]
+            L.sum_da, L.sum_dax = self.acc[2 * nb + so: 2 * nb + so + L.cp], self.acc[3 * nb + so: 3 * nb + so + L.cp]
+            L.mean, L.rstd = self.stat[so: so + L.cp], self.stat[nb + so: nb + so + L.cp]
+            L.mean_da, L.mean_dax = self.stat[2 * nb + so: 2 * nb + so + L.cp], self.stat[3 * nb + so: 3 * nb + so + L.cp]
+            L.mm, L.mv = self.moving_mean[so: so + L.cp], self.moving_var[so: so + L.cp]
+            if l.kind == "conv":
+                L.in_hw = (h, w)
+                oh, ow = (h - l.ksize + 1, w - l.ksize + 1) if l.padding == "valid" else (h, w)
+                L.out_hw = (oh, ow)
+                L.y = torch.zeros(B, oh, ow, L.cp, dtype=f32 if i == 0 else i16, device=dev)
+                if l.pool:
+                    ph, pw = oh // 2, ow // 2
+                    L.p = torch.zeros(B, ph, pw, L.cp, dtype=i16, device=dev)
+                    L.arg = torch.zeros(B, ph, pw, L.cp, dtype=u8, device=dev)
+                    h, w = ph, pw
+                else:
+                    h, w = oh, ow
+                L.bn_rows = B * h * w
+                L.s = torch.zeros(B, h, w, L.cp, dtype=bf16, device=dev)
+                L.ds = torch.zeros(B, h, w, L.cp, dtype=f32, device=dev)
+                if i == 0:
+                    L.wq = torch.zeros(l.ksize * l.ksize * l.cin, l.cout, dtype=f32, device=dev)
+                    L.dy = torch.zeros(B, oh, ow, L.cp, dtype=f32, device=dev)
+                else:
+                    L.w_fwd = torch.zeros(l.cout, l.ksize * l.ksize * l.cin, dtype=bf16, device=dev)
+                    L.w_dgrad = torch.zeros(l.cin, l.ksize * l.ksize * l.cout, dtype=bf16, device=dev)
+                    L.dy_hi = torch.zeros(B, oh, ow, L.cp, dtype=bf16, device=dev)
+                    L.dy_lo = torch.zeros(B, oh, ow, L.cp, dtype=bf16, device=dev)
+            else:
+                L.y = torch.zeros(B, L.cp, dtype=i16, device=dev)
+                L.bn_rows = B
+                last = i == len(self.layers) - 1
+                if last:
+                    L.logits = torch.zeros(B, L.cp, dtype=f32, device=dev)
+                    L.ds = torch.zeros(B, L.cp, dtype=f32, device=dev)  # dlogits
+                else:
+                    L.s = torch.zeros(B, L.cp, dtype=bf16, device=dev)
+                    L.ds = torch.zeros(B, L.cp, dtype=f32, device=dev)
+                L.w_fwd = torch.zeros(L.cp, l.cin, dtype=bf16, device=dev)
+                L.w_dgrad = torch.zeros(l.cin, L.cp, dtype=bf16, device=dev)
+                L.dy_hi = torch.zeros(B, L.cp, dtype=bf16, device=dev)
+                L.dy_lo = torch.zeros(B, L.cp, dtype=bf16, device=dev)
+            self.L.append(L)
+
+    @staticmethod
+    def _cpad(l: LayerSpec) -> int:
+        return l.cout if l.cout % 64 == 0 else _round_up(l.cout, NPAD)
+
+    # ------------------------------------------------------------------ parameters in / out
+    def load_params(self, params: Dict[str, np.ndarray], moving: Optional[Dict[str, np.ndarray]] = None):
+        """Inject weights in Keras layout: ``kernel{i}`` HWIO / [K, N], ``beta{i}`` [C]."""
+        for L in self.L:
+            k = torch.as_tensor(np.ascontiguousarray(params[f"kernel{L.idx}"]), dtype=torch.float32)
+            if k.numel() != L.kernel.numel():
+                raise ValueError(f"kernel{L.idx}: expected {L.kernel.numel()} values, got {k.numel()}")
+            L.kernel.copy_(k.reshape(-1))
+            b = torch.as_tensor(params[f"beta{L.idx}"], dtype=torch.float32)
+            L.beta.zero_()
+            L.beta[: L.spec.cout].copy_(b)
+            if moving is not None:
+                L.mm.zero_()
+                L.mv.fill_(1.0)
+                L.mm[: L.spec.cout].copy_(torch.as_tensor(moving[f"moving_mean{L.idx}"], dtype=torch.float32))
+                L.mv[: L.spec.cout].copy_(torch.as_tensor(moving[f"moving_var{L.idx}"], dtype=torch.float32))
+
+    def init_glorot(self, seed: int = 0):
+        """Keras default (Glorot uniform) initialisation from ``numpy.random.default_rng(seed)``."""
+        rng = np.random.default_rng(seed)
+        params = {}
+        for i, l in enumerate(self.layers):
+            if l.kind == "conv":
+                shape = (l.ksize, l.ksize, l.cin, l.cout)
+                fi, fo = l.ksize * l.ksize * l.cin, l.ksize * l.ksize * l.cout
+            else:
+                shape, fi, fo = (l.cin, l.cout), l.cin, l.cout
+            lim = math.sqrt(6.0 / (fi + fo))
+            params[f"kernel{i}"] = rng.uniform(-lim, lim, size=shape).astype(np.float32)
+            params[f"beta{i}"] = np.zeros(l.cout, dtype=np.float32)
+        self.load_params(params)
+        return params
+
+    def _shape_of(self, L) -> Tuple[int, ...]:
+        l = L.spec
+        return (l.ksize, l.ksize, l.cin, l.cout) if l.kind == "conv" else (l.cin, l.cout)
+
+    def get_params(self) -> Dict[str, np.ndarray]:
+        out = {}
+        for L in self.L:
+            out[f"kernel{L.idx}"] = L.kernel.detach().cpu().numpy().reshape(self._shape_of(L)).copy()
+            out[f"beta{L.idx}"] = L.beta[: L.spec.cout].detach().cpu().numpy().copy()
+        return out
+
+    def get_grads(self) -> Dict[str, np.ndarray]:
+        out = {}
+        for L in self.L:
+            out[f"kernel{L.idx}"] = L.dkernel.detach().cpu().numpy().reshape(self._shape_of(L)).copy()
+            out[f"beta{L.idx}"] = L.dbeta[: L.spec.cout].detach().cpu().numpy().copy()
+        return out
+
+    def get_adam_state(self) -> Tuple[Dict[str, np.ndarray], Dict[str, np.ndarray]]:
+        """First and second Adam moments in the same keyed layout as :meth:`get_params`."""
+        m, v = {}, {}
+        nk = self.n_kernel
+        for L in self.L:
+            k0, ksz = int(self.k_off[L.idx]), L.kernel.numel()
+            b0 = nk + int(self.b_off[L.idx])
+            for dst, arena in ((m, self.adam_m), (v, self.adam_v)):
+                dst[f"kernel{L.idx}"] = arena[k0: k0 + ksz].detach().cpu().numpy().reshape(self._shape_of(L)).copy()
+                dst[f"beta{L.idx}"] = arena[b0: b0 + L.spec.cout].detach().cpu().numpy().copy()
+        return m, v
+
+    def get_moving(self) -> Dict[str, np.ndarray]:
+        out = {}
+        for L in self.L:
+            out[f"moving_mean{L.idx}"] = L.mm[: L.spec.cout].detach().cpu().numpy().copy()
+            out[f"moving_var{L.idx}"] = L.mv[: L.spec.cout].detach().cpu().numpy().copy()
+        return out
+
+    # ------------------------------------------------------------------ kernels
+    def _call(self, name, *args):
+        self._n_launch += 1
+        watch = self.watch
+        if watch is not None and (watch is True or name in watch):
+            # CUDA events on the launching stream around this one launch (bench.py roofline /
+            # per-kernel breakdown); off by default.
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            zn.call(name, *args, self._stream)
+            e1.record()
+            self.watched.append((name, self._tag, e0, e1))
+            return
+        zn.call(name, *args, self._stream)
+
+    def _begin(self):
+        self._stream = torch.cuda.current_stream(self.device).cuda_stream
+        self._n_launch = 0
+
+    def preprocess(self, images_u8: torch.Tensor, labels_i64: Optional[torch.Tensor], index: Optional[torch.Tensor],
+                   training: bool, pad_size: int = 0, aug: Optional[torch.Tensor] = None, seed: int = 0,
+                   step: int = 0, binarize: bool = False, onehot: Optional[torch.Tensor] = None, batch: Optional[int] = None):
+        """Fused batch map of ``Preprocessing.__call__`` for the example's PadCropAndFlip
+        (zookeeper/tf/preprocessing.py:59-75, examples/larq_experiment.py:24-37)."""
+        if not hasattr(self, "_stream"):
+            self._begin()
+        B = self.B if batch is None else batch
+        _, IH, IW, C = images_u8.shape
+        H, W, _ = self.input_shape
+        self._call("zkb_preprocess_u8", zn.ptr(images_u8), zn.ptr(labels_i64), zn.ptr(index), zn.ptr(aug),
+                   zn.ptr(self.x0), zn.ptr(self.labels) if labels_i64 is not None else 0, zn.ptr(onehot),
+                   B, IH, IW, C, H, W, pad_size, int(training), int(binarize), self.num_classes, seed, step)
+
+    def _all_reduce(self, t: torch.Tensor):
+        torch.distributed.all_reduce(t, group=self.pg)
+
+    def _bn_forward(self, L, x, is_i16: bool, rows: int, stats_done: bool, training: bool = True):
+        cp = L.cp
+        if training:
+            if not stats_done:
+                self._call("zkb_bn_stats", zn.ptr(x), int(is_i16), rows, cp, zn.ptr(L.sum), zn.ptr(L.sumsq))
+            count = float(rows)
+            if self.sync_bn:
+                self._pending_bn_sync(L)
+                count *= self.world
+            bessel = 1 if L.spec.kind == "conv" else 0
+            self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, bessel, cp,
+                       zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
+            mean, rstd = L.mean, L.rstd
+        else:
+            mean, rstd = L.mm, L.eval_rstd
+        last = L.idx == len(self.L) - 1
+        self._call("zkb_bn_apply_sign", zn.ptr(x), int(is_i16), rows, cp, zn.ptr(mean), zn.ptr(rstd), zn.ptr(L.beta),
+                   0 if last else zn.ptr(L.s), zn.ptr(L.logits) if last else 0)
+
+    def _pending_bn_sync(self, L):
+        # sum and sumsq of one layer are not adjacent in the accumulator arena: two small collectives
+        self._all_reduce(L.sum)
+        self._all_reduce(L.sumsq)
+
+    def forward(self, training: bool = True):
+        """Forward pass over ``self.x0`` (filled by :meth:`preprocess`)."""
+        B = self.B
+        prev = None
+        for L in self.L:
+            l = L.spec
+            self._tag = f"fwd{L.idx}"
+            if l.kind == "conv":
+                oh, ow = L.out_hw
+                if L.idx == 0:
+                    H, W, C = self.input_shape
+                    self._call("zkb_conv_first_fwd", zn.ptr(self.x0), zn.ptr(L.wq), zn.ptr(L.y), B, H, W, C, l.cout, l.ksize)
+                    self._bn_forward(L, L.y, False, B * oh * ow, False, training)
+                else:
+                    ih, iw = L.in_hw
+                    self._call("zkb_bconv2d_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), B, ih, iw, l.cin, l.cout, l.ksize)
+                    if l.pool:
+                        self._call("zkb_maxpool2_i16", zn.ptr(L.y), B, oh, ow, L.cp, zn.ptr(L.p), zn.ptr(L.arg),
+                                   zn.ptr(L.sum), zn.ptr(L.sumsq))
+                        self._bn_forward(L, L.p, True, L.bn_rows, True, training)
+                    else:
+                        self._bn_forward(L, L.y, True, L.bn_rows, False, training)
+            else:
+                self._call("zkb_bdense_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
+                self._bn_forward(L, L.y, True, B, False, training)
+            prev = L
+
+    def prepare_weights(self):
+        for L in self.L:
+            l = L.spec
+            if L.idx == 0:
+                self._call("zkb_sign_f32", zn.ptr(L.kernel), zn.ptr(L.wq), L.kernel.numel())
+            elif l.kind == "conv":
+                self._call("zkb_prep_conv_weights", zn.ptr(L.kernel), l.ksize, l.cin, l.cout, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad))
+            else:
+                self._call("zkb_prep_dense_weights", zn.ptr(L.kernel), l.cin, l.cout, L.cp, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad))
+
+    def backward(self):
+        B = self.B
+        n = len(self.L)
+        for i in range(n - 1, -1, -1):
+            L, l = self.L[i], self.L[i].spec
+            self._tag = f"bwd{i}"
+            last = i == n - 1
+            x = L.p if (l.kind == "conv" and l.pool) else L.y
+            is_i16 = int(i != 0)
+            rows = L.bn_rows
+            ste = 0 if last else 1
+            self._call("zkb_bn_bwd_reduce", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
+                       zn.ptr(L.beta), ste, zn.ptr(L.sum_da), zn.ptr(L.sum_dax))
+            count = float(rows)
+            if self.sync_bn:
+                self._all_reduce(L.sum_da)
+                self._all_reduce(L.sum_dax)
+                count *= self.world
+            self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, L.cp, zn.ptr(L.dbeta),
+                       zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
+            if i == 0:
+                mode, of32, ohi, olo, arg, H, W = 0, zn.ptr(L.dy), 0, 0, 0, 0, 0
+            elif l.kind == "conv" and l.pool:
+                mode, of32, ohi, olo, arg = 2, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.arg)
+                H, W = L.out_hw
+            else:
+                mode, of32, ohi, olo, arg, H, W = 1, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), 0, 0, 0
+            self._call("zkb_bn_bwd_apply", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
+                       zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), ste, mode, of32, ohi, olo, arg, H, W)
+            if i == 0:
+                H0, W0, C0 = self.input_shape
+                self._call("zkb_conv_first_wgrad", zn.ptr(self.x0), zn.ptr(L.dy), zn.ptr(L.dkernel), B, H0, W0, C0, l.cout, l.ksize)
+                continue
+            prev = self.L[i - 1]
+            if l.kind == "conv":
+                ih, iw = L.in_hw
+                self._call("zkb_bconv2d_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
+                           B, ih, iw, l.cin, l.cout, l.ksize)
+                self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
+                           B, ih, iw, l.cin, l.cout, l.ksize)
+            else:
+                self._call("zkb_bdense_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
+                           l.cout, B, l.cin, L.cp, l.cout)
+                self._call("zkb_bdense_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
+                           B, l.cin, L.cp)
+
+    def loss_and_grad(self):
+        L = self.L[-1]
+        nb4 = 4 * self.n_beta
+        self._call("zkb_softmax_ce", zn.ptr(L.logits), L.cp, zn.ptr(self.labels), self.B, self.num_classes,
+                   1.0 / (self.B * self.world), zn.ptr(L.ds), self.acc[nb4:].data_ptr(), zn.ptr(self.correct))
+
+    def optimizer_step(self):
+        self.step_count += 1
+        t = self.step_count
+        # bias-corrected step size in fp32, as TF's ApplyAdam computes it from the fp32 beta powers
+        f = np.float32
+        lr_t = float(f(self.lr) * np.sqrt(f(1) - f(self.b2) ** f(t), dtype=f) / (f(1) - f(self.b1) ** f(t)))
+        nk = self.n_kernel
+        self._call("zkb_adam_clip", zn.ptr(self.params), zn.ptr(self.grads), zn.ptr(self.adam_m), zn.ptr(self.adam_v),
+                   nk, lr_t, self.b1, self.b2, self.eps, 1.0, 1)
+        self._call("zkb_adam_clip", self.params[nk:].data_ptr(), self.grads[nk:].data_ptr(), self.adam_m[nk:].data_ptr(),
+                   self.adam_v[nk:].data_ptr(), self.n_beta, lr_t, self.b1, self.b2, self.eps, 1.0, 0)
+
+    # ------------------------------------------------------------------ public steps
+    def train_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, index: Optional[torch.Tensor] = None,
+                   pad_size: int = 0, aug: Optional[torch.Tensor] = None, seed: int = 0, apply_update: bool = True,
+                   preprocessed: bool = False):
+        """preprocess -> forward -> softmax-CE -> backward -> (all-reduce) -> Adam + clip.
+
+        Everything is enqueued on the current CUDA stream; nothing synchronises with the host.
+        Read :meth:`last_loss` / :meth:`last_accuracy` afterwards (that read synchronises)."""
+        self._begin()
+        self.acc.zero_()
+        self.correct.zero_()
+        self.grads.zero_()
+        if not preprocessed:
+            self.preprocess(images_u8, labels_i64, index, True, pad_size, aug, seed, self.step_count)
+        self.prepare_weights()
+        self.forward(training=True)
+        self.loss_and_grad()
+        self.backward()
+        if self.world > 1:
+            self._all_reduce(self.grads)
+        if apply_update:
+            self.optimizer_step()
+        self.launches_per_step = self._n_launch
+
+    def eval_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, index: Optional[torch.Tensor] = None):
+        """Validation pass (larq_experiment.py:133-139): centre crop/pad, moving statistics."""
+        self._begin()
+        self.acc.zero_()
+        self.correct.zero_()
+        for L in self.L:
+            L.eval_rstd = torch.rsqrt(L.mv + BN_EPS)
+        self.preprocess(images_u8, labels_i64, index, False)
+        self.prepare_weights()
+        self.forward(training=False)
+        L = self.L[-1]
+        self._call("zkb_softmax_ce", zn.ptr(L.logits), L.cp, zn.ptr(self.labels), self.B, self.num_classes,
+                   1.0 / self.B, 0, self.acc[4 * self.n_beta:].data_ptr(), zn.ptr(self.correct))
+
+    def last_loss(self) -> float:
+        """Mean cross-entropy of the last step over this replica's batch (synchronises)."""
+        return float(self.acc[4 * self.n_beta].item()) / self.B
+
+    def last_accuracy(self) -> float:
+        return float(self.correct.item()) / self.B
+
+    def logits(self) -> np.ndarray:
+        return self.L[-1].logits[:, : self.num_classes].detach().cpu().numpy()

@@ -41,7 +41,7 @@ SIGNATURES = {
     "zkb_bconv2d_dgrad": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_dgrad": [P, P, P, P, I, I, I, P],
     "zkb_bconv2d_wgrad": [P, P, P, P, I, I, I, I, I, I, P],
-    "zkb_bdense_wgrad": [P, P, P, P, L, I, I, I, P],
+    "zkb_bdense_wgrad": [P, P, P, P, L, I, I, I, I, P],
     "zkb_bn_stats": [P, I, L, I, P, P, P],
     "zkb_bn_finalize": [P, P, D, F, F, I, I, P, P, P, P, P],
     "zkb_bn_apply_sign": [P, I, L, I, P, P, P, P, P, P],
