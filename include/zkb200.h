@@ -1,0 +1,152 @@
+/* zkb200.h -- C ABI of libzkb200.so: the hand-written sm_100a (B200) kernels behind the BinaryNet
+ * train hot path of a zookeeper-configured Larq experiment.
+ *
+ * The reference (AdamHillier/zookeeper) has no FFI for this path: every operator below is a
+ * Python call into TensorFlow / Larq made from examples/larq_experiment.py.  Each entry point cites
+ * the reference call site (file:line under /root/reference) whose arithmetic it replaces.
+ *
+ * Conventions
+ *   - Plain C types only.  All tensor pointers are DEVICE pointers owned by the caller (NHWC,
+ *     channels innermost, 16-byte aligned); the library never allocates or frees caller-visible
+ *     memory.  `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); every
+ *     call only enqueues work and returns without synchronising.
+ *   - Return value: 0 = ok; < 0 = argument error detected before any launch; > 0 = the
+ *     cudaError_t / CUresult of the failing runtime call.  zkb_last_error_string() returns the
+ *     message of the last failure on the calling thread.
+ *   - "pm1 bf16" = bfloat16 holding exactly +1.0 or -1.0 (0x3F80 / 0xBF80): the output of larq's
+ *     ste_sign.  Products of two such operands accumulate in f32 inside tensor memory and are
+ *     exact integers for K < 2^24.
+ *   - "hi/lo" = a float gradient split as hi = bf16(g), lo = bf16(g - hi); both are multiplied by
+ *     the exact +-1 operand on tcgen05 and summed in f32 (about 16 mantissa bits).
+ */
+#ifndef ZKB200_H
+#define ZKB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int zkb_abi_version(void);
+const char* zkb_last_error_string(void);
+
+/* ---- data pipeline --------------------------------------------------------------------------
+ * Fused batch map: gather `index` from a resident uint8 pool, centre zero-pad to pad_size, random
+ * crop OHxOW, random left-right flip, float32(x)/127.5 - 1 (true division), optional sign
+ * binarisation, sparse label copy and optional one-hot.  Per-sample (ox, oy, flip) come from
+ * `aug` ([B,3] int8) or, when NULL, from a counter-based generator keyed by (seed, step, sample).
+ * training == 0: centre crop/pad only.
+ * Replaces: examples/larq_experiment.py:24-37 (PadCropAndFlip.input/output) mapped per example by
+ * tf.data at :126-139 through zookeeper/tf/preprocessing.py:59-75. */
+int zkb_preprocess_u8(const uint8_t* images, const long long* labels, const int* index,
+                      const int8_t* aug, float* out, int* labels_out, float* onehot, int B, int IH,
+                      int IW, int C, int OH, int OW, int pad_size, int training, int binarize,
+                      int num_classes, unsigned long long seed, unsigned long long step,
+                      void* stream);
+
+/* ---- bit-level formulation (north_star items 2, 3) --------------------------------------------
+ * Sign + bit-pack: 32 consecutive values along K -> one uint32 (bit j = 1 iff value >= 0, i.e.
+ * +1; sign(0) = sign(-0.0) = +1).  n must be a multiple of 32.  Warp-ballot kernel.
+ * Replaces: larq ste_sign forward, "ste_sign" at examples/larq_experiment.py:53-54,65. */
+int zkb_sign_pack(const void* x, void* packed_u32, long long n, int x_is_bf16, void* stream);
+/* XNOR-popcount GEMM on CUDA cores: y[m][n] = 32*k_words - 2*popc(a[m] ^ b[n]) (int32).
+ * Replaces: QuantDense matmul, examples/larq_experiment.py:95-99. */
+int zkb_bgemm_popc(const void* a_packed, const void* b_packed, int* y, long long ldy, int M, int N,
+                   int k_words, void* stream);
+
+/* ---- first layer: float image (*) sign(W), 'valid' 3x3, Cin in {1,3} ----------------------------
+ * wq_k_co / dw_k_co: [ks*ks*Cin][Cout] == HWIO flattened.  wgrad accumulates into dw (zero it).
+ * Replaces: lq.layers.QuantConv2D without input quantizer, examples/larq_experiment.py:62-69. */
+int zkb_conv_first_fwd(const float* x, const float* wq_k_co, float* y, int B, int H, int W, int Cin,
+                       int Cout, int ksize, void* stream);
+int zkb_conv_first_wgrad(const float* x, const float* dy, float* dw_k_co, int B, int H, int W,
+                         int Cin, int Cout, int ksize, void* stream);
+
+/* ---- binary conv / dense on tcgen05 -------------------------------------------------------------
+ * Forward: act_pm1 [NB,H,W,Cin] (conv) or [rows,K] (dense), pm1 bf16; weights as written by
+ * zkb_prep_*_weights; y int16 (exact integer sums, |y| <= ks*ks*Cin).  'same' zero padding is
+ * produced by TMA im2col out-of-bounds fill.  Cin % 64 == 0 (wgrad: % 128), K % 64 == 0.
+ * Replaces: lq.layers.QuantConv2D(padding="same", ste_sign/ste_sign)
+ *           examples/larq_experiment.py:71-73,76-78,80-82,85-87,89-91 and lq.layers.QuantDense :95,97,99. */
+int zkb_bconv2d_fwd(const void* act_pm1, const void* wq_oc_k, void* y_i16, int NB, int H, int W,
+                    int Cin, int Cout, int ksize, void* stream);
+int zkb_bdense_fwd(const void* act_pm1, const void* wq_n_k, void* y_i16, long long ldy, int rows,
+                   int K, int N, void* stream);
+/* Backward w.r.t. the input (before the STE mask): dx f32 [NB,H,W,Cin] / [rows,K].
+ * Replaces: TF autodiff of the layers above (model.fit, examples/larq_experiment.py:147-153). */
+int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, void* dx_f32,
+                      int NB, int H, int W, int Cin, int Cout, int ksize, void* stream);
+int zkb_bdense_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_k_n, void* dx_f32,
+                     int rows, int K, int N, void* stream);
+/* Backward w.r.t. the latent kernel: dw f32 in HWIO / [K][ldw], ACCUMULATED into (zero it first;
+ * partial tiles are combined with float atomics).  n_out <= N columns are written. */
+int zkb_bconv2d_wgrad(const void* act_pm1, const void* dy_hi, const void* dy_lo, float* dw_hwio,
+                      int NB, int H, int W, int Cin, int Cout, int ksize, void* stream);
+int zkb_bdense_wgrad(const void* act_pm1, const void* dy_hi, const void* dy_lo, float* dw_k_n,
+                     long long ldw, int rows, int K, int N, int n_out, void* stream);
+
+/* ---- BatchNormalization(scale=False), training mode ---------------------------------------------
+ * x: f32 or int16 [rows][C].  stats: per-channel sum / sum of squares into double accumulators
+ * (caller zeroes them).  finalize: mean, rstd = rsqrt(biased var + eps); moving <- moving*momentum
+ * + batch*(1-momentum), with the Bessel-corrected variance when bessel != 0 (TF fused 4-D kernel).
+ * apply_sign: a = (x-mean)*rstd + beta; s = sign(a) as pm1 bf16 and/or a itself.
+ * Replaces: tf.keras.layers.BatchNormalization(scale=False) examples/larq_experiment.py:70,75,79,
+ *           84,88,93,96,98,100 and the ste_sign input quantizer of the following layer (:53). */
+int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum, double* sumsq,
+                 void* stream);
+int zkb_bn_finalize(const double* sum, const double* sumsq, double count, float eps, float momentum,
+                    int bessel, int C, float* mean, float* rstd, float* moving_mean,
+                    float* moving_var, void* stream);
+int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C, const float* mean,
+                      const float* rstd, const float* beta, void* s_out_bf16, float* a_out,
+                      void* stream);
+/* MaxPool2D(2,2) 'valid' on the integer conv output; first maximum in row-major window order wins
+ * (arg = 0..3); also accumulates the BatchNorm statistics of the pooled map.
+ * Replaces: tf.keras.layers.MaxPool2D examples/larq_experiment.py:74,83,92. */
+int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_out, uint8_t* arg_out,
+                     double* sum, double* sumsq, void* stream);
+/* softmax + sparse categorical cross-entropy: loss_sum += sum_b -log softmax(z_b)[label_b],
+ * correct += #argmax hits, dlogits = (softmax - onehot) * inv_global_batch (columns >= num_classes
+ * up to ld are written as 0).
+ * Replaces: Activation("softmax") + loss/metrics, examples/larq_experiment.py:101,117-118. */
+int zkb_softmax_ce(const float* logits, int ld, const int* labels, int B, int num_classes,
+                   float inv_global_batch, float* dlogits, double* loss_sum, int* correct,
+                   void* stream);
+/* BatchNorm backward.  g = gradient w.r.t. sign(a) (ste != 0: masked where |a| > 1, the ste_sign
+ * backward) or w.r.t. a (ste == 0).  reduce: sum(da), sum(da*xhat); finalize: dbeta and the two
+ * means; apply: dx = rstd*(da - mean(da) - xhat*mean(da*xhat)) written as f32 (out_mode 0), as
+ * hi/lo bf16 (1), or hi/lo scattered through the 2x2 pool argmax into the [B,H,W,C] map (2).
+ * Replaces: TF autodiff of BatchNormalization / ste_sign / MaxPool2D (model.fit, :147-153). */
+int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                      const float* mean, const float* rstd, const float* beta, int ste,
+                      double* sum_da, double* sum_dax, void* stream);
+int zkb_bn_bwd_finalize(const double* sum_da, const double* sum_dax, double count, int C,
+                        float* dbeta, float* mean_da, float* mean_dax, void* stream);
+int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                     const float* mean, const float* rstd, const float* beta, const float* mean_da,
+                     const float* mean_dax, int ste, int out_mode, float* out_f32, void* out_hi,
+                     void* out_lo, const uint8_t* arg, int H, int W, void* stream);
+
+/* ---- weights and optimizer ----------------------------------------------------------------------
+ * sign(W) in the operand layouts of the GEMM engines (kernel_quantizer="ste_sign",
+ * examples/larq_experiment.py:54,65): conv HWIO f32 -> fwd [Cout][tap][Cin], dgrad
+ * [Cin][flipped tap][Cout]; dense [K][N] f32 -> fwd [Npad][K], dgrad [K][Npad] (pad = 0). */
+int zkb_prep_conv_weights(const float* w_hwio, int ksize, int Cin, int Cout, void* w_fwd,
+                          void* w_dgrad, void* stream);
+int zkb_prep_dense_weights(const float* w_k_n, int K, int N, int Npad, void* w_fwd, void* w_dgrad,
+                           void* stream);
+int zkb_sign_f32(const float* w, float* out, long long n, void* stream);
+/* Adam in the operation order of TF's ApplyAdam (lr_t = lr*sqrt(1-b2^t)/(1-b1^t) computed by the
+ * caller) followed, for kernels (is_kernel != 0), by the ste_sign gradient mask |w| <= 1 and the
+ * clip of the latent weight to [-1, 1].
+ * Replaces: tf.keras.optimizers.Adam examples/larq_experiment.py:120-122 and
+ *           kernel_constraint="weight_clip" :55,66. */
+int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, float lr_t,
+                  float beta1, float beta2, float eps, float grad_scale, int is_kernel,
+                  void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZKB200_H */
