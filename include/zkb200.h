@@ -146,6 +146,27 @@ int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, flo
                   float beta1, float beta2, float eps, float grad_scale, int is_kernel,
                   void* stream);
 
+/* ---- for callers that cannot allocate device memory ----------------------------------------------
+ * (No counterpart in the reference: this entry point exists for hosts of this library, not for
+ * parity.)  BatchNorm(train) + sign in one call -- statistics, moving-average update, normalise,
+ * sign -- i.e. zkb_bn_stats + zkb_bn_finalize + zkb_bn_apply_sign, but the per-channel accumulators
+ * and statistics those need live in a fixed array compiled into the library instead of buffers the
+ * caller provides.  Meant for code that is handed input/output buffers only and must not call
+ * cudaMalloc itself: an operator callback inside a runtime that owns the device allocator, or a
+ * loop that cannot take the device-wide synchronisation cudaMalloc/cudaFree imply.  The call
+ * allocates nothing.
+ *   - Limit: C <= zkb_bn_train_sign_static_max_channels() (4096); larger C is refused with a
+ *     negative status and a message naming the limit.
+ *   - Every GPU that loads the library holds the array (about 96 KiB) until the process exits.
+ *   - The first call on each device looks up the array's device address (that device must be
+ *     current); make that first call before starting any stream capture.
+ *   - All calls on a GPU share the array.  It is cleared on entry, so back-to-back calls on one
+ *     stream are fine; calls that may overlap on the GPU (other streams, other threads) race. */
+int zkb_bn_train_sign_static_max_channels(void);
+int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows, int C, const float* beta,
+                             float eps, float momentum, int bessel, float* moving_mean,
+                             float* moving_var, void* s_out_bf16, float* a_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

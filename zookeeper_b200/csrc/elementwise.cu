@@ -4,6 +4,8 @@
 // All tensors are NHWC with channels innermost; every thread moves 16-byte vectors along C.
 #include <cuda_bf16.h>
 
+#include <mutex>
+
 #include "zkb_host.h"
 
 namespace zkb {
@@ -972,5 +974,106 @@ ZKB_API int zkb_adam_clip(float* w, const float* g, float* m, float* v, long lon
   adam_clip_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       w, g, m, v, n, lr_t, beta1, beta2, eps, grad_scale, is_kernel);
   ZKB_LAUNCH_CHECK("adam_clip_kernel");
+  return ZKB_OK;
+}
+
+// ============================================================================================
+// Allocation-free BatchNorm(train) + sign
+// ============================================================================================
+// Some hosts of this library are handed device buffers for inputs and outputs only and are not
+// allowed to obtain device memory themselves: an operator callback running inside another
+// runtime (the runtime owns the allocator and a stray cudaMalloc/cudaFree would stall the whole
+// device behind its back), or a latency-bound loop that cannot afford the implicit device-wide
+// synchronisation those calls carry.  The three-call sequence zkb_bn_stats -> zkb_bn_finalize ->
+// zkb_bn_apply_sign needs per-channel accumulators and statistics that such a caller has nowhere
+// to put.  zkb_bn_train_sign_static keeps them in the fixed array below instead.
+//
+// The array lives in every CUDA context that loads the library (about 96 KiB per GPU, until the
+// process exits) and is shared by ALL calls on that GPU: it still holds the previous call's values
+// on entry (the entry point clears what must start at zero), and two calls whose kernels overlap
+// on the GPU -- different streams, different host threads -- corrupt each other.
+namespace zkb {
+constexpr int kStaticBnMaxChannels = 4096;
+struct StaticBnScratch {
+  double sum[kStaticBnMaxChannels];
+  double sumsq[kStaticBnMaxChannels];
+  float mean[kStaticBnMaxChannels];
+  float rstd[kStaticBnMaxChannels];
+};
+static __device__ __align__(256) unsigned char g_static_bn_scratch[sizeof(StaticBnScratch)];
+}  // namespace zkb
+
+// Host code must not hand `g_static_bn_scratch` to a kernel directly: on the host that name is
+// only a stand-in for the symbol.  The device address is looked up once per device, with that
+// device current, and cached.
+static int static_bn_scratch(StaticBnScratch** out) {
+  static StaticBnScratch* cache[64] = {nullptr};
+  static std::mutex mu;
+  int dev = -1;
+  ZKB_CUDA(cudaGetDevice(&dev));
+  ZKB_REQUIRE(dev >= 0 && dev < 64, "bn_train_sign_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache[dev] == nullptr) {
+    void* p = nullptr;
+    ZKB_CUDA(cudaGetSymbolAddress(&p, g_static_bn_scratch));
+    ZKB_REQUIRE(p != nullptr, "bn_train_sign_static: scratch symbol has no device address");
+    cache[dev] = static_cast<StaticBnScratch*>(p);
+  }
+  *out = cache[dev];
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_train_sign_static_max_channels() { return kStaticBnMaxChannels; }
+
+ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows, int C,
+                                     const float* beta, float eps, float momentum, int bessel,
+                                     float* moving_mean, float* moving_var, void* s_out_bf16,
+                                     float* a_out, void* stream) {
+  const int vec = x_is_i16 ? 8 : 4;
+  ZKB_REQUIRE(C <= kStaticBnMaxChannels,
+              "bn_train_sign_static: C=%d exceeds the built-in scratch (at most %d channels); use "
+              "zkb_bn_stats/zkb_bn_finalize/zkb_bn_apply_sign with caller-provided buffers",
+              C, kStaticBnMaxChannels);
+  int rc = check_rows_c("bn_train_sign_static", x, rows, C, vec);
+  if (rc) return rc;
+  ZKB_REQUIRE(rows > 0, "bn_train_sign_static: rows must be positive");
+  ZKB_REQUIRE(beta && (s_out_bf16 || a_out), "bn_train_sign_static: null beta or no output");
+  ZKB_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr),
+              "bn_train_sign_static: moving_mean and moving_var go together");
+  StaticBnScratch* sc = nullptr;
+  rc = static_bn_scratch(&sc);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // the accumulators are summed into: wipe whatever the previous call left there
+  ZKB_CUDA(cudaMemsetAsync(sc->sum, 0, sizeof(double) * C, st));
+  ZKB_CUDA(cudaMemsetAsync(sc->sumsq, 0, sizeof(double) * C, st));
+  const int lanes = 256 / (C / vec);
+  const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 4);
+  const size_t smem = 2 * 256 * vec * sizeof(double);
+  const int grid_a = grid_for(rows * (C / vec), 256, 16);
+  if (x_is_i16) {
+    bn_stats_kernel<int16_t><<<grid_s, 256, smem, st>>>(static_cast<const int16_t*>(x), rows, C,
+                                                        sc->sum, sc->sumsq);
+    ZKB_LAUNCH_CHECK("bn_stats_kernel");
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(sc->sum, sc->sumsq, static_cast<double>(rows),
+                                                        eps, momentum, bessel, C, sc->mean, sc->rstd,
+                                                        moving_mean, moving_var);
+    ZKB_LAUNCH_CHECK("bn_finalize_kernel");
+    bn_apply_sign_kernel<int16_t><<<grid_a, 256, 0, st>>>(static_cast<const int16_t*>(x), rows, C,
+                                                          sc->mean, sc->rstd, beta,
+                                                          static_cast<uint16_t*>(s_out_bf16), a_out);
+  } else {
+    bn_stats_kernel<float><<<grid_s, 256, smem, st>>>(static_cast<const float*>(x), rows, C,
+                                                      sc->sum, sc->sumsq);
+    ZKB_LAUNCH_CHECK("bn_stats_kernel");
+    bn_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(sc->sum, sc->sumsq, static_cast<double>(rows),
+                                                        eps, momentum, bessel, C, sc->mean, sc->rstd,
+                                                        moving_mean, moving_var);
+    ZKB_LAUNCH_CHECK("bn_finalize_kernel");
+    bn_apply_sign_kernel<float><<<grid_a, 256, 0, st>>>(static_cast<const float*>(x), rows, C,
+                                                        sc->mean, sc->rstd, beta,
+                                                        static_cast<uint16_t*>(s_out_bf16), a_out);
+  }
+  ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
   return ZKB_OK;
 }

@@ -54,6 +54,7 @@ SIGNATURES = {
     "zkb_prep_dense_weights": [P, I, I, I, P, P, P],
     "zkb_sign_f32": [P, P, L, P],
     "zkb_adam_clip": [P, P, P, P, L, F, F, F, F, F, I, P],
+    "zkb_bn_train_sign_static": [P, I, L, I, P, F, F, I, P, P, P, P, P],
 }
 
 _lib = None
