@@ -1,0 +1,4 @@
+"""Alias of zookeeper_b200.tf.experiment (import path of the reference)."""
+import zookeeper_b200.tf.experiment as _m
+
+globals().update({k: v for k, v in vars(_m).items() if not k.startswith("__")})
