@@ -323,9 +323,16 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
   constexpr int VEC = Vec16<T>::N;
   const int tpr = C / VEC;
   const long long total = rows * tpr;
+  // blockDim and the grid stride are multiples of tpr, so a thread keeps one channel group:
+  // its per-channel parameters live in registers for the whole loop.
+  const int cl = threadIdx.x % tpr;
+  float mu[VEC], rs[VEC], be[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j]; be[j] = beta[cl * VEC + j];
+  }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cl = static_cast<int>(i % tpr);
     const long long r = i / tpr;
     Vec16<T> v;
     v.load(x + r * C + cl * VEC);
@@ -333,8 +340,7 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
     float a[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
-      const int c = cl * VEC + j;
-      a[j] = (v.get(j) - mean[c]) * rstd[c] + beta[c];
+      a[j] = (v.get(j) - mu[j]) * rs[j] + be[j];
       s[j] = pm1_bf16(a[j] >= 0.0f);
     }
     if (s_out) {
@@ -479,6 +485,18 @@ softmax_ce_kernel(const float* __restrict__ logits, int ld, const int* __restric
 // BatchNorm backward.  g is the gradient w.r.t. sign(a) (ste != 0: masked by |a| <= 1) or w.r.t.
 // a itself (ste == 0, last layer).  Pass 1: per-channel sum(da), sum(da * xhat).
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void load4(const float* p, float (&o)[4]) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = t.w;
+}
+__device__ __forceinline__ void load4(const int16_t* p, float (&o)[4]) {
+  const uint2 t = *reinterpret_cast<const uint2*>(p);
+  o[0] = static_cast<float>(static_cast<int16_t>(t.x & 0xFFFFu));
+  o[1] = static_cast<float>(static_cast<int16_t>(t.x >> 16));
+  o[2] = static_cast<float>(static_cast<int16_t>(t.y & 0xFFFFu));
+  o[3] = static_cast<float>(static_cast<int16_t>(t.y >> 16));
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long long rows, int C,
@@ -505,10 +523,11 @@ bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long 
          r += static_cast<long long>(gridDim.x) * lanes) {
       const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
       const float gg[4] = {gv.x, gv.y, gv.z, gv.w};
-      const T* xp = x + r * C + cl * VEC;
+      float xv[4];
+      load4(x + r * C + cl * VEC, xv);
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
-        const float xh = (static_cast<float>(xp[j]) - mu[j]) * rs[j];
+        const float xh = (xv[j] - mu[j]) * rs[j];
         const float a = xh + be[j];
         const float da = (ste && fabsf(a) > 1.0f) ? 0.f : gg[j];
         f0[j] += da;
@@ -555,21 +574,27 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
   const int tpr = C / VEC;
   const long long total = rows * tpr;
   const int PH = H / 2, PW = W / 2;
+  const int cl = threadIdx.x % tpr;   // fixed per thread (blockDim and grid stride are multiples of tpr)
+  float mu[VEC], rs[VEC], be[VEC], mda[VEC], mdx[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    const int c = cl * VEC + j;
+    mu[j] = mean[c]; rs[j] = rstd[c]; be[j] = beta[c]; mda[j] = mean_da[c]; mdx[j] = mean_dax[c];
+  }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int cl = static_cast<int>(i % tpr);
     const long long r = i / tpr;
     const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
     const float gg[4] = {gv.x, gv.y, gv.z, gv.w};
-    const T* xp = x + r * C + cl * VEC;
+    float xv[4];
+    load4(x + r * C + cl * VEC, xv);
     float dx[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
-      const int c = cl * VEC + j;
-      const float xh = (static_cast<float>(xp[j]) - mean[c]) * rstd[c];
-      const float a = xh + beta[c];
+      const float xh = (xv[j] - mu[j]) * rs[j];
+      const float a = xh + be[j];
       const float da = (ste && fabsf(a) > 1.0f) ? 0.f : gg[j];
-      dx[j] = rstd[c] * (da - mean_da[c] - xh * mean_dax[c]);
+      dx[j] = rs[j] * (da - mda[j] - xh * mdx[j]);
     }
     if (out_mode == 0) {
       *reinterpret_cast<float4*>(out_f32 + r * C + cl * VEC) = make_float4(dx[0], dx[1], dx[2], dx[3]);
@@ -1075,5 +1100,309 @@ ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows
                                                         static_cast<uint16_t*>(s_out_bf16), a_out);
   }
   ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
+  return ZKB_OK;
+}
+
+// ============================================================================================
+// First layer, fused with its BatchNorm: the K = ks*ks*Cin (9 or 27) float conv is recomputed from
+// the image wherever its output is needed instead of being stored.  At batch 4096 the stored map
+// would be 1.4 GB written once and read four times; the image it is recomputed from is 12.8 MB.
+//   stats   : y on the fly -> per-channel sum / sumsq
+//   bn_sign : y -> (y-mean)*rstd+beta -> sign as pm1 bf16
+//   bwd_red : g (grad wrt sign output) + recomputed a, xhat -> sum(da), sum(da*xhat)
+//   bwd_wgr : dy = rstd*(da - mean_da - xhat*mean_dax) on the fly -> dW[k][co] += x[pix+tap]*dy
+// Thread = 4 output channels of one pixel; a block walks pixels with 256/(Cout/4) pixel lanes.
+// Replaces the same reference lines as zkb_conv_first_fwd + zkb_bn_* (larq_experiment.py:62-70).
+// ============================================================================================
+namespace zkb {
+
+template <int KS, int CIN>
+struct FirstConv {
+  static constexpr int K = KS * KS * CIN;
+  // y[4] for channels c4..c4+3 of pixel pix; xv receives the K input taps.
+  __device__ static __forceinline__ void at(const float* __restrict__ x, const float* s_w, int Cout,
+                                            long long pix, int H, int W, int c4, float (&xv)[K],
+                                            float (&y)[4]) {
+    const int OH = H - KS + 1, OW = W - KS + 1;
+    const int ow = static_cast<int>(pix % OW);
+    const long long t = pix / OW;
+    const int oh = static_cast<int>(t % OH);
+    const long long b = t / OH;
+    const float* base = x + ((b * H + oh) * W + ow) * CIN;
+#pragma unroll
+    for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < KS; ++kw)
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci)
+          xv[(kh * KS + kw) * CIN + ci] = __ldg(base + (kh * W + kw) * CIN + ci);
+    y[0] = y[1] = y[2] = y[3] = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const float4 w = *reinterpret_cast<const float4*>(s_w + k * Cout + c4);
+      y[0] = fmaf(xv[k], w.x, y[0]);
+      y[1] = fmaf(xv[k], w.y, y[1]);
+      y[2] = fmaf(xv[k], w.z, y[2]);
+      y[3] = fmaf(xv[k], w.w, y[3]);
+    }
+  }
+};
+
+// dynamic smem: [2 * 256 * 4 doubles for block_channel_reduce][K * Cout floats of sign(W)]
+__device__ __forceinline__ float* first_conv_weights_smem() {
+  extern __shared__ double s_red[];
+  return reinterpret_cast<float*>(s_red + 2 * 256 * 4);
+}
+
+template <int KS, int CIN>
+__global__ void __launch_bounds__(256)
+conv_first_bn_stats_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
+                           int W, int Cout, double* __restrict__ sum, double* __restrict__ sumsq) {
+  using FC = FirstConv<KS, CIN>;
+  float* s_w = first_conv_weights_smem();
+  for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
+  __syncthreads();
+  const int tpr = Cout / 4, lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
+  double a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
+  float f0[4] = {0, 0, 0, 0}, f1[4] = {0, 0, 0, 0};
+  int n = 0;
+  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
+       pix += static_cast<long long>(gridDim.x) * lanes) {
+    float xv[FC::K], y[4];
+    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { f0[j] += y[j]; f1[j] = fmaf(y[j], y[j], f1[j]); }
+    if (++n == 32) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
+      n = 0;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
+  block_channel_reduce<4>(a0, a1, tpr, Cout, sum, sumsq);
+}
+
+template <int KS, int CIN>
+__global__ void __launch_bounds__(256)
+conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
+                          int W, int Cout, const float* __restrict__ mean,
+                          const float* __restrict__ rstd, const float* __restrict__ beta,
+                          uint16_t* __restrict__ s_out) {
+  using FC = FirstConv<KS, CIN>;
+  float* s_w = first_conv_weights_smem();
+  for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
+  __syncthreads();
+  const int tpr = Cout / 4, lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
+  float mu[4], rs[4], be[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { mu[j] = mean[cl * 4 + j]; rs[j] = rstd[cl * 4 + j]; be[j] = beta[cl * 4 + j]; }
+  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
+       pix += static_cast<long long>(gridDim.x) * lanes) {
+    float xv[FC::K], y[4];
+    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+    uint16_t s[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) s[j] = pm1_bf16((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f);
+    *reinterpret_cast<uint2*>(s_out + pix * Cout + cl * 4) =
+        make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
+  }
+}
+
+template <int KS, int CIN>
+__global__ void __launch_bounds__(256)
+conv_first_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ wq,
+                             const float* __restrict__ g, int B, int H, int W, int Cout,
+                             const float* __restrict__ mean, const float* __restrict__ rstd,
+                             const float* __restrict__ beta, double* __restrict__ sum_da,
+                             double* __restrict__ sum_dax) {
+  using FC = FirstConv<KS, CIN>;
+  float* s_w = first_conv_weights_smem();
+  for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
+  __syncthreads();
+  const int tpr = Cout / 4, lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
+  float mu[4], rs[4], be[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { mu[j] = mean[cl * 4 + j]; rs[j] = rstd[cl * 4 + j]; be[j] = beta[cl * 4 + j]; }
+  double a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
+  float f0[4] = {0, 0, 0, 0}, f1[4] = {0, 0, 0, 0};
+  int n = 0;
+  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
+       pix += static_cast<long long>(gridDim.x) * lanes) {
+    float gg[4];
+    load4(g + pix * Cout + cl * 4, gg);
+    float xv[FC::K], y[4];
+    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float xh = (y[j] - mu[j]) * rs[j];
+      const float da = (fabsf(xh + be[j]) > 1.0f) ? 0.f : gg[j];
+      f0[j] += da;
+      f1[j] = fmaf(da, xh, f1[j]);
+    }
+    if (++n == 64) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
+      n = 0;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
+  block_channel_reduce<4>(a0, a1, tpr, Cout, sum_da, sum_dax);
+}
+
+template <int KS, int CIN>
+__global__ void __launch_bounds__(256)
+conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ wq,
+                            const float* __restrict__ g, int B, int H, int W, int Cout,
+                            const float* __restrict__ mean, const float* __restrict__ rstd,
+                            const float* __restrict__ beta, const float* __restrict__ mean_da,
+                            const float* __restrict__ mean_dax, float* __restrict__ dw) {
+  using FC = FirstConv<KS, CIN>;
+  float* s_w = first_conv_weights_smem();
+  for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
+  __syncthreads();
+  const int tpr = Cout / 4, lanes = blockDim.x / tpr;
+  const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
+  float mu[4], rs[4], be[4], mda[4], mdx[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = cl * 4 + j;
+    mu[j] = mean[c]; rs[j] = rstd[c]; be[j] = beta[c]; mda[j] = mean_da[c]; mdx[j] = mean_dax[c];
+  }
+  float acc[FC::K][4];
+#pragma unroll
+  for (int k = 0; k < FC::K; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
+  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
+       pix += static_cast<long long>(gridDim.x) * lanes) {
+    float gg[4];
+    load4(g + pix * Cout + cl * 4, gg);
+    float xv[FC::K], y[4], dy[4];
+    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float xh = (y[j] - mu[j]) * rs[j];
+      const float da = (fabsf(xh + be[j]) > 1.0f) ? 0.f : gg[j];
+      dy[j] = rs[j] * (da - mda[j] - xh * mdx[j]);
+    }
+#pragma unroll
+    for (int k = 0; k < FC::K; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[k][j] = fmaf(xv[k], dy[j], acc[k][j]);
+  }
+  // combine the pixel lanes of the block through shared memory, one tap at a time
+  __syncthreads();
+  float* s_acc = reinterpret_cast<float*>(first_conv_weights_smem());  // weights no longer needed
+  for (int k = 0; k < FC::K; ++k) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) s_acc[rl * Cout + cl * 4 + j] = acc[k][j];
+    __syncthreads();
+    for (int c = threadIdx.x; c < Cout; c += blockDim.x) {
+      float t = 0.f;
+      for (int r = 0; r < lanes; ++r) t += s_acc[r * Cout + c];
+      atomicAdd(dw + k * Cout + c, t);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace zkb
+
+static int first_conv_check(const char* who, const void* x, const void* wq, int B, int H, int W,
+                            int Cin, int Cout, int ksize) {
+  ZKB_REQUIRE(x && wq, "%s: null pointer", who);
+  ZKB_REQUIRE(ksize == 3 && (Cin == 1 || Cin == 3),
+              "%s: only 3x3 kernels over 1 or 3 input channels are built", who);
+  ZKB_REQUIRE(Cout % 4 == 0 && Cout / 4 <= 256 && 256 % (Cout / 4) == 0,
+              "%s: Cout=%d must be a multiple of 4 with Cout/4 dividing 256", who, Cout);
+  ZKB_REQUIRE(B >= 0 && H >= ksize && W >= ksize, "%s: bad shape", who);
+  return ZKB_OK;
+}
+
+static size_t first_conv_smem(int K, int Cout) {
+  const size_t w = static_cast<size_t>(K) * Cout * sizeof(float);
+  const size_t lanes_acc = static_cast<size_t>(256 / (Cout / 4)) * Cout * sizeof(float);
+  return 2 * 256 * 4 * sizeof(double) + (w > lanes_acc ? w : lanes_acc);
+}
+
+static int first_conv_grid(int B, int H, int W, int Cout) {
+  const long long pixels = static_cast<long long>(B) * (H - 2) * (W - 2);
+  const int lanes = 256 / (Cout / 4);
+  long long g = (pixels + lanes * 16 - 1) / (lanes * 16);
+  const long long cap = static_cast<long long>(zkb_sm_count()) * 6;
+  if (g > cap) g = cap;
+  return g < 1 ? 1 : static_cast<int>(g);
+}
+
+#define ZKB_FIRST_DISPATCH(kernel, ...)                                                   \
+  do {                                                                                    \
+    const size_t smem__ = first_conv_smem(9 * Cin, Cout);                                 \
+    const int grid__ = first_conv_grid(B, H, W, Cout);                                    \
+    cudaStream_t st__ = static_cast<cudaStream_t>(stream);                                \
+    if (Cin == 1) {                                                                       \
+      kernel<3, 1><<<grid__, 256, smem__, st__>>>(__VA_ARGS__);                           \
+    } else {                                                                              \
+      ZKB_CUDA(cudaFuncSetAttribute(kernel<3, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                    static_cast<int>(smem__)));                           \
+      kernel<3, 3><<<grid__, 256, smem__, st__>>>(__VA_ARGS__);                           \
+    }                                                                                     \
+    ZKB_LAUNCH_CHECK(#kernel);                                                            \
+  } while (0)
+
+ZKB_API int zkb_conv_first_bn_stats(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
+                                    int Cout, int ksize, double* sum, double* sumsq, void* stream) {
+  int rc = first_conv_check("conv_first_bn_stats", x, wq_k_co, B, H, W, Cin, Cout, ksize);
+  if (rc) return rc;
+  ZKB_REQUIRE(sum && sumsq, "conv_first_bn_stats: null accumulator");
+  if (B == 0) return ZKB_OK;
+  ZKB_FIRST_DISPATCH(conv_first_bn_stats_kernel, x, wq_k_co, B, H, W, Cout, sum, sumsq);
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_bn_sign(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
+                                   int Cout, int ksize, const float* mean, const float* rstd,
+                                   const float* beta, void* s_out_bf16, void* stream) {
+  int rc = first_conv_check("conv_first_bn_sign", x, wq_k_co, B, H, W, Cin, Cout, ksize);
+  if (rc) return rc;
+  ZKB_REQUIRE(mean && rstd && beta && s_out_bf16, "conv_first_bn_sign: null pointer");
+  if (B == 0) return ZKB_OK;
+  ZKB_FIRST_DISPATCH(conv_first_bn_sign_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
+                     static_cast<uint16_t*>(s_out_bf16));
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_bwd_reduce(const float* x, const float* wq_k_co, const float* g, int B,
+                                      int H, int W, int Cin, int Cout, int ksize, const float* mean,
+                                      const float* rstd, const float* beta, double* sum_da,
+                                      double* sum_dax, void* stream) {
+  int rc = first_conv_check("conv_first_bwd_reduce", x, wq_k_co, B, H, W, Cin, Cout, ksize);
+  if (rc) return rc;
+  ZKB_REQUIRE(g && mean && rstd && beta && sum_da && sum_dax, "conv_first_bwd_reduce: null pointer");
+  ZKB_REQUIRE(ZKB_ALIGNED16(g), "conv_first_bwd_reduce: g must be 16-byte aligned");
+  if (B == 0) return ZKB_OK;
+  ZKB_FIRST_DISPATCH(conv_first_bwd_reduce_kernel, x, wq_k_co, g, B, H, W, Cout, mean, rstd, beta,
+                     sum_da, sum_dax);
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_bwd_wgrad(const float* x, const float* wq_k_co, const float* g, int B,
+                                     int H, int W, int Cin, int Cout, int ksize, const float* mean,
+                                     const float* rstd, const float* beta, const float* mean_da,
+                                     const float* mean_dax, float* dw_k_co, void* stream) {
+  int rc = first_conv_check("conv_first_bwd_wgrad", x, wq_k_co, B, H, W, Cin, Cout, ksize);
+  if (rc) return rc;
+  ZKB_REQUIRE(g && mean && rstd && beta && mean_da && mean_dax && dw_k_co,
+              "conv_first_bwd_wgrad: null pointer");
+  ZKB_REQUIRE(ZKB_ALIGNED16(g), "conv_first_bwd_wgrad: g must be 16-byte aligned");
+  if (B == 0) return ZKB_OK;
+  ZKB_FIRST_DISPATCH(conv_first_bwd_wgrad_kernel, x, wq_k_co, g, B, H, W, Cout, mean, rstd, beta,
+                     mean_da, mean_dax, dw_k_co);
   return ZKB_OK;
 }

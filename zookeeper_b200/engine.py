@@ -26,6 +26,7 @@ import numpy as np
 import torch
 
 from . import native as zn
+from .dataparallel import DataParallel
 
 BN_EPS = 1e-3
 BN_MOMENTUM = 0.99
@@ -66,9 +67,9 @@ def binarynet_layers(input_shape=(28, 28, 1), filters=128, dense_units=1024, num
     for _ in range(3):
         h, w = h // 2, w // 2
     layers += [
-        LayerSpec("dense", h * w * 4 * f, dense_units),
-        LayerSpec("dense", dense_units, dense_units),
-        LayerSpec("dense", dense_units, num_classes),
+        LayerSpec("dense", h * w * 4 * f, dense_units, 1, "valid"),
+        LayerSpec("dense", dense_units, dense_units, 1, "valid"),
+        LayerSpec("dense", dense_units, num_classes, 1, "valid"),
     ]
     return layers
 
@@ -103,9 +104,8 @@ class BinaryNetEngine:
         self.num_classes = int(num_classes)
         self.lr, self.b1, self.b2, self.eps = float(learning_rate), beta_1, beta_2, epsilon
         self.pg = process_group
-        self.world = 1
-        if process_group is not None or (torch.distributed.is_available() and torch.distributed.is_initialized()):
-            self.world = torch.distributed.get_world_size(process_group)
+        self.dp = DataParallel(process_group)
+        self.world = self.dp.world
         self.sync_bn = bool(sync_bn) and self.world > 1
         self.step_count = 0
         self.launches_per_step = 0
@@ -327,7 +327,7 @@ class BinaryNetEngine:
                    B, IH, IW, C, H, W, pad_size, int(training), int(binarize), self.num_classes, seed, step)
 
     def _all_reduce(self, t: torch.Tensor):
-        torch.distributed.all_reduce(t, group=self.pg)
+        self.dp.all_reduce_sum_(t)
 
     def _bn_forward(self, L, x, is_i16: bool, rows: int, stats_done: bool, training: bool = True):
         cp = L.cp
