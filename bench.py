@@ -170,7 +170,7 @@ def algorithmic_work(eng, name, tag):
         M, N, K = B * oh * ow, l.cout, l.ksize * l.ksize * l.cin
     else:
         M, N, K = B, l.cout, l.cin
-    if name in ("zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
+    if name in ("zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
                 "zkb_bconv2d_wgrad", "zkb_bdense_wgrad"):
         return ("flop", 2.0 * M * N * K)  # split terms are implementation overhead, not counted
     rows, C = L.bn_rows, L.cp
@@ -181,8 +181,10 @@ def algorithmic_work(eng, name, tag):
         "zkb_maxpool2_i16": (M * N * 2) + rows * C * 3,
         "zkb_bn_bwd_reduce": rows * C * (4 + xb),
         "zkb_bn_bwd_apply": rows * C * (4 + xb) + M * N * 4,
-        "zkb_conv_first_fwd": M * N * 4 + B * 28 * 28 * 4,
-        "zkb_conv_first_wgrad": M * N * 4 + B * 28 * 28 * 4,
+        "zkb_conv_first_bn_stats": B * 28 * 28 * 4,
+        "zkb_conv_first_bn_sign": M * N * 2 + B * 28 * 28 * 4,
+        "zkb_conv_first_bwd_reduce": M * N * 4 + B * 28 * 28 * 4,
+        "zkb_conv_first_bwd_wgrad": M * N * 4 + B * 28 * 28 * 4,
     }
     if name in table:
         return ("byte", float(table[name]))

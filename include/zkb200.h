@@ -63,6 +63,29 @@ int zkb_conv_first_fwd(const float* x, const float* wq_k_co, float* y, int B, in
 int zkb_conv_first_wgrad(const float* x, const float* dy, float* dw_k_co, int B, int H, int W,
                          int Cin, int Cout, int ksize, void* stream);
 
+/* First layer fused with its BatchNormalization: the small conv is recomputed from the image
+ * inside each pass, so its [B,OH,OW,Cout] float map is never written to memory.
+ *   bn_stats  : per-channel sum / sumsq of conv(x, wq)          (then zkb_bn_finalize)
+ *   bn_sign   : sign((conv - mean)*rstd + beta) as pm1 bf16
+ *   bwd_reduce: g = grad w.r.t. that sign; sum(da), sum(da*xhat) with the ste mask |a| <= 1
+ *               (then zkb_bn_bwd_finalize)
+ *   bwd_wgrad : dW[k][co] += sum_pix x[pix+tap k] * rstd*(da - mean_da - xhat*mean_dax)
+ * Replaces: examples/larq_experiment.py:62-70 (first QuantConv2D + BatchNormalization) and their
+ *           autodiff in model.fit (:147-153). */
+int zkb_conv_first_bn_stats(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
+                            int Cout, int ksize, double* sum, double* sumsq, void* stream);
+int zkb_conv_first_bn_sign(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
+                           int Cout, int ksize, const float* mean, const float* rstd,
+                           const float* beta, void* s_out_bf16, void* s_out_i8, void* stream);
+int zkb_conv_first_bwd_reduce(const float* x, const float* wq_k_co, const float* g, int B, int H,
+                              int W, int Cin, int Cout, int ksize, const float* mean,
+                              const float* rstd, const float* beta, double* sum_da,
+                              double* sum_dax, void* stream);
+int zkb_conv_first_bwd_wgrad(const float* x, const float* wq_k_co, const float* g, int B, int H,
+                             int W, int Cin, int Cout, int ksize, const float* mean,
+                             const float* rstd, const float* beta, const float* mean_da,
+                             const float* mean_dax, float* dw_k_co, void* stream);
+
 /* ---- binary conv / dense on tcgen05 -------------------------------------------------------------
  * Forward: act_pm1 [NB,H,W,Cin] (conv) or [rows,K] (dense), pm1 bf16; weights as written by
  * zkb_prep_*_weights; y int16 (exact integer sums, |y| <= ks*ks*Cin).  'same' zero padding is
@@ -73,6 +96,14 @@ int zkb_bconv2d_fwd(const void* act_pm1, const void* wq_oc_k, void* y_i16, int N
                     int Cin, int Cout, int ksize, void* stream);
 int zkb_bdense_fwd(const void* act_pm1, const void* wq_n_k, void* y_i16, long long ldy, int rows,
                    int K, int N, void* stream);
+/* The same forward products on the int8 pipe (tcgen05 kind::i8, int32 accumulators): operands are
+ * int8 holding +1 / -1 (0 in padded weight rows); half the operand bytes and twice the MMA rate of
+ * the bf16 form, bit-identical y.  Cin % 128 == 0, K % 128 == 0.  This is the path the engine's
+ * forward runs. */
+int zkb_bconv2d_fwd_i8(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H, int W,
+                       int Cin, int Cout, int ksize, void* stream);
+int zkb_bdense_fwd_i8(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy, int rows,
+                      int K, int N, void* stream);
 /* Backward w.r.t. the input (before the STE mask): dx f32 [NB,H,W,Cin] / [rows,K].
  * Replaces: TF autodiff of the layers above (model.fit, examples/larq_experiment.py:147-153). */
 int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, void* dx_f32,
@@ -90,7 +121,8 @@ int zkb_bdense_wgrad(const void* act_pm1, const void* dy_hi, const void* dy_lo, 
  * x: f32 or int16 [rows][C].  stats: per-channel sum / sum of squares into double accumulators
  * (caller zeroes them).  finalize: mean, rstd = rsqrt(biased var + eps); moving <- moving*momentum
  * + batch*(1-momentum), with the Bessel-corrected variance when bessel != 0 (TF fused 4-D kernel).
- * apply_sign: a = (x-mean)*rstd + beta; s = sign(a) as pm1 bf16 and/or a itself.
+ * apply_sign: a = (x-mean)*rstd + beta; s = sign(a) as pm1 bf16 and/or int8 and/or a itself
+ *             (any output pointer may be NULL).
  * Replaces: tf.keras.layers.BatchNormalization(scale=False) examples/larq_experiment.py:70,75,79,
  *           84,88,93,96,98,100 and the ste_sign input quantizer of the following layer (:53). */
 int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum, double* sumsq,
@@ -100,7 +132,7 @@ int zkb_bn_finalize(const double* sum, const double* sumsq, double count, float 
                     float* moving_var, void* stream);
 int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C, const float* mean,
                       const float* rstd, const float* beta, void* s_out_bf16, float* a_out,
-                      void* stream);
+                      void* s_out_i8, void* stream);
 /* MaxPool2D(2,2) 'valid' on the integer conv output; first maximum in row-major window order wins
  * (arg = 0..3); also accumulates the BatchNorm statistics of the pooled map.
  * Replaces: tf.keras.layers.MaxPool2D examples/larq_experiment.py:74,83,92. */
@@ -131,11 +163,12 @@ int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long long rows
 /* ---- weights and optimizer ----------------------------------------------------------------------
  * sign(W) in the operand layouts of the GEMM engines (kernel_quantizer="ste_sign",
  * examples/larq_experiment.py:54,65): conv HWIO f32 -> fwd [Cout][tap][Cin], dgrad
- * [Cin][flipped tap][Cout]; dense [K][N] f32 -> fwd [Npad][K], dgrad [K][Npad] (pad = 0). */
+ * [Cin][flipped tap][Cout]; dense [K][N] f32 -> fwd [Npad][K], dgrad [K][Npad] (pad = 0);
+ * w_fwd_i8 (optional) receives the forward layout as int8 for the kind::i8 GEMM. */
 int zkb_prep_conv_weights(const float* w_hwio, int ksize, int Cin, int Cout, void* w_fwd,
-                          void* w_dgrad, void* stream);
+                          void* w_dgrad, void* w_fwd_i8, void* stream);
 int zkb_prep_dense_weights(const float* w_k_n, int K, int N, int Npad, void* w_fwd, void* w_dgrad,
-                           void* stream);
+                           void* w_fwd_i8, void* stream);
 int zkb_sign_f32(const float* w, float* out, long long n, void* stream);
 /* Adam in the operation order of TF's ApplyAdam (lr_t = lr*sqrt(1-b2^t)/(1-b1^t) computed by the
  * caller) followed, for kernels (is_kernel != 0), by the ste_sign gradient mask |w| <= 1 and the

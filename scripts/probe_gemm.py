@@ -67,7 +67,7 @@ def prep_conv(w_hwio):
     ks, _, cin, cout = w_hwio.shape
     wf = torch.empty(cout, ks * ks * cin, dtype=torch.bfloat16, device=dev)
     wd = torch.empty(cin, ks * ks * cout, dtype=torch.bfloat16, device=dev)
-    zn.call("zkb_prep_conv_weights", zn.ptr(w_hwio.float().contiguous()), ks, cin, cout, zn.ptr(wf), zn.ptr(wd), 0)
+    zn.call("zkb_prep_conv_weights", zn.ptr(w_hwio.float().contiguous()), ks, cin, cout, zn.ptr(wf), zn.ptr(wd), 0, 0)
     return wf, wd
 
 

@@ -101,7 +101,7 @@ def test_sign_pack_and_popcount_gemm_golden(native_lib):
 
 def test_three_formulations_of_the_binary_dense_forward_agree_at_full_size(native_lib):
     """Batch 4096 x K 4608 x N 1024 (dense1 of BinaryNet at configs[1]): tcgen05 (bf16 operands, f32
-    accumulate), CUDA-core XNOR-popcount over packed words, and a float matmul must give the same
+    accumulate), tcgen05 kind::i8 (int32 accumulate), CUDA-core XNOR-popcount over packed words, and a float matmul must give the same
     integers -- the exactness claim of DESIGN.md section 3.1."""
     from zookeeper_b200 import native as zn
 
@@ -117,9 +117,13 @@ def test_three_formulations_of_the_binary_dense_forward_agree_at_full_size(nativ
     y_pc = torch.empty(M, N, dtype=torch.int32, device="cuda")
     zn.call("zkb_bgemm_popc", zn.ptr(pa), zn.ptr(pw), zn.ptr(y_pc), N, M, N, K // 32, 0)
     torch.cuda.synchronize()
+    y_i8 = torch.empty(M, N, dtype=torch.int16, device="cuda")
+    zn.call("zkb_bdense_fwd_i8", zn.ptr(a), zn.ptr(w), zn.ptr(y_i8), N, M, K, N, 0)
+    torch.cuda.synchronize()
     ref = (a.float() @ w.float().t()).to(torch.int32)
     assert torch.equal(y_pc, ref)
     assert torch.equal(y_tc.to(torch.int32), ref)
+    assert torch.equal(y_i8.to(torch.int32), ref)
     assert int(ref.abs().max()) <= K and bool(((ref + K) % 2 == 0).all())    # parity of a +-1 sum
 
 
@@ -133,7 +137,10 @@ def _prep_conv(zn, w_hwio):
     ks, _, cin, cout = w_hwio.shape
     wf = torch.empty(cout, ks * ks * cin, dtype=torch.bfloat16, device="cuda")
     wd = torch.empty(cin, ks * ks * cout, dtype=torch.bfloat16, device="cuda")
-    zn.call("zkb_prep_conv_weights", zn.ptr(w_hwio.float().contiguous()), ks, cin, cout, zn.ptr(wf), zn.ptr(wd), 0)
+    wf8 = torch.empty(cout, ks * ks * cin, dtype=torch.int8, device="cuda")
+    zn.call("zkb_prep_conv_weights", zn.ptr(w_hwio.float().contiguous()), ks, cin, cout, zn.ptr(wf), zn.ptr(wd),
+            zn.ptr(wf8), 0)
+    _prep_conv.last_i8 = wf8
     return wf, wd
 
 
@@ -150,6 +157,12 @@ def test_binary_conv_forward_is_bit_exact_with_zero_same_padding(native_lib, B, 
     torch.cuda.synchronize()
     ref = _conv_ref(x, w)
     assert torch.equal(y.double(), ref)
+    # the same layer on the int8 pipe (kind::i8, int32 accumulators): identical integers
+    y8 = torch.full((B, H, W, Cout), -7, dtype=torch.int16, device="cuda")
+    x8 = x.contiguous()
+    zn.call("zkb_bconv2d_fwd_i8", zn.ptr(x8), zn.ptr(_prep_conv.last_i8), zn.ptr(y8), B, H, W, Cin, Cout, 3, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(y8, y)
     # border outputs sum fewer taps: corner has 4 of 9 -> |y| <= 4*Cin there
     assert float(ref[:, 0, 0].abs().max()) <= 4 * Cin
 

@@ -32,7 +32,7 @@ def _reference(zn, x, is_i16, C, beta, bessel):
     zn.call("zkb_bn_finalize", acc[0].data_ptr(), acc[1].data_ptr(), float(rows), EPS, MOM, bessel, C,
             zn.ptr(mean), zn.ptr(rstd), zn.ptr(mm), zn.ptr(mv), 0)
     zn.call("zkb_bn_apply_sign", zn.ptr(x), is_i16, rows, C, zn.ptr(mean), zn.ptr(rstd), zn.ptr(beta),
-            zn.ptr(s), zn.ptr(a), 0)
+            zn.ptr(s), zn.ptr(a), 0, 0)
     torch.cuda.synchronize()
     return s, a, mm, mv
 

@@ -319,7 +319,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const float* __restrict__ beta,
-                     uint16_t* __restrict__ s_out, float* __restrict__ a_out) {
+                     uint16_t* __restrict__ s_out, float* __restrict__ a_out,
+                     int8_t* __restrict__ s8_out = nullptr) {
   constexpr int VEC = Vec16<T>::N;
   const int tpr = C / VEC;
   const long long total = rows * tpr;
@@ -353,6 +354,21 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
         *reinterpret_cast<uint2*>(o) =
             make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
       }
+    }
+    if (s8_out) {
+      // the same signs as int8 (+1 / -1): operand of the kind::i8 forward GEMM
+      uint32_t w8[VEC / 4];
+#pragma unroll
+      for (int q = 0; q < VEC / 4; ++q) {
+        w8[q] = 0;
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          w8[q] |= ((s[4 * q + e] & 0x8000u) ? 0xFFu : 0x01u) << (8 * e);
+      }
+      if (VEC == 8)
+        *reinterpret_cast<uint2*>(s8_out + r * C + cl * VEC) = make_uint2(w8[0], w8[(VEC / 4) - 1]);
+      else
+        *reinterpret_cast<uint32_t*>(s8_out + r * C + cl * VEC) = w8[0];
     }
     if (a_out) {
       float* o = a_out + r * C + cl * VEC;
@@ -643,7 +659,8 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
 // conv: W f32 [ks,ks,Cin,Cout] (HWIO) -> fwd [Cout][tap][Cin], dgrad [Cin][tap_flipped][Cout] (bf16)
 __global__ void __launch_bounds__(256)
 prep_conv_weights_kernel(const float* __restrict__ w, int ks, int Cin, int Cout,
-                         uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad) {
+                         uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad,
+                         int8_t* __restrict__ w_fwd8) {
   const int taps = ks * ks;
   const long long total = static_cast<long long>(taps) * Cin * Cout;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
@@ -654,6 +671,7 @@ prep_conv_weights_kernel(const float* __restrict__ w, int ks, int Cin, int Cout,
     const int tap = static_cast<int>(t / Cin);
     const uint16_t s = pm1_bf16(w[i] >= 0.0f);
     w_fwd[(static_cast<long long>(co) * taps + tap) * Cin + ci] = s;
+    if (w_fwd8) w_fwd8[(static_cast<long long>(co) * taps + tap) * Cin + ci] = (s & 0x8000u) ? -1 : 1;
     const int kh = tap / ks, kw = tap % ks;
     const int ftap = (ks - 1 - kh) * ks + (ks - 1 - kw);
     w_dgrad[(static_cast<long long>(ci) * taps + ftap) * Cout + co] = s;
@@ -663,7 +681,8 @@ prep_conv_weights_kernel(const float* __restrict__ w, int ks, int Cin, int Cout,
 // dense: W f32 [K][N] -> fwd [Npad][K] (rows >= N zero), dgrad [K][Npad] (cols >= N zero)
 __global__ void __launch_bounds__(256)
 prep_dense_weights_kernel(const float* __restrict__ w, int K, int N, int Npad,
-                          uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad) {
+                          uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad,
+                          int8_t* __restrict__ w_fwd8) {
   const long long total = static_cast<long long>(K) * Npad;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -671,6 +690,7 @@ prep_dense_weights_kernel(const float* __restrict__ w, int K, int N, int Npad,
     const int k = static_cast<int>(i / Npad);
     const uint16_t s = (n < N) ? pm1_bf16(w[static_cast<long long>(k) * N + n] >= 0.0f) : 0;
     w_fwd[static_cast<long long>(n) * K + k] = s;
+    if (w_fwd8) w_fwd8[static_cast<long long>(n) * K + k] = (s == 0) ? 0 : ((s & 0x8000u) ? -1 : 1);
     w_dgrad[i] = s;
   }
 }
@@ -851,22 +871,22 @@ ZKB_API int zkb_bn_finalize(const double* sum, const double* sumsq, double count
 
 ZKB_API int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C, const float* mean,
                               const float* rstd, const float* beta, void* s_out_bf16, float* a_out,
-                              void* stream) {
+                              void* s_out_i8, void* stream) {
   const int vec = x_is_i16 ? 8 : 4;
   int rc = check_rows_c("bn_apply_sign", x, rows, C, vec);
   if (rc) return rc;
   ZKB_REQUIRE(mean && rstd && beta, "bn_apply_sign: null statistics");
-  ZKB_REQUIRE(s_out_bf16 || a_out, "bn_apply_sign: no output requested");
+  ZKB_REQUIRE(s_out_bf16 || a_out || s_out_i8, "bn_apply_sign: no output requested");
   if (rows == 0) return ZKB_OK;
   const int grid = grid_for(rows * (C / vec), 256, 16);
   if (x_is_i16)
     bn_apply_sign_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const int16_t*>(x), rows, C, mean, rstd, beta,
-        static_cast<uint16_t*>(s_out_bf16), a_out);
+        static_cast<uint16_t*>(s_out_bf16), a_out, static_cast<int8_t*>(s_out_i8));
   else
     bn_apply_sign_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const float*>(x), rows, C, mean, rstd, beta, static_cast<uint16_t*>(s_out_bf16),
-        a_out);
+        a_out, static_cast<int8_t*>(s_out_i8));
   ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
   return ZKB_OK;
 }
@@ -961,22 +981,24 @@ ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long l
 }
 
 ZKB_API int zkb_prep_conv_weights(const float* w_hwio, int ksize, int Cin, int Cout, void* w_fwd,
-                                  void* w_dgrad, void* stream) {
+                                  void* w_dgrad, void* w_fwd_i8, void* stream) {
   ZKB_REQUIRE(w_hwio && w_fwd && w_dgrad, "prep_conv_weights: null pointer");
   const long long total = static_cast<long long>(ksize) * ksize * Cin * Cout;
   prep_conv_weights_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      w_hwio, ksize, Cin, Cout, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad));
+      w_hwio, ksize, Cin, Cout, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad),
+      static_cast<int8_t*>(w_fwd_i8));
   ZKB_LAUNCH_CHECK("prep_conv_weights_kernel");
   return ZKB_OK;
 }
 
 ZKB_API int zkb_prep_dense_weights(const float* w_k_n, int K, int N, int Npad, void* w_fwd,
-                                   void* w_dgrad, void* stream) {
+                                   void* w_dgrad, void* w_fwd_i8, void* stream) {
   ZKB_REQUIRE(w_k_n && w_fwd && w_dgrad, "prep_dense_weights: null pointer");
   ZKB_REQUIRE(Npad >= N, "prep_dense_weights: Npad < N");
   const long long total = static_cast<long long>(K) * Npad;
   prep_dense_weights_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      w_k_n, K, N, Npad, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad));
+      w_k_n, K, N, Npad, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad),
+      static_cast<int8_t*>(w_fwd_i8));
   ZKB_LAUNCH_CHECK("prep_dense_weights_kernel");
   return ZKB_OK;
 }
@@ -1190,7 +1212,7 @@ __global__ void __launch_bounds__(256)
 conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
                           int W, int Cout, const float* __restrict__ mean,
                           const float* __restrict__ rstd, const float* __restrict__ beta,
-                          uint16_t* __restrict__ s_out) {
+                          uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out) {
   using FC = FirstConv<KS, CIN>;
   float* s_w = first_conv_weights_smem();
   for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
@@ -1210,6 +1232,12 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
     for (int j = 0; j < 4; ++j) s[j] = pm1_bf16((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f);
     *reinterpret_cast<uint2*>(s_out + pix * Cout + cl * 4) =
         make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
+    if (s8_out) {
+      uint32_t w8 = 0;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) w8 |= ((s[e] & 0x8000u) ? 0xFFu : 0x01u) << (8 * e);
+      *reinterpret_cast<uint32_t*>(s8_out + pix * Cout + cl * 4) = w8;
+    }
   }
 }
 
@@ -1368,13 +1396,13 @@ ZKB_API int zkb_conv_first_bn_stats(const float* x, const float* wq_k_co, int B,
 
 ZKB_API int zkb_conv_first_bn_sign(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
                                    int Cout, int ksize, const float* mean, const float* rstd,
-                                   const float* beta, void* s_out_bf16, void* stream) {
+                                   const float* beta, void* s_out_bf16, void* s_out_i8, void* stream) {
   int rc = first_conv_check("conv_first_bn_sign", x, wq_k_co, B, H, W, Cin, Cout, ksize);
   if (rc) return rc;
   ZKB_REQUIRE(mean && rstd && beta && s_out_bf16, "conv_first_bn_sign: null pointer");
   if (B == 0) return ZKB_OK;
   ZKB_FIRST_DISPATCH(conv_first_bn_sign_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
-                     static_cast<uint16_t*>(s_out_bf16));
+                     static_cast<uint16_t*>(s_out_bf16), static_cast<int8_t*>(s_out_i8));
   return ZKB_OK;
 }
 

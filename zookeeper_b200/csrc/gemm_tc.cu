@@ -16,6 +16,7 @@
 // TF runs for larq QuantConv2D / QuantDense (reference call sites:
 // examples/larq_experiment.py:71-73,76-82,85-91,95-99).
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "zkb_host.h"
 #include "zkb_ptx.cuh"
@@ -25,9 +26,11 @@ namespace zkb {
 static constexpr int kMaxStages = 8;
 static constexpr int kATileBytes = 128 * 128;  // 128 rows x 64 bf16
 static constexpr int kSmemBudget = 227 * 1024 - 2048;
+static constexpr int kEpiStagingBytes = 8 * 4096;  // one 4 KB TMA-store box per epilogue warp
 
 struct KGemmParams {
   int M, N;
+  int kelems;    // K elements per 128-byte row: 64 (bf16) or 128 (int8)
   int num_kb;    // 64-element k-blocks per A term
   int a_terms;   // 1 or 2
   int block_n;   // 32..256, multiple of 32
@@ -37,6 +40,7 @@ struct KGemmParams {
   int a_im2col;
   int OH, OW, pad, kw_taps, cblocks;
   int out_kind;  // 0: f32, 1: int16 (exact integers expected)
+  int is_i8;     // operands are signed int8 (+-1 / 0), accumulators int32 (kind::i8)
   void* out;
   long long ldo;
 };
@@ -56,9 +60,10 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
   return reinterpret_cast<uint8_t*>(a);
 }
 
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-                  const __grid_constant__ CUtensorMap tmB, const KGemmParams p) {
+                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+                  const KGemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
   SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem + static_cast<size_t>(p.num_stages) * p.stage_bytes);
@@ -74,7 +79,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(smem_u32(&ctl->tfull[a]), 1);
-      mbar_init(smem_u32(&ctl->tempty[a]), 128);
+      mbar_init(smem_u32(&ctl->tempty[a]), 256);
     }
     fence_mbar_init();
   }
@@ -82,6 +87,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     tma_prefetch_desc(&tmA0);
     if (p.a_terms == 2) tma_prefetch_desc(&tmA1);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmOut);
   }
   if (warp == 1) tmem_alloc_512(smem_u32(&ctl->tmem_base));
   tc_fence_before();
@@ -118,16 +124,16 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
             const int cb = kb - tap * p.cblocks;
             const int kh = tap / p.kw_taps;
             const int kw = tap - kh * p.kw_taps;
-            tma_load_im2col_4d(sA, &tmA0, full, cb * 64, ow - p.pad, oh - p.pad, img,
+            tma_load_im2col_4d(sA, &tmA0, full, cb * p.kelems, ow - p.pad, oh - p.pad, img,
                                static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
             if (p.a_terms == 2)
-              tma_load_im2col_4d(sA + kATileBytes, &tmA1, full, cb * 64, ow - p.pad, oh - p.pad,
+              tma_load_im2col_4d(sA + kATileBytes, &tmA1, full, cb * p.kelems, ow - p.pad, oh - p.pad,
                                  img, static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
           } else {
-            tma_load_2d(sA, &tmA0, full, kb * 64, m0);
-            if (p.a_terms == 2) tma_load_2d(sA + kATileBytes, &tmA1, full, kb * 64, m0);
+            tma_load_2d(sA, &tmA0, full, kb * p.kelems, m0);
+            if (p.a_terms == 2) tma_load_2d(sA + kATileBytes, &tmA1, full, kb * p.kelems, m0);
           }
-          tma_load_2d(sB, &tmB, full, kb * 64, n0);
+          tma_load_2d(sB, &tmB, full, kb * p.kelems, n0);
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
@@ -138,7 +144,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = umma_idesc_bf16(128, p.block_n, 0, 0);
+      const uint32_t idesc = p.is_i8 ? umma_idesc_s8(128, p.block_n) : umma_idesc_bf16(128, p.block_n, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -157,7 +163,11 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
             for (int k = 0; k < 4; ++k) {
               const uint64_t ad = umma_smem_desc_sw128(sA + t * kATileBytes + k * 32, 16, 1024);
               const uint64_t bd = umma_smem_desc_sw128(sB + k * 32, 16, 1024);
-              umma_f16(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              // a 128-byte row holds 64 bf16 or 128 int8: either way 4 MMAs of 32 bytes of K
+              if (p.is_i8)
+                umma_i8(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              else
+                umma_f16(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
             }
           }
           umma_commit(smem_u32(&ctl->empty[stage]));
@@ -172,57 +182,77 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
       }
     }
   } else {
-    // ------------------------------------------------------------ epilogue (warps 2..5)
-    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    // ------------------------------------------------------------ epilogue (warps 2..9)
+    // Two warps per TMEM lane quarter, alternating 128-byte-wide column units.  A unit is read
+    // from TMEM (tcgen05.ld 32x32b), converted, written to a 4 KB swizzled staging box in shared
+    // memory and stored with one TMA store per warp: full 128-byte lines, rows/columns beyond
+    // M/N are clipped by the TMA unit.
+    const int ew = warp - 2;
+    const int q = warp & 3;        // TMEM lane quarter this warp may read
+    const int half = ew >> 2;
+    const int unit_cols = p.out_kind == 0 ? 32 : 64;
+    const int units = (p.block_n + unit_cols - 1) / unit_cols;
+    const uint32_t stage_box = smem_u32(smem + static_cast<size_t>(p.num_stages) * p.stage_bytes +
+                                        1024 + static_cast<size_t>(ew) * 4096);
+    const uint32_t my_row = stage_box + static_cast<uint32_t>(lane) * 128u;
+    const uint32_t sw = static_cast<uint32_t>(lane & 7);
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int tm = tile / p.tiles_n;
       const int tn = tile - tm * p.tiles_n;
-      const long long row = static_cast<long long>(tm) * 128 + q * 32 + lane;
+      const int row0 = tm * 128 + q * 32;
       const int n0 = tn * p.block_n;
       mbar_wait(smem_u32(&ctl->tfull[as]), aphase);
       tc_fence_after();
       const uint32_t tbase =
           tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as) * 256u;
-      for (int c = 0; c < p.block_n / 32; ++c) {
+      for (int u = half; u < units; u += 2) {
+        const int c0 = u * unit_cols;
         uint32_t r[32];
-        tmem_ld_32x32(tbase + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_32x32(tbase + static_cast<uint32_t>(c0), r);
         tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (row < p.M && col0 < p.N) {
-          const bool full_cols = (col0 + 32 <= p.N);
-          if (p.out_kind == 0) {
-            float* o = reinterpret_cast<float*>(p.out) + row * p.ldo + col0;
-            if (full_cols) {
+        if (lane == 0) tma_store_wait_read_all();   // previous box of this warp has left smem
+        __syncwarp();
+        if (p.out_kind == 0) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                       __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-                *reinterpret_cast<float4*>(o + 4 * j) = v;
-              }
-            } else {
-              for (int j = 0; j < 32 && col0 + j < p.N; ++j) o[j] = __uint_as_float(r[j]);
-            }
-          } else {
-            int16_t* o = reinterpret_cast<int16_t*>(p.out) + row * p.ldo + col0;
-            if (full_cols) {
+          for (int j = 0; j < 8; ++j)
+            st_shared_v4(my_row + ((static_cast<uint32_t>(j) ^ sw) << 4), r[4 * j], r[4 * j + 1],
+                         r[4 * j + 2], r[4 * j + 3]);
+        } else {
+          uint32_t w[16];
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                uint32_t w[4];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const int lo = __float2int_rn(__uint_as_float(r[8 * j + 2 * e]));
-                  const int hi = __float2int_rn(__uint_as_float(r[8 * j + 2 * e + 1]));
-                  w[e] = (static_cast<uint32_t>(lo) & 0xFFFFu) | (static_cast<uint32_t>(hi) << 16);
-                }
-                *reinterpret_cast<uint4*>(o + 8 * j) = make_uint4(w[0], w[1], w[2], w[3]);
-              }
-            } else {
-              for (int j = 0; j < 32 && col0 + j < p.N; ++j)
-                o[j] = static_cast<int16_t>(__float2int_rn(__uint_as_float(r[j])));
-            }
+          for (int e = 0; e < 16; ++e) {
+            const int lo = p.is_i8 ? static_cast<int>(r[2 * e]) : __float2int_rn(__uint_as_float(r[2 * e]));
+            const int hi = p.is_i8 ? static_cast<int>(r[2 * e + 1])
+                                   : __float2int_rn(__uint_as_float(r[2 * e + 1]));
+            w[e] = (static_cast<uint32_t>(lo) & 0xFFFFu) | (static_cast<uint32_t>(hi) << 16);
           }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_shared_v4(my_row + ((static_cast<uint32_t>(j) ^ sw) << 4), w[4 * j], w[4 * j + 1],
+                         w[4 * j + 2], w[4 * j + 3]);
+          if (c0 + 32 < p.block_n) {   // second half of the 64-column int16 unit
+            tmem_ld_32x32(tbase + static_cast<uint32_t>(c0 + 32), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              const int lo = p.is_i8 ? static_cast<int>(r[2 * e]) : __float2int_rn(__uint_as_float(r[2 * e]));
+              const int hi = p.is_i8 ? static_cast<int>(r[2 * e + 1])
+                                     : __float2int_rn(__uint_as_float(r[2 * e + 1]));
+              w[e] = (static_cast<uint32_t>(lo) & 0xFFFFu) | (static_cast<uint32_t>(hi) << 16);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              st_shared_v4(my_row + ((static_cast<uint32_t>(j + 4) ^ sw) << 4), w[4 * j], w[4 * j + 1],
+                           w[4 * j + 2], w[4 * j + 3]);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmOut, stage_box, n0 + c0, row0);
+          tma_store_commit();
         }
       }
       tc_fence_before();
@@ -230,6 +260,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
       as ^= 1;
       if (as == 0) aphase ^= 1u;
     }
+    if (lane == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
@@ -244,11 +275,13 @@ struct WGemmParams {
   int n_valid;  // columns of D actually written (<= N)
   long long P;  // reduction length (pixels / batch rows)
   int b_terms;  // 1 or 2
-  int block_n;  // 64, 128 or 256
+  int block_n;  // 64 or 128
   int a_im2col;
   int OH, OW, pad, kw_taps, taps;
+  int tpi;      // taps per work item (a filter row for convs, 1 otherwise): they share the B tile
+  int kpix;     // reduction rows per pipeline stage (32 or 64)
   int ci_tiles, n_tiles, splits;
-  int chunks_per_split;  // 64-row chunks of P
+  int chunks_per_split;  // kpix-row chunks of P
   int num_stages, stage_bytes;
   float* out;
   long long ldo;
@@ -272,16 +305,17 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // work item -> (split, tap, ci_tile, n_tile); n fastest so that neighbours share the A stream.
+  // work item -> (split, tap group, ci_tile, n_tile); n fastest so that neighbours share the A stream.
   int wi = blockIdx.x;
   const int tn = wi % p.n_tiles;
   wi /= p.n_tiles;
   const int tc = wi % p.ci_tiles;
   wi /= p.ci_tiles;
-  const int tap = wi % p.taps;
-  const int split = wi / p.taps;
+  const int groups = p.taps / p.tpi;
+  const int tap0 = (wi % groups) * p.tpi;
+  const int split = wi / groups;
 
-  const long long total_chunks = (p.P + 63) / 64;
+  const long long total_chunks = (p.P + p.kpix - 1) / p.kpix;
   const long long chunk_lo = static_cast<long long>(split) * p.chunks_per_split;
   long long chunk_hi = chunk_lo + p.chunks_per_split;
   if (chunk_hi > total_chunks) chunk_hi = total_chunks;
@@ -305,43 +339,50 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
-  const int nb = p.block_n / 64;                 // 64-channel boxes of B per term
-  const int b_term_bytes = nb * 8192;
+  const int nb = p.block_n / 64;            // 64-channel boxes of B per term
+  const int box_bytes = p.kpix * 128;       // one [64 channels x kpix rows] box
+  const int a_tile_bytes = 2 * box_bytes;   // 128 channels of A
+  const int b_term_bytes = nb * box_bytes;
+  const int a_bytes = p.tpi * a_tile_bytes;
 
   if (n_chunks > 0) {
     if (warp == 0) {
       if (lane == 0) {
-        const int kh = tap / p.kw_taps;
-        const int kw = tap - kh * p.kw_taps;
         int stage = 0;
         uint32_t phase = 0;
         for (int ch = 0; ch < n_chunks; ++ch) {
-          const long long pix0 = (chunk_lo + ch) * 64;
+          const long long pix0 = (chunk_lo + ch) * p.kpix;
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
           const uint32_t full = smem_u32(&ctl->full[stage]);
           mbar_expect_tx(full, static_cast<uint32_t>(p.stage_bytes));
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
-          const uint32_t sB = sA + 16384;
+          const uint32_t sB = sA + a_bytes;
+          // B first: every tap's MMAs need it
+          for (int j = 0; j < nb; ++j) {
+            tma_load_2d(sB + j * box_bytes, &tmB0, full, tn * p.block_n + j * 64,
+                        static_cast<int>(pix0));
+            if (p.b_terms == 2)
+              tma_load_2d(sB + b_term_bytes + j * box_bytes, &tmB1, full, tn * p.block_n + j * 64,
+                          static_cast<int>(pix0));
+          }
           if (p.a_im2col) {
             const int hw = p.OH * p.OW;
             const int img = static_cast<int>(pix0 / hw);
             const int rem = static_cast<int>(pix0 - static_cast<long long>(img) * hw);
             const int oh = rem / p.OW;
             const int ow = rem - oh * p.OW;
-            for (int h = 0; h < 2; ++h)
-              tma_load_im2col_4d(sA + h * 8192, &tmA, full, tc * 128 + h * 64, ow - p.pad,
-                                 oh - p.pad, img, static_cast<uint16_t>(kw),
-                                 static_cast<uint16_t>(kh));
+            for (int t = 0; t < p.tpi; ++t) {
+              const int tap = tap0 + t;
+              const int kh = tap / p.kw_taps;
+              const int kw = tap - kh * p.kw_taps;
+              for (int h = 0; h < 2; ++h)
+                tma_load_im2col_4d(sA + t * a_tile_bytes + h * box_bytes, &tmA, full,
+                                   tc * 128 + h * 64, ow - p.pad, oh - p.pad, img,
+                                   static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
+            }
           } else {
             for (int h = 0; h < 2; ++h)
-              tma_load_2d(sA + h * 8192, &tmA, full, tc * 128 + h * 64, static_cast<int>(pix0));
-          }
-          for (int j = 0; j < nb; ++j) {
-            tma_load_2d(sB + j * 8192, &tmB0, full, tn * p.block_n + j * 64,
-                        static_cast<int>(pix0));
-            if (p.b_terms == 2)
-              tma_load_2d(sB + b_term_bytes + j * 8192, &tmB1, full, tn * p.block_n + j * 64,
-                          static_cast<int>(pix0));
+              tma_load_2d(sA + h * box_bytes, &tmA, full, tc * 128 + h * 64, static_cast<int>(pix0));
           }
           if (++stage == p.num_stages) {
             stage = 0;
@@ -352,21 +393,26 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     } else if (warp == 1) {
       if (lane == 0) {
         const uint32_t idesc = umma_idesc_bf16(128, p.block_n, 1, 1);
+        const int ksteps = p.kpix / 16;
         int stage = 0;
         uint32_t phase = 0;
         for (int ch = 0; ch < n_chunks; ++ch) {
           mbar_wait(smem_u32(&ctl->full[stage]), phase);
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
-          const uint32_t sB = sA + 16384;
-          for (int t = 0; t < p.b_terms; ++t) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each).
-              const uint64_t ad = umma_smem_desc_sw128(sA + k * 2048, 8192, 1024);
-              const uint64_t bd =
-                  umma_smem_desc_sw128(sB + t * b_term_bytes + k * 2048, 8192, 1024);
-              umma_f16(tmem_base, ad, bd, idesc, (ch | t | k) != 0 ? 1u : 0u);
+          const uint32_t sB = sA + a_bytes;
+          for (int t = 0; t < p.tpi; ++t) {
+            const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(t * p.block_n);
+            for (int bt = 0; bt < p.b_terms; ++bt) {
+              for (int k = 0; k < ksteps; ++k) {
+                // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each); the next 64-wide
+                // channel block of an operand starts box_bytes further on.
+                const uint64_t ad = umma_smem_desc_sw128(sA + t * a_tile_bytes + k * 2048,
+                                                         box_bytes, 1024);
+                const uint64_t bd = umma_smem_desc_sw128(sB + bt * b_term_bytes + k * 2048,
+                                                         box_bytes, 1024);
+                umma_f16(d_tmem, ad, bd, idesc, (ch | bt | k) != 0 ? 1u : 0u);
+              }
             }
           }
           umma_commit(smem_u32(&ctl->empty[stage]));
@@ -381,18 +427,22 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       const int q = warp & 3;
       mbar_wait(smem_u32(&ctl->tfull), 0);
       tc_fence_after();
-      const int row_in_tap = tc * 128 + q * 32 + lane;          // channel of A
-      const long long orow = static_cast<long long>(tap) * p.Ma + row_in_tap;
-      const uint32_t tbase = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-      for (int c = 0; c < p.block_n / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(tbase + static_cast<uint32_t>(c * 32), r);
-        tmem_ld_wait();
-        const int col0 = tn * p.block_n + c * 32;
-        if (row_in_tap < p.Ma) {
-          float* o = p.out + orow * p.ldo + col0;
-          for (int j = 0; j < 32; ++j)
-            if (col0 + j < p.n_valid) atomicAdd(o + j, __uint_as_float(r[j]));
+      const int row_in_tap = tc * 128 + q * 32 + lane;  // channel of A
+      for (int t = 0; t < p.tpi; ++t) {
+        const long long orow = static_cast<long long>(tap0 + t) * p.Ma + row_in_tap;
+        const uint32_t tbase =
+            tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * p.block_n);
+        for (int c = 0; c < p.block_n / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tbase + static_cast<uint32_t>(c * 32), r);
+          tmem_ld_wait();
+          const int col0 = tn * p.block_n + c * 32;
+          if (row_in_tap < p.Ma) {
+            float* o = p.out + orow * p.ldo + col0;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < p.n_valid) atomicAdd(o + j, __uint_as_float(r[j]));
+          }
         }
       }
     }
@@ -422,10 +472,16 @@ static int pick_block_n(int N) {
 // Bmat: bf16 [N][K] row-major.  out: f32 or int16 [M][ldo].
 static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, void* out,
                         int out_kind, long long ldo, long long M, int N, int K, int im2col, int NB,
-                        int H, int W, int C, int ksize, int pad, cudaStream_t stream) {
+                        int H, int W, int C, int ksize, int pad, cudaStream_t stream,
+                        int elem_bytes = 2) {
+  const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
+  const CUtensorMapDataType dt =
+      elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  ZKB_REQUIRE(elem_bytes == 2 || (elem_bytes == 1 && !A_lo && out_kind == 1),
+              "kgemm: int8 operands are for the single-term integer forward only");
   ZKB_REQUIRE(A_hi && Bmat && out, "kgemm: null pointer");
   ZKB_REQUIRE(M > 0 && N > 0 && K > 0, "kgemm: empty problem M=%lld N=%d K=%d", M, N, K);
-  ZKB_REQUIRE(K % 64 == 0, "kgemm: K=%d must be a multiple of 64", K);
+  ZKB_REQUIRE(K % kelems == 0, "kgemm: K=%d must be a multiple of %d", K, kelems);
   ZKB_REQUIRE(M < (1ll << 31) - 256, "kgemm: M=%lld too large", M);
   ZKB_REQUIRE(out_kind == 0 || out_kind == 1, "kgemm: out_kind must be 0 (f32) or 1 (i16)");
   ZKB_REQUIRE(ldo >= N, "kgemm: ldo=%lld < N=%d", ldo, N);
@@ -435,11 +491,13 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   KGemmParams p{};
   p.M = static_cast<int>(M);
   p.N = N;
-  p.num_kb = K / 64;
+  p.num_kb = K / kelems;
+  p.kelems = kelems;
+  p.is_i8 = elem_bytes == 1;
   p.a_terms = A_lo ? 2 : 1;
   p.block_n = pick_block_n(N);
   p.stage_bytes = p.a_terms * kATileBytes + p.block_n * 128;
-  p.num_stages = kSmemBudget / p.stage_bytes;
+  p.num_stages = (kSmemBudget - kEpiStagingBytes) / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
   ZKB_REQUIRE(p.num_stages >= 2, "kgemm: tile does not fit in shared memory");
   p.tiles_m = static_cast<int>((M + 127) / 128);
@@ -451,7 +509,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   CUtensorMap tmA0, tmA1, tmB;
   int rc;
   if (im2col) {
-    ZKB_REQUIRE(C % 64 == 0, "kgemm: channels C=%d must be a multiple of 64", C);
+    ZKB_REQUIRE(C % kelems == 0, "kgemm: channels C=%d must be a multiple of %d", C, kelems);
     ZKB_REQUIRE(K == ksize * ksize * C, "kgemm: K=%d != ksize^2*C", K);
     ZKB_REQUIRE(M == static_cast<long long>(NB) * H * W, "kgemm: M != NB*H*W");
     ZKB_REQUIRE(ksize == 2 * pad + 1, "kgemm: only 'same' windows (ksize == 2*pad+1)");
@@ -459,38 +517,47 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     p.OW = W;
     p.pad = pad;
     p.kw_taps = ksize;
-    p.cblocks = C / 64;
-    rc = zkb_tmap_im2col_nhwc(&tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A_hi, NB, H, W, C, ksize,
-                              pad, 64, 128);
+    p.cblocks = C / kelems;
+    rc = zkb_tmap_im2col_nhwc(&tmA0, dt, elem_bytes, A_hi, NB, H, W, C, ksize, pad, kelems, 128);
     if (rc) return rc;
     tmA1 = tmA0;
     if (A_lo) {
-      rc = zkb_tmap_im2col_nhwc(&tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A_lo, NB, H, W, C,
-                                ksize, pad, 64, 128);
+      rc = zkb_tmap_im2col_nhwc(&tmA1, dt, elem_bytes, A_lo, NB, H, W, C, ksize, pad, kelems, 128);
       if (rc) return rc;
     }
   } else {
-    rc = zkb_tmap_tiled_2d(&tmA0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A_hi, K, M,
-                           static_cast<uint64_t>(K) * 2, 64, 128);
+    rc = zkb_tmap_tiled_2d(&tmA0, dt, elem_bytes, A_hi, K, M, static_cast<uint64_t>(K) * elem_bytes,
+                           kelems, 128);
     if (rc) return rc;
     tmA1 = tmA0;
     if (A_lo) {
-      rc = zkb_tmap_tiled_2d(&tmA1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A_lo, K, M,
-                             static_cast<uint64_t>(K) * 2, 64, 128);
+      rc = zkb_tmap_tiled_2d(&tmA1, dt, elem_bytes, A_lo, K, M, static_cast<uint64_t>(K) * elem_bytes,
+                             kelems, 128);
       if (rc) return rc;
     }
   }
-  rc = zkb_tmap_tiled_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Bmat, K, N,
-                         static_cast<uint64_t>(K) * 2, 64, p.block_n);
+  rc = zkb_tmap_tiled_2d(&tmB, dt, elem_bytes, Bmat, K, N, static_cast<uint64_t>(K) * elem_bytes, kelems,
+                         p.block_n);
   if (rc) return rc;
 
-  const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + sizeof(SharedCtl) + 1024;
+  // output through TMA stores: boxes of 128 bytes x 32 rows
+  CUtensorMap tmOut;
+  if (out_kind == 0)
+    rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, N, M,
+                           static_cast<uint64_t>(ldo) * 4, 32, 32);
+  else
+    rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, N, M,
+                           static_cast<uint64_t>(ldo) * 2, 64, 32);
+  if (rc) return rc;
+
+  // layout: [stages][1 KB: barriers + TMEM slot][8 x 4 KB staging boxes] (+1 KB alignment slack)
+  const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + 1024 + kEpiStagingBytes + 1024;
   ZKB_CUDA(cudaFuncSetAttribute(kgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 227 * 1024));
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = zkb_sm_count();
   const int grid = tiles < sms ? tiles : sms;
-  kgemm_bf16_kernel<<<grid, 192, smem, stream>>>(tmA0, tmA1, tmB, p);
+  kgemm_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
   ZKB_LAUNCH_CHECK("kgemm_bf16_kernel");
   return ZKB_OK;
 }
@@ -516,18 +583,26 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   p.a_im2col = im2col;
   p.taps = im2col ? ksize * ksize : 1;
   p.kw_taps = im2col ? ksize : 1;
+  // A filter row of taps per work item shares one dy tile (3 accumulators of block_n TMEM columns).
+  p.tpi = (im2col && ksize * p.block_n <= 512) ? ksize : 1;
+  p.kpix = 64;
+  // tuning overrides for A/B measurements (scripts/bench_gemm.py); not part of the ABI contract
+  if (const char* e = getenv("ZKB_WGRAD_TPI")) p.tpi = (atoi(e) == ksize && im2col) ? ksize : 1;
+  if (const char* e = getenv("ZKB_WGRAD_KPIX")) p.kpix = atoi(e) == 32 ? 32 : (atoi(e) == 48 ? 48 : 64);
   p.pad = pad;
   p.OH = H;
   p.OW = W;
   p.ci_tiles = Ma / 128;
   p.n_tiles = N / p.block_n;
-  p.stage_bytes = 16384 + p.b_terms * (p.block_n / 64) * 8192;
+  const int box_bytes = p.kpix * 128;
+  p.stage_bytes = p.tpi * 2 * box_bytes + p.b_terms * (p.block_n / 64) * box_bytes;
   p.num_stages = kSmemBudget / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
+  ZKB_REQUIRE(p.num_stages >= 2, "wgemm: stage does not fit in shared memory");
   p.out = out;
   p.ldo = ldo;
-  const long long chunks = (P + 63) / 64;
-  const int out_tiles = p.taps * p.ci_tiles * p.n_tiles;
+  const long long chunks = (P + p.kpix - 1) / p.kpix;
+  const int out_tiles = (p.taps / p.tpi) * p.ci_tiles * p.n_tiles;
   const int sms = zkb_sm_count();
   long long splits = (2ll * sms + out_tiles - 1) / out_tiles;  // ~2 waves of work items
   if (splits > chunks) splits = chunks;
@@ -541,19 +616,19 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
     ZKB_REQUIRE(P == static_cast<long long>(NB) * H * W, "wgemm: P != NB*H*W");
     ZKB_REQUIRE(ksize == 2 * pad + 1, "wgemm: only 'same' windows (ksize == 2*pad+1)");
     rc = zkb_tmap_im2col_nhwc(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, NB, H, W, Ma, ksize,
-                              pad, 64, 64);
+                              pad, 64, p.kpix);
   } else {
     rc = zkb_tmap_tiled_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, Ma, P,
-                           static_cast<uint64_t>(Ma) * 2, 64, 64);
+                           static_cast<uint64_t>(Ma) * 2, 64, p.kpix);
   }
   if (rc) return rc;
   rc = zkb_tmap_tiled_2d(&tmB0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B_hi, N, P,
-                         static_cast<uint64_t>(N) * 2, 64, 64);
+                         static_cast<uint64_t>(N) * 2, 64, p.kpix);
   if (rc) return rc;
   tmB1 = tmB0;
   if (B_lo) {
     rc = zkb_tmap_tiled_2d(&tmB1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B_lo, N, P,
-                           static_cast<uint64_t>(N) * 2, 64, 64);
+                           static_cast<uint64_t>(N) * 2, 64, p.kpix);
     if (rc) return rc;
   }
   const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + sizeof(SharedCtlW) + 1024;
@@ -573,6 +648,20 @@ ZKB_API int zkb_bconv2d_fwd(const void* act_pm1, const void* wq_oc_k, void* y_i1
   return launch_kgemm(act_pm1, nullptr, wq_oc_k, y_i16, 1, Cout,
                       static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
                       Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream));
+}
+
+ZKB_API int zkb_bconv2d_fwd_i8(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H,
+                               int W, int Cin, int Cout, int ksize, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_fwd_i8: ksize must be odd");
+  return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout,
+                      static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
+                      Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1);
+}
+
+ZKB_API int zkb_bdense_fwd_i8(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,
+                              int rows, int K, int N, void* stream) {
+  return launch_kgemm(act_i8, nullptr, wq_n_k_i8, y_i16, 1, ldy, rows, N, K, 0, 0, 0, 0, 0, 0, 0,
+                      static_cast<cudaStream_t>(stream), 1);
 }
 
 ZKB_API int zkb_bdense_fwd(const void* act_pm1, const void* wq_n_k, void* y_i16, long long ldy,

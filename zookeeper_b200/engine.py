@@ -93,7 +93,7 @@ class BinaryNetEngine:
     def __init__(self, layers: Sequence[LayerSpec], input_shape: Tuple[int, int, int], batch_size: int,
                  num_classes: int, learning_rate: float = 5e-3, device: Optional[torch.device] = None,
                  process_group=None, sync_bn: bool = False, beta_1: float = 0.9, beta_2: float = 0.999,
-                 epsilon: float = 1e-7):
+                 epsilon: float = 1e-7, forward_int8: bool = True):
         zn.load()  # fail loudly now if the CUDA library is missing
         if not torch.cuda.is_available():
             raise RuntimeError("BinaryNetEngine needs a CUDA device (B200); there is no CPU fallback")
@@ -107,6 +107,9 @@ class BinaryNetEngine:
         self.dp = DataParallel(process_group)
         self.world = self.dp.world
         self.sync_bn = bool(sync_bn) and self.world > 1
+        # forward binary GEMMs on tcgen05 kind::i8 (int8 +-1 operands, exact int32 accumulation):
+        # half the operand bytes and twice the MMA rate of the bf16 path, bit-identical results
+        self.forward_int8 = bool(forward_int8)
         self.step_count = 0
         self.launches_per_step = 0
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
@@ -183,7 +186,9 @@ class BinaryNetEngine:
                 L.in_hw = (h, w)
                 oh, ow = (h - l.ksize + 1, w - l.ksize + 1) if l.padding == "valid" else (h, w)
                 L.out_hw = (oh, ow)
-                L.y = torch.zeros(B, oh, ow, L.cp, dtype=f32 if i == 0 else i16, device=dev)
+                # the first layer's float map is never stored: its K=9 conv is recomputed inside
+                # the fused BatchNorm kernels (zkb_conv_first_bn_* / _bwd_*)
+                L.y = None if i == 0 else torch.zeros(B, oh, ow, L.cp, dtype=i16, device=dev)
                 if l.pool:
                     ph, pw = oh // 2, ow // 2
                     L.p = torch.zeros(B, ph, pw, L.cp, dtype=i16, device=dev)
@@ -193,12 +198,13 @@ class BinaryNetEngine:
                     h, w = oh, ow
                 L.bn_rows = B * h * w
                 L.s = torch.zeros(B, h, w, L.cp, dtype=bf16, device=dev)
+                L.s8 = torch.zeros(B, h, w, L.cp, dtype=torch.int8, device=dev) if self.forward_int8 else None
                 L.ds = torch.zeros(B, h, w, L.cp, dtype=f32, device=dev)
                 if i == 0:
                     L.wq = torch.zeros(l.ksize * l.ksize * l.cin, l.cout, dtype=f32, device=dev)
-                    L.dy = torch.zeros(B, oh, ow, L.cp, dtype=f32, device=dev)
                 else:
                     L.w_fwd = torch.zeros(l.cout, l.ksize * l.ksize * l.cin, dtype=bf16, device=dev)
+                    L.w_fwd8 = torch.zeros(l.cout, l.ksize * l.ksize * l.cin, dtype=torch.int8, device=dev) if self.forward_int8 else None
                     L.w_dgrad = torch.zeros(l.cin, l.ksize * l.ksize * l.cout, dtype=bf16, device=dev)
                     L.dy_hi = torch.zeros(B, oh, ow, L.cp, dtype=bf16, device=dev)
                     L.dy_lo = torch.zeros(B, oh, ow, L.cp, dtype=bf16, device=dev)
@@ -211,8 +217,10 @@ class BinaryNetEngine:
                     L.ds = torch.zeros(B, L.cp, dtype=f32, device=dev)  # dlogits
                 else:
                     L.s = torch.zeros(B, L.cp, dtype=bf16, device=dev)
+                    L.s8 = torch.zeros(B, L.cp, dtype=torch.int8, device=dev) if self.forward_int8 else None
                     L.ds = torch.zeros(B, L.cp, dtype=f32, device=dev)
                 L.w_fwd = torch.zeros(L.cp, l.cin, dtype=bf16, device=dev)
+                L.w_fwd8 = torch.zeros(L.cp, l.cin, dtype=torch.int8, device=dev) if self.forward_int8 else None
                 L.w_dgrad = torch.zeros(l.cin, L.cp, dtype=bf16, device=dev)
                 L.dy_hi = torch.zeros(B, L.cp, dtype=bf16, device=dev)
                 L.dy_lo = torch.zeros(B, L.cp, dtype=bf16, device=dev)
@@ -346,7 +354,8 @@ class BinaryNetEngine:
             mean, rstd = L.mm, L.eval_rstd
         last = L.idx == len(self.L) - 1
         self._call("zkb_bn_apply_sign", zn.ptr(x), int(is_i16), rows, cp, zn.ptr(mean), zn.ptr(rstd), zn.ptr(L.beta),
-                   0 if last else zn.ptr(L.s), zn.ptr(L.logits) if last else 0)
+                   0 if last else zn.ptr(L.s), zn.ptr(L.logits) if last else 0,
+                   0 if last else zn.ptr(getattr(L, "s8", None)))
 
     def _pending_bn_sync(self, L):
         # sum and sumsq of one layer are not adjacent in the accumulator arena: two small collectives
@@ -363,12 +372,13 @@ class BinaryNetEngine:
             if l.kind == "conv":
                 oh, ow = L.out_hw
                 if L.idx == 0:
-                    H, W, C = self.input_shape
-                    self._call("zkb_conv_first_fwd", zn.ptr(self.x0), zn.ptr(L.wq), zn.ptr(L.y), B, H, W, C, l.cout, l.ksize)
-                    self._bn_forward(L, L.y, False, B * oh * ow, False, training)
+                    self._first_layer_forward(L, training)
                 else:
                     ih, iw = L.in_hw
-                    self._call("zkb_bconv2d_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), B, ih, iw, l.cin, l.cout, l.ksize)
+                    if self.forward_int8:
+                        self._call("zkb_bconv2d_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), B, ih, iw, l.cin, l.cout, l.ksize)
+                    else:
+                        self._call("zkb_bconv2d_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), B, ih, iw, l.cin, l.cout, l.ksize)
                     if l.pool:
                         self._call("zkb_maxpool2_i16", zn.ptr(L.y), B, oh, ow, L.cp, zn.ptr(L.p), zn.ptr(L.arg),
                                    zn.ptr(L.sum), zn.ptr(L.sumsq))
@@ -376,9 +386,46 @@ class BinaryNetEngine:
                     else:
                         self._bn_forward(L, L.y, True, L.bn_rows, False, training)
             else:
-                self._call("zkb_bdense_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
+                if self.forward_int8:
+                    self._call("zkb_bdense_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
+                else:
+                    self._call("zkb_bdense_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
                 self._bn_forward(L, L.y, True, B, False, training)
             prev = L
+
+    def _first_layer_forward(self, L, training: bool):
+        l = L.spec
+        H, W, C = self.input_shape
+        geom = (self.B, H, W, C, l.cout, l.ksize)
+        if training:
+            self._call("zkb_conv_first_bn_stats", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(L.sum), zn.ptr(L.sumsq))
+            count = float(L.bn_rows)
+            if self.sync_bn:
+                self._pending_bn_sync(L)
+                count *= self.world
+            self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, 1, L.cp,
+                       zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
+            mean, rstd = L.mean, L.rstd
+        else:
+            mean, rstd = L.mm, L.eval_rstd
+        self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
+                   zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
+
+    def _first_layer_backward(self, L):
+        l = L.spec
+        H, W, C = self.input_shape
+        geom = (self.B, H, W, C, l.cout, l.ksize)
+        self._call("zkb_conv_first_bwd_reduce", zn.ptr(self.x0), zn.ptr(L.wq), zn.ptr(L.ds), *geom, zn.ptr(L.mean),
+                   zn.ptr(L.rstd), zn.ptr(L.beta), zn.ptr(L.sum_da), zn.ptr(L.sum_dax))
+        count = float(L.bn_rows)
+        if self.sync_bn:
+            self._all_reduce(L.sum_da)
+            self._all_reduce(L.sum_dax)
+            count *= self.world
+        self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, L.cp, zn.ptr(L.dbeta),
+                   zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
+        self._call("zkb_conv_first_bwd_wgrad", zn.ptr(self.x0), zn.ptr(L.wq), zn.ptr(L.ds), *geom, zn.ptr(L.mean),
+                   zn.ptr(L.rstd), zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), zn.ptr(L.dkernel))
 
     def prepare_weights(self):
         for L in self.L:
@@ -386,9 +433,11 @@ class BinaryNetEngine:
             if L.idx == 0:
                 self._call("zkb_sign_f32", zn.ptr(L.kernel), zn.ptr(L.wq), L.kernel.numel())
             elif l.kind == "conv":
-                self._call("zkb_prep_conv_weights", zn.ptr(L.kernel), l.ksize, l.cin, l.cout, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad))
+                self._call("zkb_prep_conv_weights", zn.ptr(L.kernel), l.ksize, l.cin, l.cout, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad),
+                           zn.ptr(L.w_fwd8))
             else:
-                self._call("zkb_prep_dense_weights", zn.ptr(L.kernel), l.cin, l.cout, L.cp, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad))
+                self._call("zkb_prep_dense_weights", zn.ptr(L.kernel), l.cin, l.cout, L.cp, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad),
+                           zn.ptr(L.w_fwd8))
 
     def backward(self):
         B = self.B
@@ -396,9 +445,12 @@ class BinaryNetEngine:
         for i in range(n - 1, -1, -1):
             L, l = self.L[i], self.L[i].spec
             self._tag = f"bwd{i}"
+            if i == 0:
+                self._first_layer_backward(L)
+                continue
             last = i == n - 1
             x = L.p if (l.kind == "conv" and l.pool) else L.y
-            is_i16 = int(i != 0)
+            is_i16 = 1
             rows = L.bn_rows
             ste = 0 if last else 1
             self._call("zkb_bn_bwd_reduce", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
@@ -410,19 +462,13 @@ class BinaryNetEngine:
                 count *= self.world
             self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, L.cp, zn.ptr(L.dbeta),
                        zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
-            if i == 0:
-                mode, of32, ohi, olo, arg, H, W = 0, zn.ptr(L.dy), 0, 0, 0, 0, 0
-            elif l.kind == "conv" and l.pool:
+            if l.kind == "conv" and l.pool:
                 mode, of32, ohi, olo, arg = 2, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.arg)
                 H, W = L.out_hw
             else:
                 mode, of32, ohi, olo, arg, H, W = 1, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), 0, 0, 0
             self._call("zkb_bn_bwd_apply", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
                        zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), ste, mode, of32, ohi, olo, arg, H, W)
-            if i == 0:
-                H0, W0, C0 = self.input_shape
-                self._call("zkb_conv_first_wgrad", zn.ptr(self.x0), zn.ptr(L.dy), zn.ptr(L.dkernel), B, H0, W0, C0, l.cout, l.ksize)
-                continue
             prev = self.L[i - 1]
             if l.kind == "conv":
                 ih, iw = L.in_hw

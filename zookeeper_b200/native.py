@@ -36,22 +36,28 @@ SIGNATURES = {
     "zkb_bgemm_popc": [P, P, P, L, I, I, I, P],
     "zkb_conv_first_fwd": [P, P, P, I, I, I, I, I, I, P],
     "zkb_conv_first_wgrad": [P, P, P, I, I, I, I, I, I, P],
+    "zkb_conv_first_bn_stats": [P, P, I, I, I, I, I, I, P, P, P],
+    "zkb_conv_first_bn_sign": [P, P, I, I, I, I, I, I, P, P, P, P, P, P],
+    "zkb_conv_first_bwd_reduce": [P, P, P, I, I, I, I, I, I, P, P, P, P, P, P],
+    "zkb_conv_first_bwd_wgrad": [P, P, P, I, I, I, I, I, I, P, P, P, P, P, P, P],
     "zkb_bconv2d_fwd": [P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_fwd": [P, P, P, L, I, I, I, P],
+    "zkb_bconv2d_fwd_i8": [P, P, P, I, I, I, I, I, I, P],
+    "zkb_bdense_fwd_i8": [P, P, P, L, I, I, I, P],
     "zkb_bconv2d_dgrad": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_dgrad": [P, P, P, P, I, I, I, P],
     "zkb_bconv2d_wgrad": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_wgrad": [P, P, P, P, L, I, I, I, I, P],
     "zkb_bn_stats": [P, I, L, I, P, P, P],
     "zkb_bn_finalize": [P, P, D, F, F, I, I, P, P, P, P, P],
-    "zkb_bn_apply_sign": [P, I, L, I, P, P, P, P, P, P],
+    "zkb_bn_apply_sign": [P, I, L, I, P, P, P, P, P, P, P],
     "zkb_maxpool2_i16": [P, I, I, I, I, P, P, P, P, P],
     "zkb_softmax_ce": [P, I, P, I, I, F, P, P, P, P],
     "zkb_bn_bwd_reduce": [P, P, I, L, I, P, P, P, I, P, P, P],
     "zkb_bn_bwd_finalize": [P, P, D, I, P, P, P, P],
     "zkb_bn_bwd_apply": [P, P, I, L, I, P, P, P, P, P, I, I, P, P, P, P, I, I, P],
-    "zkb_prep_conv_weights": [P, I, I, I, P, P, P],
-    "zkb_prep_dense_weights": [P, I, I, I, P, P, P],
+    "zkb_prep_conv_weights": [P, I, I, I, P, P, P, P],
+    "zkb_prep_dense_weights": [P, I, I, I, P, P, P, P],
     "zkb_sign_f32": [P, P, L, P],
     "zkb_adam_clip": [P, P, P, P, L, F, F, F, F, F, I, P],
     "zkb_bn_train_sign_static": [P, I, L, I, P, F, F, I, P, P, P, P, P],
