@@ -1,0 +1,39 @@
+"""2-GPU check: SyncBN data-parallel step at global batch 2B == single-GPU step at batch 2B."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, ".")
+from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers  # noqa: E402
+
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+Bg = 64
+rng = np.random.default_rng(0)
+img = torch.as_tensor(rng.integers(0, 256, (Bg, 28, 28, 1), dtype=np.uint8)).cuda()
+lab = torch.as_tensor(rng.integers(0, 10, (Bg,)).astype(np.int64)).cuda()
+aug = torch.as_tensor(rng.integers(0, 2, (Bg, 3)).astype(np.int8)).cuda()
+
+eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), Bg // world, 10, sync_bn=True)
+eng.init_glorot(0)
+sl = slice(rank, Bg, world)
+eng.train_step(img[sl].contiguous(), lab[sl].contiguous(), None, pad_size=32, aug=aug[sl].contiguous(), apply_update=False)
+torch.cuda.synchronize()
+g_dp = eng.grads.clone()
+loss_dp = torch.tensor([eng.last_loss()], device="cuda", dtype=torch.float64)
+dist.all_reduce(loss_dp)
+if rank == 0:
+    single = BinaryNetEngine(binarynet_layers(), (28, 28, 1), Bg, 10, data_parallel=False)
+    single.init_glorot(0)
+    single.train_step(img, lab, None, pad_size=32, aug=aug, apply_update=False)
+    torch.cuda.synchronize()
+    rel = ((g_dp - single.grads).norm() / single.grads.norm()).item()
+    print(f"DP(2, SyncBN) vs single GPU at global batch {Bg}: grad rel err {rel:.3e}, "
+          f"loss {loss_dp.item() / world:.6f} vs {single.last_loss():.6f}")
+    assert rel < 1e-4
+dist.barrier()
+dist.destroy_process_group()

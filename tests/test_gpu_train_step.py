@@ -154,3 +154,25 @@ def test_eval_step_matches_oracle(native_lib):
     torch.cuda.synchronize()
     assert np.array_equal(eng.x0.cpu().numpy(), x)
     assert _rel(eng.logits(), ref) < 1e-4
+
+
+def test_cifar_shaped_config_matches_oracle(native_lib):
+    """BASELINE.json configs[2]: the same BinaryNet factory on 32x32x3 inputs (first conv K = 27,
+    odd 15x15 -> 7x7 pooling drops the trailing row/column, flatten 3*3*512)."""
+    B, shape = 6, (32, 32, 3)
+    O, layers_o, params, img, lab, eng = _setup(B, seed=21, input_shape=shape)
+    aug = O.augmentation_params(5, 0, B, 40, 32, 32)
+    x = O.preprocess(img, (32, 32), True, 40, aug)
+    ref = O.forward_backward(params, layers_o, x, lab, torch.float64, keep_acts=True)
+    eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda(), None, pad_size=40,
+                   aug=torch.as_tensor(aug).cuda(), apply_update=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(eng.x0.cpu().numpy(), x)
+    for i in range(1, 9):
+        L = eng.L[i]
+        y = L.y.cpu().numpy().astype(np.int64)[..., : L.spec.cout]
+        assert np.array_equal(y, np.rint(ref.acts[f"y{i}"]).astype(np.int64)), f"layer {i}"
+    assert abs(eng.last_loss() - ref.loss) <= REL_TOL * abs(ref.loss)
+    g = eng.get_grads()
+    for k, v in ref.grads.items():
+        assert _rel(g[k], v) < REL_TOL, f"grad {k}: rel {_rel(g[k], v):.3g}"

@@ -535,6 +535,7 @@ bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long 
       f0[j] = f1[j] = 0.f;
     }
     int n = 0;
+#pragma unroll 4
     for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
          r += static_cast<long long>(gridDim.x) * lanes) {
       const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
@@ -844,7 +845,7 @@ ZKB_API int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, dou
   ZKB_REQUIRE(sum && sumsq, "bn_stats: null accumulator");
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / vec);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 4);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 8);
   const size_t smem = 2 * 256 * vec * sizeof(double);
   if (x_is_i16)
     bn_stats_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
@@ -900,7 +901,7 @@ ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_
   if (B == 0) return ZKB_OK;
   const long long rows = static_cast<long long>(B) * (H / 2) * (W / 2);
   const int lanes = 256 / (C / 8);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, 4);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, 8);
   const size_t smem = 2 * 256 * 8 * sizeof(double);
   maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);
@@ -928,7 +929,7 @@ ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long 
   ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax, "bn_bwd_reduce: null pointer");
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / 4);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 4);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 8);
   const size_t smem = 2 * 256 * 4 * sizeof(double);
   if (x_is_i16)
     bn_bwd_reduce_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
@@ -1095,7 +1096,7 @@ ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows
   ZKB_CUDA(cudaMemsetAsync(sc->sum, 0, sizeof(double) * C, st));
   ZKB_CUDA(cudaMemsetAsync(sc->sumsq, 0, sizeof(double) * C, st));
   const int lanes = 256 / (C / vec);
-  const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 4);
+  const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 8);
   const size_t smem = 2 * 256 * vec * sizeof(double);
   const int grid_a = grid_for(rows * (C / vec), 256, 16);
   if (x_is_i16) {
@@ -1141,16 +1142,80 @@ namespace zkb {
 template <int KS, int CIN>
 struct FirstConv {
   static constexpr int K = KS * KS * CIN;
+  // For K <= 9 each thread keeps its 4 channels of sign(W) in registers (36 floats); reading them
+  // from shared memory instead costs 9 x 512 B of smem bandwidth per pixel and was the bottleneck.
+  static constexpr bool kRegW = K <= 9;
+  static constexpr int KR = kRegW ? K : 1;
+  __device__ static __forceinline__ void load_w(const float* __restrict__ wq, int Cout, int c4,
+                                                float4 (&wr)[KR]) {
+    if constexpr (kRegW) {
+#pragma unroll
+      for (int k = 0; k < K; ++k) wr[k] = *reinterpret_cast<const float4*>(wq + k * Cout + c4);
+    } else {
+      wr[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  // Sliding KSxKS window along one output row: per pixel only the KS*CIN new taps are loaded and
+  // the index arithmetic is done once per row instead of once per pixel.
+  struct Row {
+    float win[KS][KS * CIN];
+    const float* base;
+    int W;
+    __device__ __forceinline__ void begin(const float* __restrict__ x, unsigned row, int H, int W_) {
+      const unsigned OH = H - KS + 1;
+      const unsigned b = row / OH;
+      const unsigned oh = row - b * OH;
+      W = W_;
+      base = x + static_cast<size_t>(b * H + oh) * W * CIN;
+#pragma unroll
+      for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+        for (int j = 0; j < (KS - 1) * CIN; ++j) win[kh][j] = __ldg(base + kh * W * CIN + j);
+    }
+    // taps of output pixel `ow` of this row into xv (then slide by one pixel)
+    __device__ __forceinline__ void step(int ow, float (&xv)[K]) {
+#pragma unroll
+      for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+        for (int ci = 0; ci < CIN; ++ci)
+          win[kh][(KS - 1) * CIN + ci] = __ldg(base + (kh * W + ow + KS - 1) * CIN + ci);
+#pragma unroll
+      for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+        for (int j = 0; j < KS * CIN; ++j) xv[kh * KS * CIN + j] = win[kh][j];
+#pragma unroll
+      for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+        for (int j = 0; j < (KS - 1) * CIN; ++j) win[kh][j] = win[kh][j + CIN];
+    }
+  };
+  __device__ static __forceinline__ void dot(const float (&xv)[K], const float* s_w,
+                                             const float4 (&wr)[KR], int Cout, int c4, float (&y)[4]) {
+    y[0] = y[1] = y[2] = y[3] = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      float4 w;
+      if constexpr (kRegW) w = wr[k];
+      else w = *reinterpret_cast<const float4*>(s_w + k * Cout + c4);
+      y[0] = fmaf(xv[k], w.x, y[0]);
+      y[1] = fmaf(xv[k], w.y, y[1]);
+      y[2] = fmaf(xv[k], w.z, y[2]);
+      y[3] = fmaf(xv[k], w.w, y[3]);
+    }
+  }
   // y[4] for channels c4..c4+3 of pixel pix; xv receives the K input taps.
-  __device__ static __forceinline__ void at(const float* __restrict__ x, const float* s_w, int Cout,
-                                            long long pix, int H, int W, int c4, float (&xv)[K],
-                                            float (&y)[4]) {
-    const int OH = H - KS + 1, OW = W - KS + 1;
-    const int ow = static_cast<int>(pix % OW);
-    const long long t = pix / OW;
-    const int oh = static_cast<int>(t % OH);
-    const long long b = t / OH;
-    const float* base = x + ((b * H + oh) * W + ow) * CIN;
+  __device__ static __forceinline__ void at(const float* __restrict__ x, const float* s_w,
+                                            const float4 (&wr)[KR], int Cout, long long pix, int H,
+                                            int W, int c4, float (&xv)[K], float (&y)[4]) {
+    // 32-bit index arithmetic (the host checks B*OH*OW < 2^31): 64-bit div/mod cost more than
+    // the 9-tap convolution itself
+    const unsigned OH = H - KS + 1, OW = W - KS + 1;
+    const unsigned upix = static_cast<unsigned>(pix);
+    const unsigned t = upix / OW;
+    const unsigned ow = upix - t * OW;
+    const unsigned b = t / OH;
+    const unsigned oh = t - b * OH;
+    const float* base = x + (static_cast<size_t>(b * H + oh) * W + ow) * CIN;
 #pragma unroll
     for (int kh = 0; kh < KS; ++kh)
 #pragma unroll
@@ -1161,7 +1226,9 @@ struct FirstConv {
     y[0] = y[1] = y[2] = y[3] = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      const float4 w = *reinterpret_cast<const float4*>(s_w + k * Cout + c4);
+      float4 w;
+      if constexpr (kRegW) w = wr[k];
+      else w = *reinterpret_cast<const float4*>(s_w + k * Cout + c4);
       y[0] = fmaf(xv[k], w.x, y[0]);
       y[1] = fmaf(xv[k], w.y, y[1]);
       y[2] = fmaf(xv[k], w.z, y[2]);
@@ -1186,14 +1253,22 @@ conv_first_bn_stats_kernel(const float* __restrict__ x, const float* __restrict_
   __syncthreads();
   const int tpr = Cout / 4, lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  float4 wr[FC::KR];
+  FC::load_w(wq, Cout, cl * 4, wr);
   const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
   double a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
   float f0[4] = {0, 0, 0, 0}, f1[4] = {0, 0, 0, 0};
   int n = 0;
-  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
-       pix += static_cast<long long>(gridDim.x) * lanes) {
+  const unsigned OWr = W - KS + 1;
+  const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
+  for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   typename FC::Row walk;
+   walk.begin(x, row, H, W);
+   for (unsigned owi = 0; owi < OWr; ++owi) {
+    const long long pix = static_cast<long long>(row) * OWr + owi;
     float xv[FC::K], y[4];
-    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+    walk.step(owi, xv);
+    FC::dot(xv, s_w, wr, Cout, cl * 4, y);
 #pragma unroll
     for (int j = 0; j < 4; ++j) { f0[j] += y[j]; f1[j] = fmaf(y[j], y[j], f1[j]); }
     if (++n == 32) {
@@ -1201,6 +1276,7 @@ conv_first_bn_stats_kernel(const float* __restrict__ x, const float* __restrict_
       for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
       n = 0;
     }
+   }
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
@@ -1219,14 +1295,22 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
   __syncthreads();
   const int tpr = Cout / 4, lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  float4 wr[FC::KR];
+  FC::load_w(wq, Cout, cl * 4, wr);
   const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
   float mu[4], rs[4], be[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) { mu[j] = mean[cl * 4 + j]; rs[j] = rstd[cl * 4 + j]; be[j] = beta[cl * 4 + j]; }
-  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
-       pix += static_cast<long long>(gridDim.x) * lanes) {
+  const unsigned OWr = W - KS + 1;
+  const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
+  for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   typename FC::Row walk;
+   walk.begin(x, row, H, W);
+   for (unsigned owi = 0; owi < OWr; ++owi) {
+    const long long pix = static_cast<long long>(row) * OWr + owi;
     float xv[FC::K], y[4];
-    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+    walk.step(owi, xv);
+    FC::dot(xv, s_w, wr, Cout, cl * 4, y);
     uint16_t s[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) s[j] = pm1_bf16((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f);
@@ -1238,6 +1322,7 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
       for (int e = 0; e < 4; ++e) w8 |= ((s[e] & 0x8000u) ? 0xFFu : 0x01u) << (8 * e);
       *reinterpret_cast<uint32_t*>(s8_out + pix * Cout + cl * 4) = w8;
     }
+   }
   }
 }
 
@@ -1254,6 +1339,8 @@ conv_first_bwd_reduce_kernel(const float* __restrict__ x, const float* __restric
   __syncthreads();
   const int tpr = Cout / 4, lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  float4 wr[FC::KR];
+  FC::load_w(wq, Cout, cl * 4, wr);
   const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
   float mu[4], rs[4], be[4];
 #pragma unroll
@@ -1261,12 +1348,18 @@ conv_first_bwd_reduce_kernel(const float* __restrict__ x, const float* __restric
   double a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
   float f0[4] = {0, 0, 0, 0}, f1[4] = {0, 0, 0, 0};
   int n = 0;
-  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
-       pix += static_cast<long long>(gridDim.x) * lanes) {
+  const unsigned OWr = W - KS + 1;
+  const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
+  for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   typename FC::Row walk;
+   walk.begin(x, row, H, W);
+   for (unsigned owi = 0; owi < OWr; ++owi) {
+    const long long pix = static_cast<long long>(row) * OWr + owi;
     float gg[4];
     load4(g + pix * Cout + cl * 4, gg);
     float xv[FC::K], y[4];
-    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+    walk.step(owi, xv);
+    FC::dot(xv, s_w, wr, Cout, cl * 4, y);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float xh = (y[j] - mu[j]) * rs[j];
@@ -1279,6 +1372,7 @@ conv_first_bwd_reduce_kernel(const float* __restrict__ x, const float* __restric
       for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
       n = 0;
     }
+   }
   }
 #pragma unroll
   for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
@@ -1298,6 +1392,8 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
   __syncthreads();
   const int tpr = Cout / 4, lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr, rl = threadIdx.x / tpr;
+  float4 wr[FC::KR];
+  FC::load_w(wq, Cout, cl * 4, wr);
   const long long pixels = static_cast<long long>(B) * (H - KS + 1) * (W - KS + 1);
   float mu[4], rs[4], be[4], mda[4], mdx[4];
 #pragma unroll
@@ -1308,12 +1404,18 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
   float acc[FC::K][4];
 #pragma unroll
   for (int k = 0; k < FC::K; ++k) acc[k][0] = acc[k][1] = acc[k][2] = acc[k][3] = 0.f;
-  for (long long pix = static_cast<long long>(blockIdx.x) * lanes + rl; pix < pixels;
-       pix += static_cast<long long>(gridDim.x) * lanes) {
+  const unsigned OWr = W - KS + 1;
+  const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
+  for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   typename FC::Row walk;
+   walk.begin(x, row, H, W);
+   for (unsigned owi = 0; owi < OWr; ++owi) {
+    const long long pix = static_cast<long long>(row) * OWr + owi;
     float gg[4];
     load4(g + pix * Cout + cl * 4, gg);
     float xv[FC::K], y[4], dy[4];
-    FC::at(x, s_w, Cout, pix, H, W, cl * 4, xv, y);
+    walk.step(owi, xv);
+    FC::dot(xv, s_w, wr, Cout, cl * 4, y);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float xh = (y[j] - mu[j]) * rs[j];
@@ -1324,6 +1426,7 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
     for (int k = 0; k < FC::K; ++k)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[k][j] = fmaf(xv[k], dy[j], acc[k][j]);
+   }
   }
   // combine the pixel lanes of the block through shared memory, one tap at a time
   __syncthreads();
@@ -1351,6 +1454,7 @@ static int first_conv_check(const char* who, const void* x, const void* wq, int 
   ZKB_REQUIRE(Cout % 4 == 0 && Cout / 4 <= 256 && 256 % (Cout / 4) == 0,
               "%s: Cout=%d must be a multiple of 4 with Cout/4 dividing 256", who, Cout);
   ZKB_REQUIRE(B >= 0 && H >= ksize && W >= ksize, "%s: bad shape", who);
+  ZKB_REQUIRE(static_cast<long long>(B) * H * W < (1ll << 31), "%s: B*H*W must stay below 2^31", who);
   return ZKB_OK;
 }
 

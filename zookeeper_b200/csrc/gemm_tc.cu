@@ -347,47 +347,50 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
   if (n_chunks > 0) {
     if (warp == 0) {
-      if (lane == 0) {
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int ch = 0; ch < n_chunks; ++ch) {
-          const long long pix0 = (chunk_lo + ch) * p.kpix;
+      // Producer warp.  A stage needs up to 10 TMA loads; lane l owns load l so that they are
+      // issued in parallel (one thread issuing them back to back was a measurable part of the
+      // per-chunk critical path).  Load l: l < nB -> B box (term = l / nb, block = l % nb);
+      // l >= nB -> A box (tap = (l - nB) / 2, half = (l - nB) % 2).
+      const int nB = p.b_terms * nb;
+      const int n_loads = nB + 2 * p.tpi;
+      const bool is_b = lane < nB;
+      const int bt = is_b ? lane / nb : 0, bj = is_b ? lane % nb : 0;
+      const int at = is_b ? 0 : (lane - nB) >> 1, ah = is_b ? 0 : (lane - nB) & 1;
+      const int tap = tap0 + at;
+      const int kh = tap / p.kw_taps;
+      const int kw = tap - kh * p.kw_taps;
+      const uint32_t my_off = is_b ? static_cast<uint32_t>(a_bytes + bt * b_term_bytes + bj * box_bytes)
+                                   : static_cast<uint32_t>(at * a_tile_bytes + ah * box_bytes);
+      const CUtensorMap* my_map = is_b ? (bt == 0 ? &tmB0 : &tmB1) : &tmA;
+      const int my_c = is_b ? tn * p.block_n + bj * 64 : tc * 128 + ah * 64;
+      const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int ch = 0; ch < n_chunks; ++ch) {
+        const unsigned pix0 = static_cast<unsigned>((chunk_lo + ch) * p.kpix);
+        const uint32_t full = smem_u32(&ctl->full[stage]);
+        if (lane == 0) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
-          const uint32_t full = smem_u32(&ctl->full[stage]);
           mbar_expect_tx(full, static_cast<uint32_t>(p.stage_bytes));
-          const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
-          const uint32_t sB = sA + a_bytes;
-          // B first: every tap's MMAs need it
-          for (int j = 0; j < nb; ++j) {
-            tma_load_2d(sB + j * box_bytes, &tmB0, full, tn * p.block_n + j * 64,
-                        static_cast<int>(pix0));
-            if (p.b_terms == 2)
-              tma_load_2d(sB + b_term_bytes + j * box_bytes, &tmB1, full, tn * p.block_n + j * 64,
-                          static_cast<int>(pix0));
-          }
-          if (p.a_im2col) {
-            const int hw = p.OH * p.OW;
-            const int img = static_cast<int>(pix0 / hw);
-            const int rem = static_cast<int>(pix0 - static_cast<long long>(img) * hw);
-            const int oh = rem / p.OW;
-            const int ow = rem - oh * p.OW;
-            for (int t = 0; t < p.tpi; ++t) {
-              const int tap = tap0 + t;
-              const int kh = tap / p.kw_taps;
-              const int kw = tap - kh * p.kw_taps;
-              for (int h = 0; h < 2; ++h)
-                tma_load_im2col_4d(sA + t * a_tile_bytes + h * box_bytes, &tmA, full,
-                                   tc * 128 + h * 64, ow - p.pad, oh - p.pad, img,
-                                   static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
-            }
+        }
+        __syncwarp();
+        if (lane < n_loads) {
+          const uint32_t dst = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes) + my_off;
+          if (is_b || !p.a_im2col) {
+            tma_load_2d(dst, my_map, full, my_c, static_cast<int>(pix0));
           } else {
-            for (int h = 0; h < 2; ++h)
-              tma_load_2d(sA + h * box_bytes, &tmA, full, tc * 128 + h * 64, static_cast<int>(pix0));
+            const unsigned img = pix0 / hw;
+            const unsigned rem = pix0 - img * hw;
+            const unsigned oh = rem / static_cast<unsigned>(p.OW);
+            const unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
+            tma_load_im2col_4d(dst, my_map, full, my_c, static_cast<int>(ow) - p.pad,
+                               static_cast<int>(oh) - p.pad, static_cast<int>(img),
+                               static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
           }
-          if (++stage == p.num_stages) {
-            stage = 0;
-            phase ^= 1u;
-          }
+        }
+        if (++stage == p.num_stages) {
+          stage = 0;
+          phase ^= 1u;
         }
       }
     } else if (warp == 1) {

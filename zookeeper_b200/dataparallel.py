@@ -13,9 +13,9 @@ import torch.distributed as dist
 
 
 class DataParallel:
-    def __init__(self, process_group=None):
+    def __init__(self, process_group=None, enabled: bool = True):
         self.group = process_group
-        active = dist.is_available() and dist.is_initialized()
+        active = enabled and dist.is_available() and dist.is_initialized()
         self.world = dist.get_world_size(process_group) if active else 1
         self.rank = dist.get_rank(process_group) if active else 0
 

@@ -93,7 +93,7 @@ class BinaryNetEngine:
     def __init__(self, layers: Sequence[LayerSpec], input_shape: Tuple[int, int, int], batch_size: int,
                  num_classes: int, learning_rate: float = 5e-3, device: Optional[torch.device] = None,
                  process_group=None, sync_bn: bool = False, beta_1: float = 0.9, beta_2: float = 0.999,
-                 epsilon: float = 1e-7, forward_int8: bool = True):
+                 epsilon: float = 1e-7, forward_int8: bool = True, data_parallel: bool = True):
         zn.load()  # fail loudly now if the CUDA library is missing
         if not torch.cuda.is_available():
             raise RuntimeError("BinaryNetEngine needs a CUDA device (B200); there is no CPU fallback")
@@ -104,7 +104,7 @@ class BinaryNetEngine:
         self.num_classes = int(num_classes)
         self.lr, self.b1, self.b2, self.eps = float(learning_rate), beta_1, beta_2, epsilon
         self.pg = process_group
-        self.dp = DataParallel(process_group)
+        self.dp = DataParallel(process_group, enabled=data_parallel)
         self.world = self.dp.world
         self.sync_bn = bool(sync_bn) and self.world > 1
         # forward binary GEMMs on tcgen05 kind::i8 (int8 +-1 operands, exact int32 accumulation):
