@@ -41,6 +41,9 @@ struct KGemmParams {
   int OH, OW, pad, kw_taps, cblocks;
   int out_kind;  // 0: f32, 1: int16 (exact integers expected)
   int is_i8;     // operands are signed int8 (+-1 / 0), accumulators int32 (kind::i8)
+  int dbg;       // measurement switches (scripts/bench_gemm.py): 1 = no MMA issue, 2 = no TMA loads
+  int swap;      // 1: operand roles swapped -- the MMA computes D^T[128 out channels, 256 pixels]
+                 //    so that narrow (128-column) layers still issue 256-wide MMAs; f32 output only
   void* out;
   long long ldo;
 };
@@ -97,7 +100,68 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (lane == 0 && p.swap) {
+      // stage layout: [W tile 128 x 128 B][X term 0: 256 pixel rows][X term 1: 256 pixel rows]
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int tm = tile / p.tiles_n;
+        const int tn = tile - tm * p.tiles_n;
+        const int m0 = tm * 256;
+        const int c0 = tn * 128;
+        int img[2] = {0, 0}, oh[2] = {0, 0}, ow[2] = {0, 0};
+        int live[2];
+        for (int h = 0; h < 2; ++h) {
+          const int mh = m0 + h * 128;
+          live[h] = mh < p.M;   // a box entirely beyond the last pixel is not loaded (its columns
+                                // of D^T are never stored)
+          if (p.a_im2col && live[h]) {
+            const int hw = p.OH * p.OW;
+            img[h] = mh / hw;
+            const int rem = mh - img[h] * hw;
+            oh[h] = rem / p.OW;
+            ow[h] = rem - oh[h] * p.OW;
+          }
+        }
+        const uint32_t tx = static_cast<uint32_t>(kATileBytes + p.a_terms * kATileBytes * (live[0] + live[1]));
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
+          const uint32_t full = smem_u32(&ctl->full[stage]);
+          if (p.dbg & 2) {
+            mbar_arrive(full);
+            if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+            continue;
+          }
+          mbar_expect_tx(full, tx);
+          const uint32_t sW = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
+          const uint32_t sX = sW + kATileBytes;
+          tma_load_2d(sW, &tmB, full, kb * p.kelems, c0);
+          int kh = 0, kw = 0, cb = kb;
+          if (p.a_im2col) {
+            const int tap = kb / p.cblocks;
+            cb = kb - tap * p.cblocks;
+            kh = tap / p.kw_taps;
+            kw = tap - kh * p.kw_taps;
+          }
+          for (int t = 0; t < p.a_terms; ++t) {
+            const CUtensorMap* mp = t == 0 ? &tmA0 : &tmA1;
+            for (int h = 0; h < 2; ++h) {
+              if (!live[h]) continue;
+              const uint32_t dst = sX + static_cast<uint32_t>(t * 2 * kATileBytes + h * kATileBytes);
+              if (p.a_im2col)
+                tma_load_im2col_4d(dst, mp, full, cb * p.kelems, ow[h] - p.pad, oh[h] - p.pad, img[h],
+                                   static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
+              else
+                tma_load_2d(dst, mp, full, kb * p.kelems, m0 + h * 128);
+            }
+          }
+          if (++stage == p.num_stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    } else if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -116,6 +180,11 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
           const uint32_t full = smem_u32(&ctl->full[stage]);
+          if (p.dbg & 2) {
+            mbar_arrive(full);
+            if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+            continue;
+          }
           mbar_expect_tx(full, static_cast<uint32_t>(p.stage_bytes));
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
           const uint32_t sB = sA + static_cast<uint32_t>(p.a_terms) * kATileBytes;
@@ -144,7 +213,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      const uint32_t idesc = p.is_i8 ? umma_idesc_s8(128, p.block_n) : umma_idesc_bf16(128, p.block_n, 0, 0);
+      const uint32_t idesc = p.is_i8 ? umma_idesc_s8(128, p.block_n) : umma_idesc_bf16(128, p.block_n, 0, 0);  // swap: block_n = 256 pixels
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
@@ -161,9 +230,14 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
           for (int t = 0; t < p.a_terms; ++t) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              const uint64_t ad = umma_smem_desc_sw128(sA + t * kATileBytes + k * 32, 16, 1024);
-              const uint64_t bd = umma_smem_desc_sw128(sB + k * 32, 16, 1024);
+              // swap: the weight tile (first 16 KB of the stage) is the M operand, the 256 pixel
+              // rows of term t are the N operand
+              const uint64_t ad = p.swap ? umma_smem_desc_sw128(sA + k * 32, 16, 1024)
+                                         : umma_smem_desc_sw128(sA + t * kATileBytes + k * 32, 16, 1024);
+              const uint64_t bd = p.swap ? umma_smem_desc_sw128(sA + kATileBytes + t * 2 * kATileBytes + k * 32, 16, 1024)
+                                         : umma_smem_desc_sw128(sB + k * 32, 16, 1024);
               // a 128-byte row holds 64 bf16 or 128 int8: either way 4 MMAs of 32 bytes of K
+              if (p.dbg & 1) continue;
               if (p.is_i8)
                 umma_i8(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
               else
@@ -207,6 +281,39 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
       tc_fence_after();
       const uint32_t tbase =
           tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as) * 256u;
+      if (p.swap) {
+        // D^T: TMEM lane = output channel, column = pixel.  A unit is 32 pixels x this warp's 32
+        // channels, transposed through the staging box (row = pixel, 4 bytes per lane).
+        const int ch0 = tn * 128 + q * 32;
+        for (int u = half; u < 8; u += 2) {
+          const int pix0 = tm * 256 + u * 32;
+          if (pix0 >= p.M) break;
+          uint32_t r[32];
+          tmem_ld_32x32(tbase + static_cast<uint32_t>(u * 32), r);
+          tmem_ld_wait();
+          if (lane == 0) tma_store_wait_read_all();
+          __syncwarp();
+          const uint32_t lane_chunk = static_cast<uint32_t>(lane >> 2);
+          const uint32_t lane_byte = static_cast<uint32_t>(lane & 3) * 4u;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const uint32_t addr = stage_box + static_cast<uint32_t>(j) * 128u +
+                                  ((lane_chunk ^ static_cast<uint32_t>(j & 7)) << 4) + lane_byte;
+            asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(r[j]) : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmOut, stage_box, ch0, pix0);
+            tma_store_commit();
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(smem_u32(&ctl->tempty[as]));
+        as ^= 1;
+        if (as == 0) aphase ^= 1u;
+        continue;
+      }
       for (int u = half; u < units; u += 2) {
         const int c0 = u * unit_cols;
         uint32_t r[32];
@@ -274,12 +381,16 @@ struct WGemmParams {
   int N;        // columns of the B operand (multiple of 64)
   int n_valid;  // columns of D actually written (<= N)
   long long P;  // reduction length (pixels / batch rows)
-  int b_terms;  // 1 or 2
-  int block_n;  // 64 or 128
+  int b_terms;  // 1 or 2 (dy = hi + lo)
+  int block_n;  // N of one MMA: 64, 128 or 256
+  int concat;   // 1: the MMA's 256 columns are [hi(128) | lo(128)] of a 128-wide layer; the two
+                //    halves of the accumulator are added in the epilogue
+  int cols_per_tile;  // output columns one work item covers (128 when concat, else block_n)
   int a_im2col;
   int OH, OW, pad, kw_taps, taps;
-  int tpi;      // taps per work item (a filter row for convs, 1 otherwise): they share the B tile
-  int kpix;     // reduction rows per pipeline stage (32 or 64)
+  int tpi;      // taps per work item: they share the B (dy) tile, one TMEM accumulator each
+  int kpix;     // reduction rows per pipeline stage (32, 48 or 64)
+  int dbg;      // measurement switches (scripts/bench_gemm.py): 1 = no MMA issue, 2 = no TMA loads
   int ci_tiles, n_tiles, splits;
   int chunks_per_split;  // kpix-row chunks of P
   int num_stages, stage_bytes;
@@ -295,6 +406,10 @@ struct SharedCtlW {
   uint32_t pad_;
 };
 
+// 256-column MMAs run the tensor pipe ~1.7x more efficiently than 128-column ones (operand
+// fetch from shared memory is amortised over twice the columns), so a work item always issues
+// N = 256 where the layer allows: 256 output channels at once, or, for 128-wide layers, the hi
+// and lo halves of dy side by side.
 __global__ void __launch_bounds__(192, 1)
 wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB0,
                   const __grid_constant__ CUtensorMap tmB1, const WGemmParams p) {
@@ -305,15 +420,16 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  // work item -> (split, tap group, ci_tile, n_tile); n fastest so that neighbours share the A stream.
+  // work item -> (split, tap group, ci_tile, n_tile)
   int wi = blockIdx.x;
   const int tn = wi % p.n_tiles;
   wi /= p.n_tiles;
   const int tc = wi % p.ci_tiles;
   wi /= p.ci_tiles;
-  const int groups = p.taps / p.tpi;
+  const int groups = (p.taps + p.tpi - 1) / p.tpi;
   const int tap0 = (wi % groups) * p.tpi;
   const int split = wi / groups;
+  const int tcount = (p.taps - tap0) < p.tpi ? (p.taps - tap0) : p.tpi;  // taps of this item
 
   const long long total_chunks = (p.P + p.kpix - 1) / p.kpix;
   const long long chunk_lo = static_cast<long long>(split) * p.chunks_per_split;
@@ -339,30 +455,30 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = ctl->tmem_base;
-  const int nb = p.block_n / 64;            // 64-channel boxes of B per term
   const int box_bytes = p.kpix * 128;       // one [64 channels x kpix rows] box
   const int a_tile_bytes = 2 * box_bytes;   // 128 channels of A
-  const int b_term_bytes = nb * box_bytes;
   const int a_bytes = p.tpi * a_tile_bytes;
+  const int boxes_per_term = p.concat ? 2 : p.block_n / 64;
+  const int nB = p.b_terms * boxes_per_term;          // B boxes per stage
+  const int b_term_bytes = boxes_per_term * box_bytes;
+  const int mma_terms = p.concat ? 1 : p.b_terms;      // concat: hi and lo ride in one MMA
 
   if (n_chunks > 0) {
     if (warp == 0) {
-      // Producer warp.  A stage needs up to 10 TMA loads; lane l owns load l so that they are
-      // issued in parallel (one thread issuing them back to back was a measurable part of the
-      // per-chunk critical path).  Load l: l < nB -> B box (term = l / nb, block = l % nb);
-      // l >= nB -> A box (tap = (l - nB) / 2, half = (l - nB) % 2).
-      const int nB = p.b_terms * nb;
-      const int n_loads = nB + 2 * p.tpi;
+      // Producer warp: lane l owns TMA load l of a stage so that they are issued in parallel.
+      // l < nB -> B box (term = l / boxes_per_term); l >= nB -> A box (tap = (l-nB)/2, half = (l-nB)%2).
+      const int n_loads = nB + 2 * tcount;
+      const uint32_t tx_bytes = static_cast<uint32_t>(n_loads * box_bytes);
       const bool is_b = lane < nB;
-      const int bt = is_b ? lane / nb : 0, bj = is_b ? lane % nb : 0;
+      const int bt = is_b ? lane / boxes_per_term : 0, bj = is_b ? lane % boxes_per_term : 0;
       const int at = is_b ? 0 : (lane - nB) >> 1, ah = is_b ? 0 : (lane - nB) & 1;
       const int tap = tap0 + at;
       const int kh = tap / p.kw_taps;
       const int kw = tap - kh * p.kw_taps;
-      const uint32_t my_off = is_b ? static_cast<uint32_t>(a_bytes + bt * b_term_bytes + bj * box_bytes)
+      const uint32_t my_off = is_b ? static_cast<uint32_t>(a_bytes + (bt * boxes_per_term + bj) * box_bytes)
                                    : static_cast<uint32_t>(at * a_tile_bytes + ah * box_bytes);
       const CUtensorMap* my_map = is_b ? (bt == 0 ? &tmB0 : &tmB1) : &tmA;
-      const int my_c = is_b ? tn * p.block_n + bj * 64 : tc * 128 + ah * 64;
+      const int my_c = is_b ? tn * p.cols_per_tile + bj * 64 : tc * 128 + ah * 64;
       const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
       int stage = 0;
       uint32_t phase = 0;
@@ -371,10 +487,11 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const uint32_t full = smem_u32(&ctl->full[stage]);
         if (lane == 0) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
-          mbar_expect_tx(full, static_cast<uint32_t>(p.stage_bytes));
+          if (p.dbg & 2) mbar_arrive(full);
+          else mbar_expect_tx(full, tx_bytes);
         }
         __syncwarp();
-        if (lane < n_loads) {
+        if (lane < n_loads && !(p.dbg & 2)) {
           const uint32_t dst = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes) + my_off;
           if (is_b || !p.a_im2col) {
             tma_load_2d(dst, my_map, full, my_c, static_cast<int>(pix0));
@@ -404,17 +521,17 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
           const uint32_t sB = sA + a_bytes;
-          for (int t = 0; t < p.tpi; ++t) {
+          for (int t = 0; t < tcount; ++t) {
             const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(t * p.block_n);
-            for (int bt = 0; bt < p.b_terms; ++bt) {
+            for (int bt = 0; bt < mma_terms; ++bt) {
               for (int k = 0; k < ksteps; ++k) {
-                // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each); the next 64-wide
-                // channel block of an operand starts box_bytes further on.
+                // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each); successive 64-wide
+                // channel blocks of an operand are box_bytes apart.
                 const uint64_t ad = umma_smem_desc_sw128(sA + t * a_tile_bytes + k * 2048,
                                                          box_bytes, 1024);
                 const uint64_t bd = umma_smem_desc_sw128(sB + bt * b_term_bytes + k * 2048,
                                                          box_bytes, 1024);
-                umma_f16(d_tmem, ad, bd, idesc, (ch | bt | k) != 0 ? 1u : 0u);
+                if (!(p.dbg & 1)) umma_f16(d_tmem, ad, bd, idesc, (ch | bt | k) != 0 ? 1u : 0u);
               }
             }
           }
@@ -431,15 +548,23 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_wait(smem_u32(&ctl->tfull), 0);
       tc_fence_after();
       const int row_in_tap = tc * 128 + q * 32 + lane;  // channel of A
-      for (int t = 0; t < p.tpi; ++t) {
+      for (int t = 0; t < tcount; ++t) {
         const long long orow = static_cast<long long>(tap0 + t) * p.Ma + row_in_tap;
         const uint32_t tbase =
             tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * p.block_n);
-        for (int c = 0; c < p.block_n / 32; ++c) {
+        for (int c = 0; c < p.cols_per_tile / 32; ++c) {
           uint32_t r[32];
           tmem_ld_32x32(tbase + static_cast<uint32_t>(c * 32), r);
           tmem_ld_wait();
-          const int col0 = tn * p.block_n + c * 32;
+          if (p.concat) {   // add the lo half of the accumulator
+            uint32_t r2[32];
+            tmem_ld_32x32(tbase + static_cast<uint32_t>(128 + c * 32), r2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+          }
+          const int col0 = tn * p.cols_per_tile + c * 32;
           if (row_in_tap < p.Ma) {
             float* o = p.out + orow * p.ldo + col0;
 #pragma unroll
@@ -496,15 +621,28 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   p.N = N;
   p.num_kb = K / kelems;
   p.kelems = kelems;
+  if (const char* e = getenv("ZKB_GEMM_DBG")) p.dbg = atoi(e);
   p.is_i8 = elem_bytes == 1;
   p.a_terms = A_lo ? 2 : 1;
   p.block_n = pick_block_n(N);
   p.stage_bytes = p.a_terms * kATileBytes + p.block_n * 128;
+  // narrow f32-output layers (dgrad into 128 input channels): swap operand roles so that the
+  // MMAs are 256 wide (see KGemmParams::swap)
+  p.swap = (out_kind == 0 && elem_bytes == 2 && N % 128 == 0 && N < 256) ? 1 : 0;
+  if (const char* e = getenv("ZKB_KGEMM_SWAP")) p.swap = (atoi(e) && out_kind == 0 && elem_bytes == 2 && N % 128 == 0) ? 1 : 0;
+  if (p.swap) {
+    p.block_n = 256;
+    p.stage_bytes = kATileBytes + p.a_terms * 2 * kATileBytes;
+  }
   p.num_stages = (kSmemBudget - kEpiStagingBytes) / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
   ZKB_REQUIRE(p.num_stages >= 2, "kgemm: tile does not fit in shared memory");
   p.tiles_m = static_cast<int>((M + 127) / 128);
   p.tiles_n = (N + p.block_n - 1) / p.block_n;
+  if (p.swap) {
+    p.tiles_m = static_cast<int>((M + 255) / 256);
+    p.tiles_n = N / 128;
+  }
   p.a_im2col = im2col;
   p.out_kind = out_kind;
   p.out = out;
@@ -540,7 +678,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     }
   }
   rc = zkb_tmap_tiled_2d(&tmB, dt, elem_bytes, Bmat, K, N, static_cast<uint64_t>(K) * elem_bytes, kelems,
-                         p.block_n);
+                         p.swap ? 128 : p.block_n);
   if (rc) return rc;
 
   // output through TMA stores: boxes of 128 bytes x 32 rows
@@ -582,30 +720,49 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   p.n_valid = n_valid;
   p.P = P;
   p.b_terms = B_lo ? 2 : 1;
-  p.block_n = (N % 128 == 0) ? 128 : 64;
   p.a_im2col = im2col;
   p.taps = im2col ? ksize * ksize : 1;
   p.kw_taps = im2col ? ksize : 1;
-  // A filter row of taps per work item shares one dy tile (3 accumulators of block_n TMEM columns).
-  p.tpi = (im2col && ksize * p.block_n <= 512) ? ksize : 1;
+  // MMA width: 256 columns whenever the layer allows it (see the kernel's comment)
+  if (N % 256 == 0) {
+    p.block_n = 256; p.concat = 0; p.cols_per_tile = 256;
+  } else if (N == 128 && p.b_terms == 2) {
+    p.block_n = 256; p.concat = 1; p.cols_per_tile = 128;
+  } else if (N % 128 == 0) {
+    p.block_n = 128; p.concat = 0; p.cols_per_tile = 128;
+  } else {
+    p.block_n = 64; p.concat = 0; p.cols_per_tile = 64;
+  }
+  // taps per work item: as many accumulators as fit the 512 TMEM columns, at most a filter row
+  p.tpi = 1;
+  if (im2col) {
+    p.tpi = 512 / p.block_n;
+    if (p.tpi > ksize) p.tpi = ksize;
+  }
   p.kpix = 64;
   // tuning overrides for A/B measurements (scripts/bench_gemm.py); not part of the ABI contract
-  if (const char* e = getenv("ZKB_WGRAD_TPI")) p.tpi = (atoi(e) == ksize && im2col) ? ksize : 1;
+  if (const char* e = getenv("ZKB_GEMM_DBG")) p.dbg = atoi(e);
+  if (const char* e = getenv("ZKB_WGRAD_TPI")) {
+    const int v = atoi(e);
+    if (im2col && v >= 1 && v * p.block_n <= 512) p.tpi = v;
+  }
   if (const char* e = getenv("ZKB_WGRAD_KPIX")) p.kpix = atoi(e) == 32 ? 32 : (atoi(e) == 48 ? 48 : 64);
   p.pad = pad;
   p.OH = H;
   p.OW = W;
   p.ci_tiles = Ma / 128;
-  p.n_tiles = N / p.block_n;
+  p.n_tiles = N / p.cols_per_tile;
   const int box_bytes = p.kpix * 128;
-  p.stage_bytes = p.tpi * 2 * box_bytes + p.b_terms * (p.block_n / 64) * box_bytes;
+  const int boxes_b = p.b_terms * (p.concat ? 2 : p.block_n / 64);
+  p.stage_bytes = (p.tpi * 2 + boxes_b) * box_bytes;
   p.num_stages = kSmemBudget / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
   ZKB_REQUIRE(p.num_stages >= 2, "wgemm: stage does not fit in shared memory");
   p.out = out;
   p.ldo = ldo;
   const long long chunks = (P + p.kpix - 1) / p.kpix;
-  const int out_tiles = (p.taps / p.tpi) * p.ci_tiles * p.n_tiles;
+  const int groups = (p.taps + p.tpi - 1) / p.tpi;
+  const int out_tiles = groups * p.ci_tiles * p.n_tiles;
   const int sms = zkb_sm_count();
   long long splits = (2ll * sms + out_tiles - 1) / out_tiles;  // ~2 waves of work items
   if (splits > chunks) splits = chunks;
