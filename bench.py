@@ -339,6 +339,11 @@ def main():
             ach = work[1] / avg_s / 1e9
             roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                         "traffic": None}
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                roofline["traffic"] = json.load(f).get(f"{dominant[0]}[{dominant[1]}]")
+        except OSError:
+            pass
         roofline.update({"kernel": f"{dominant[0]}[{dominant[1]}]", "avg_launch_ms": statistics.mean(dom_ms),
                          "launches_timed": len(dom_ms),
                          "peak_source": "MEASURED_PEAKS.json (sustained)" if peaks else "fallback",
