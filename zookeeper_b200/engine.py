@@ -112,6 +112,15 @@ class BinaryNetEngine:
         self.forward_int8 = bool(forward_int8)
         self.step_count = 0
         self.launches_per_step = 0
+        # Two engine-owned streams: the dependent chain of a step runs on a high-priority one, the
+        # weight-gradient GEMMs (nothing in the backward chain waits for them) on a low-priority
+        # one, so that the tensor-pipe-bound wgrad of layer i overlaps the HBM-bound BatchNorm
+        # backward of layer i-1.
+        self.overlap = True
+        lo_pri, hi_pri = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
+        self._main = torch.cuda.Stream(device=self.device, priority=hi_pri)
+        self._side = torch.cuda.Stream(device=self.device, priority=lo_pri)
+        self._side_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
@@ -327,20 +336,22 @@ class BinaryNetEngine:
         return out
 
     # ------------------------------------------------------------------ kernels
-    def _call(self, name, *args):
+    def _call(self, name, *args, on=None):
+        """Launch entry point ``name`` on the step's main stream, or on torch stream ``on``."""
         self._n_launch += 1
+        handle = self._stream if on is None else on.cuda_stream
         watch = self.watch
         if watch is not None and (watch is True or name in watch):
             # CUDA events on the launching stream around this one launch (bench.py roofline /
             # per-kernel breakdown); off by default.
             e0 = torch.cuda.Event(enable_timing=True)
             e1 = torch.cuda.Event(enable_timing=True)
-            e0.record()
-            zn.call(name, *args, self._stream)
-            e1.record()
+            e0.record(on) if on is not None else e0.record()
+            zn.call(name, *args, handle)
+            e1.record(on) if on is not None else e1.record()
             self.watched.append((name, self._tag, e0, e1))
             return
-        zn.call(name, *args, self._stream)
+        zn.call(name, *args, handle)
 
     def _begin(self):
         self._stream = torch.cuda.current_stream(self.device).cuda_stream
@@ -465,9 +476,12 @@ class BinaryNetEngine:
                 self._call("zkb_prep_dense_weights", zn.ptr(L.kernel), l.cin, l.cout, L.cp, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad),
                            zn.ptr(L.w_fwd8))
 
-    def backward(self):
+    def backward(self, side=None):
+        """Backward pass.  With ``side`` (a low-priority stream) the wgrad GEMMs are issued there:
+        each waits for its layer's dy and is joined before the gradients are consumed."""
         B = self.B
         n = len(self.L)
+        main = torch.cuda.current_stream(self.device)
         for i in range(n - 1, -1, -1):
             L, l = self.L[i], self.L[i].spec
             self._tag = f"bwd{i}"
@@ -496,17 +510,24 @@ class BinaryNetEngine:
             self._call("zkb_bn_bwd_apply", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
                        zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), ste, mode, of32, ohi, olo, arg, H, W)
             prev = self.L[i - 1]
+            if side is not None:
+                ev = self._side_events[i]
+                ev.record(main)          # dy_i is complete (and the gradient arena was zeroed) here
+                side.wait_event(ev)
             if l.kind == "conv":
                 ih, iw = L.in_hw
-                self._call("zkb_bconv2d_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
-                           B, ih, iw, l.cin, l.cout, l.ksize)
+                # dgrad first: it is on the critical path (the next BatchNorm backward needs it)
                 self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                            B, ih, iw, l.cin, l.cout, l.ksize)
+                self._call("zkb_bconv2d_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
+                           B, ih, iw, l.cin, l.cout, l.ksize, on=side)
             else:
-                self._call("zkb_bdense_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
-                           l.cout, B, l.cin, L.cp, l.cout)
                 self._call("zkb_bdense_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                            B, l.cin, L.cp)
+                self._call("zkb_bdense_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
+                           l.cout, B, l.cin, L.cp, l.cout, on=side)
+        if side is not None:
+            main.wait_stream(side)       # every dW is in the arena before all-reduce / Adam
 
     def loss_and_grad(self):
         L = self.L[-1]
@@ -534,20 +555,28 @@ class BinaryNetEngine:
 
         Everything is enqueued on the current CUDA stream; nothing synchronises with the host.
         Read :meth:`last_loss` / :meth:`last_accuracy` afterwards (that read synchronises)."""
-        self._begin()
-        self.acc.zero_()
-        self.correct.zero_()
-        self.grads.zero_()
-        if not preprocessed:
-            self.preprocess(images_u8, labels_i64, index, True, pad_size, aug, seed, self.step_count)
-        self.prepare_weights()
-        self.forward(training=True)
-        self.loss_and_grad()
-        self.backward()
-        if self.world > 1:
-            self._all_reduce(self.grads)
-        if apply_update:
-            self.optimizer_step()
+        # per-launch timing of everything (watch is True) wants a serial schedule
+        use_side = self.overlap and self.watch is not True
+        caller = torch.cuda.current_stream(self.device)
+        if use_side:
+            self._main.wait_stream(caller)
+        with torch.cuda.stream(self._main if use_side else caller):
+            self._begin()
+            self.acc.zero_()
+            self.correct.zero_()
+            self.grads.zero_()
+            if not preprocessed:
+                self.preprocess(images_u8, labels_i64, index, True, pad_size, aug, seed, self.step_count)
+            self.prepare_weights()
+            self.forward(training=True)
+            self.loss_and_grad()
+            self.backward(self._side if use_side else None)
+            if self.world > 1:
+                self._all_reduce(self.grads)
+            if apply_update:
+                self.optimizer_step()
+        if use_side:
+            caller.wait_stream(self._main)
         self.launches_per_step = self._n_launch
 
     def eval_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, index: Optional[torch.Tensor] = None):
