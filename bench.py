@@ -159,6 +159,9 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 def algorithmic_work(eng, name, tag):
     """('flop'|'byte', amount) for one launch of entry point `name` issued for layer `tag`."""
+    g = global_work(eng, name)
+    if g:
+        return g
     i = int(tag[3:]) if tag[3:].isdigit() else None
     if i is None:
         return None
@@ -188,6 +191,17 @@ def algorithmic_work(eng, name, tag):
     }
     if name in table:
         return ("byte", float(table[name]))
+    return None
+
+
+def global_work(eng, name):
+    """Byte models of the launches that are not tied to one layer."""
+    B = eng.B
+    H, W, C = eng.input_shape
+    if name == "zkb_preprocess_u8":
+        return ("byte", float(B * H * W * C * 5 + B * 8))
+    if name == "zkb_adam_clip":
+        return ("byte", 28.0 * (eng.n_kernel + eng.n_beta) / 2)  # two launches: kernels, betas
     return None
 
 
@@ -258,6 +272,35 @@ def main():
         per.setdefault((name, tag), []).append(e0.elapsed_time(e1))
     eng.watch, eng.watched = None, []
     dominant = max(per, key=lambda k: sum(per[k]))
+    # per entry point: time, share of the (serial) step and achieved rate against its roofline
+    peaks_hbm, peaks_tc = 6447.5, 1401.9
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            _p = json.load(f)
+            peaks_hbm, peaks_tc = _p.get("hbm_gbs", peaks_hbm), _p.get("bf16_tflops_sustained", peaks_tc)
+    except OSError:
+        pass
+    serial_ms = sum(sum(v) for v in per.values())
+    kernels = {}
+    for (name, tag), v in per.items():
+        k = kernels.setdefault(name, {"ms": 0.0, "flop": 0.0, "byte": 0.0, "launches": 0})
+        k["ms"] += sum(v)
+        k["launches"] += len(v)
+        w = algorithmic_work(eng, name, tag)
+        if w:
+            k[w[0]] += w[1] * len(v)
+    kernel_table = {}
+    for name, k in sorted(kernels.items(), key=lambda kv: -kv[1]["ms"]):
+        if k["ms"] / serial_ms < 0.004:
+            continue
+        row = {"ms": round(k["ms"], 4), "share": round(k["ms"] / serial_ms, 4), "launches": k["launches"]}
+        if k["flop"]:
+            row.update({"achieved": round(k["flop"] / (k["ms"] * 1e-3) / 1e12, 1), "unit": "TFLOP/s", "bound": "tensor",
+                        "frac": round(k["flop"] / (k["ms"] * 1e-3) / 1e12 / peaks_tc, 3)})
+        elif k["byte"]:
+            row.update({"achieved": round(k["byte"] / (k["ms"] * 1e-3) / 1e9, 0), "unit": "GB/s", "bound": "hbm",
+                        "frac": round(k["byte"] / (k["ms"] * 1e-3) / 1e9 / peaks_hbm, 3)})
+        kernel_table[name] = row
     if args.breakdown and rank == 0:
         tot = sum(sum(v) for v in per.values())
         byname = {}
@@ -318,6 +361,24 @@ def main():
     h2d = B * int(np.prod(INPUT_SHAPE)) + B * 8
     d2h = 8
 
+    # ---- gradient all-reduce in isolation (bus bandwidth = 2(n-1)/n * bytes / t)
+    allreduce = None
+    if world > 1:
+        buf = eng.grads.clone()
+        for _ in range(3):
+            dist.all_reduce(buf)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(20):
+            dist.all_reduce(buf)
+        a1.record()
+        barrier()
+        ar_ms = max_over_ranks(a0.elapsed_time(a1)) / 20
+        nbytes = buf.numel() * 4
+        allreduce = {"bytes": nbytes, "ms": ar_ms, "bus_gbs": 2.0 * (world - 1) / world * nbytes / (ar_ms * 1e-3) / 1e9,
+                     "backend": "nccl " + ".".join(str(v) for v in torch.cuda.nccl.version())}
+
     # ---- roofline of the dominant kernel
     peaks = {}
     try:
@@ -360,7 +421,10 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps, "last_loss": loss},
             "gpu_launches": launches, "clocks": clock_info, "roofline": roofline,
+            "kernels": kernel_table, "serial_ms_per_step": round(serial_ms, 3),
         }
+        if allreduce:
+            line["allreduce"] = allreduce
         if world == 1 and not args.no_cpu_baseline:
             times, cores = cpu_train_steps(40, 2, CPU_SAMPLE_BATCH, budget_s=20.0)
             v = CPU_SAMPLE_BATCH * len(times) / sum(times)

@@ -764,7 +764,11 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   const int groups = (p.taps + p.tpi - 1) / p.tpi;
   const int out_tiles = groups * p.ci_tiles * p.n_tiles;
   const int sms = zkb_sm_count();
-  long long splits = (2ll * sms + out_tiles - 1) / out_tiles;  // ~2 waves of work items
+  // Short work items: the wgrad kernels run on a low-priority stream next to the dependent
+  // backward chain, and a high-priority kernel can only take an SM when a wgrad CTA retires.
+  int waves = 2;
+  if (const char* e = getenv("ZKB_WGRAD_WAVES")) waves = atoi(e) > 0 ? atoi(e) : waves;
+  long long splits = (static_cast<long long>(waves) * sms + out_tiles - 1) / out_tiles;
   if (splits > chunks) splits = chunks;
   if (splits < 1) splits = 1;
   p.chunks_per_split = static_cast<int>((chunks + splits - 1) / splits);
