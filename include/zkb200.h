@@ -36,14 +36,15 @@ const char* zkb_last_error_string(void);
  * crop OHxOW, random left-right flip, float32(x)/127.5 - 1 (true division), optional sign
  * binarisation, sparse label copy and optional one-hot.  Per-sample (ox, oy, flip) come from
  * `aug` ([B,3] int8) or, when NULL, from a counter-based generator keyed by (seed, step, sample).
- * training == 0: centre crop/pad only.
+ * training == 0: centre crop/pad only.  step_dev (optional, device memory) overrides `step`, so a
+ * captured CUDA graph can advance the generator between replays.
  * Replaces: examples/larq_experiment.py:24-37 (PadCropAndFlip.input/output) mapped per example by
  * tf.data at :126-139 through zookeeper/tf/preprocessing.py:59-75. */
 int zkb_preprocess_u8(const uint8_t* images, const long long* labels, const int* index,
                       const int8_t* aug, float* out, int* labels_out, float* onehot, int B, int IH,
                       int IW, int C, int OH, int OW, int pad_size, int training, int binarize,
                       int num_classes, unsigned long long seed, unsigned long long step,
-                      void* stream);
+                      const unsigned long long* step_dev, void* stream);
 
 /* ---- bit-level formulation (north_star items 2, 3) --------------------------------------------
  * Sign + bit-pack: 32 consecutive values along K -> one uint32 (bit j = 1 iff value >= 0, i.e.
@@ -172,12 +173,13 @@ int zkb_prep_dense_weights(const float* w_k_n, int K, int N, int Npad, void* w_f
 int zkb_sign_f32(const float* w, float* out, long long n, void* stream);
 /* Adam in the operation order of TF's ApplyAdam (lr_t = lr*sqrt(1-b2^t)/(1-b1^t) computed by the
  * caller) followed, for kernels (is_kernel != 0), by the ste_sign gradient mask |w| <= 1 and the
- * clip of the latent weight to [-1, 1].
+ * clip of the latent weight to [-1, 1].  lr_t_dev (optional, device memory) overrides lr_t (for
+ * captured CUDA graphs).
  * Replaces: tf.keras.optimizers.Adam examples/larq_experiment.py:120-122 and
  *           kernel_constraint="weight_clip" :55,66. */
 int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, float lr_t,
                   float beta1, float beta2, float eps, float grad_scale, int is_kernel,
-                  void* stream);
+                  const float* lr_t_dev, void* stream);
 
 /* ---- for callers that cannot allocate device memory ----------------------------------------------
  * (No counterpart in the reference: this entry point exists for hosts of this library, not for

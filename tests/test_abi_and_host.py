@@ -36,7 +36,7 @@ def test_argument_errors_are_reported_before_any_launch(native_lib):
     from zookeeper_b200 import native as zn
 
     with pytest.raises(zn.ZkbError, match="null pointer") as e:
-        zn.call("zkb_preprocess_u8", 0, 0, 0, 0, 0, 0, 0, 4, 28, 28, 1, 28, 28, 32, 1, 0, 10, 0, 0, 0)
+        zn.call("zkb_preprocess_u8", 0, 0, 0, 0, 0, 0, 0, 4, 28, 28, 1, 28, 28, 32, 1, 0, 10, 0, 0, 0, 0)
     assert e.value.status < 0
     with pytest.raises(zn.ZkbError, match="multiple of 32"):
         zn.call("zkb_sign_pack", 16, 16, 33, 0, 0)

@@ -32,7 +32,7 @@ def _preprocess(zn, img, out_hw, training, pad=0, aug=None, labels=None, binariz
     lab_out = torch.zeros(B, dtype=torch.int32, device="cuda") if labels is not None else None
     oh = torch.zeros(B, onehot_classes, dtype=torch.float32, device="cuda") if onehot_classes else None
     zn.call("zkb_preprocess_u8", zn.ptr(d_img), zn.ptr(d_lab), 0, zn.ptr(d_aug), zn.ptr(out), zn.ptr(lab_out),
-            zn.ptr(oh), B, IH, IW, C, out_hw[0], out_hw[1], pad, int(training), int(binarize), max(onehot_classes, 1), 0, 0, 0)
+            zn.ptr(oh), B, IH, IW, C, out_hw[0], out_hw[1], pad, int(training), int(binarize), max(onehot_classes, 1), 0, 0, 0, 0)
     torch.cuda.synchronize()
     return out.cpu().numpy(), (lab_out.cpu().numpy() if lab_out is not None else None), (oh.cpu().numpy() if oh is not None else None)
 
@@ -54,7 +54,7 @@ def test_preprocess_golden_variants(native_lib):
     assert np.array_equal(b, O.preprocess(img, (32, 32), True, 40, aug, binarize=True))
     assert set(np.unique(b).tolist()) <= {-1.0, 1.0}
     # empty batch is a no-op
-    zn.call("zkb_preprocess_u8", 16, 0, 0, 0, 16, 0, 0, 0, 32, 32, 3, 32, 32, 40, 1, 0, 1, 0, 0, 0)
+    zn.call("zkb_preprocess_u8", 16, 0, 0, 0, 16, 0, 0, 0, 32, 32, 3, 32, 32, 40, 1, 0, 1, 0, 0, 0, 0)
 
 
 def test_preprocess_gathers_by_index_and_uses_counter_rng(native_lib):
@@ -69,7 +69,7 @@ def test_preprocess_gathers_by_index_and_uses_counter_rng(native_lib):
     out = torch.empty(16, 28, 28, 1, dtype=torch.float32, device="cuda")
     lab = torch.empty(16, dtype=torch.int32, device="cuda")
     zn.call("zkb_preprocess_u8", zn.ptr(d_pool), zn.ptr(d_lab), zn.ptr(d_idx), 0, zn.ptr(out), zn.ptr(lab), 0,
-            16, 28, 28, 1, 28, 28, 32, 1, 0, 10, 77, 5, 0)
+            16, 28, 28, 1, 28, 28, 32, 1, 0, 10, 77, 5, 0, 0)
     torch.cuda.synchronize()
     aug = O.augmentation_params(77, 5, 16, 32, 28, 28)
     assert np.array_equal(out.cpu().numpy(), O.preprocess(pool[index], (28, 28), True, 32, aug))

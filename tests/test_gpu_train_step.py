@@ -259,3 +259,36 @@ def test_keras_shaped_fit_runs_on_the_engine(native_lib):
         assert task.model.engine.step_count == 2 * (256 // 64)
     finally:
         cli.commands = saved
+
+
+def test_cuda_graph_replay_matches_per_kernel_launches(native_lib):
+    """capture_train_step / train_step_graph: same trajectory as ordinary steps (same sample
+    indices, same counter-based augmentation, same Adam step sizes)."""
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    B, n = 32, 96
+    rng = np.random.default_rng(2)
+    pool = torch.as_tensor(rng.integers(0, 256, (n, 28, 28, 1), dtype=np.uint8)).cuda()
+    labs = torch.as_tensor(rng.integers(0, 10, (n,)).astype(np.int64)).cuda()
+    idx = [torch.as_tensor(rng.permutation(n)[:B].astype(np.int32)).cuda() for _ in range(4)]
+    a = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+    b = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+    a.init_glorot(0)
+    b.init_glorot(0)
+    for k in range(4):
+        a.train_step(pool, labs, idx[k], pad_size=32, seed=5)
+    b.train_step(pool, labs, idx[0], pad_size=32, seed=5)
+    b.capture_train_step(pool, labs, 32, 5)
+    losses = []
+    for k in range(1, 4):
+        b.train_step_graph(idx[k])
+        losses.append(b.last_loss())
+    torch.cuda.synchronize()
+    assert a.step_count == b.step_count == 4
+    assert np.array_equal(a.x0.cpu().numpy(), b.x0.cpu().numpy())          # same augmentation stream
+    assert abs(a.last_loss() - losses[-1]) <= 1e-3 * abs(a.last_loss())
+    pa, pb = a.get_params(), b.get_params()
+    for k in pa:
+        # float atomics in wgrad make runs differ in the last bits; near-zero gradients then move a
+        # few weights by +-lr in the other direction -- bound the fraction, as between any two runs
+        assert (np.abs(pa[k] - pb[k]) > 1e-3).mean() < 5e-3, k

@@ -41,6 +41,8 @@ struct PreParams {
   float* onehot;            // [B, num_classes] or null
   int B, IH, IW, C, OH, OW, pad_size, training, binarize, num_classes;
   unsigned long long seed, step;
+  const unsigned long long* step_dev;  // when non-null the step counter is read from device memory
+                                       // (lets a captured CUDA graph advance the augmentation RNG)
 };
 
 __device__ __forceinline__ void sample_aug(const PreParams& p, int b, int& ox, int& oy, int& flip) {
@@ -54,7 +56,8 @@ __device__ __forceinline__ void sample_aug(const PreParams& p, int b, int& ox, i
     flip = p.aug[3 * b + 2];
     return;
   }
-  const uint64_t r = mix64(mix64(p.seed ^ (p.step * 0xD1342543DE82EF95ull)) + static_cast<uint64_t>(b));
+  const uint64_t step = p.step_dev ? *p.step_dev : p.step;
+  const uint64_t r = mix64(mix64(p.seed ^ (step * 0xD1342543DE82EF95ull)) + static_cast<uint64_t>(b));
   const int rx = p.pad_size - p.OW + 1;
   const int ry = p.pad_size - p.OH + 1;
   ox = static_cast<int>((r & 0xFFFFu) % static_cast<uint32_t>(rx));
@@ -711,8 +714,9 @@ sign_f32_kernel(const float* __restrict__ w, float* __restrict__ out, long long 
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 adam_clip_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m,
-                 float* __restrict__ v, long long n, float lr_t, float b1, float b2, float eps,
-                 float gscale, int is_kernel) {
+                 float* __restrict__ v, long long n, float lr_t_host, float b1, float b2, float eps,
+                 float gscale, int is_kernel, const float* __restrict__ lr_t_dev) {
+  const float lr_t = lr_t_dev ? *lr_t_dev : lr_t_host;  // device copy: for captured CUDA graphs
   const long long nv = n / 4;
   const long long tid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -769,7 +773,8 @@ ZKB_API int zkb_preprocess_u8(const uint8_t* images, const long long* labels, co
                               const int8_t* aug, float* out, int* labels_out, float* onehot, int B,
                               int IH, int IW, int C, int OH, int OW, int pad_size, int training,
                               int binarize, int num_classes, unsigned long long seed,
-                              unsigned long long step, void* stream) {
+                              unsigned long long step, const unsigned long long* step_dev,
+                              void* stream) {
   ZKB_REQUIRE(images && out, "preprocess: null pointer");
   ZKB_REQUIRE(B >= 0 && IH > 0 && IW > 0 && C > 0 && OH > 0 && OW > 0, "preprocess: bad shape");
   if (B == 0) return ZKB_OK;
@@ -779,7 +784,7 @@ ZKB_API int zkb_preprocess_u8(const uint8_t* images, const long long* labels, co
     ZKB_REQUIRE(pad_size >= OH && pad_size >= OW, "preprocess: pad_size %d < crop size", pad_size);
   ZKB_REQUIRE(!onehot || (labels && num_classes > 0), "preprocess: one-hot needs labels");
   PreParams p{images, labels, index, aug, out, labels_out, onehot, B, IH, IW, C, OH, OW,
-              pad_size, training, binarize, num_classes, seed, step};
+              pad_size, training, binarize, num_classes, seed, step, step_dev};
   const long long work = static_cast<long long>(B) * OH * OW * C / 4;
   preprocess_kernel<<<grid_for(work, 256, 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
   ZKB_LAUNCH_CHECK("preprocess_kernel");
@@ -1014,13 +1019,13 @@ ZKB_API int zkb_sign_f32(const float* w, float* out, long long n, void* stream) 
 
 ZKB_API int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, float lr_t,
                           float beta1, float beta2, float eps, float grad_scale, int is_kernel,
-                          void* stream) {
+                          const float* lr_t_dev, void* stream) {
   ZKB_REQUIRE(w && g && m && v && n >= 0, "adam_clip: bad arguments");
   ZKB_REQUIRE(ZKB_ALIGNED16(w) && ZKB_ALIGNED16(g) && ZKB_ALIGNED16(m) && ZKB_ALIGNED16(v),
               "adam_clip: arenas must be 16-byte aligned");
   if (n == 0) return ZKB_OK;
   adam_clip_kernel<<<grid_for(n / 4 + 1, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      w, g, m, v, n, lr_t, beta1, beta2, eps, grad_scale, is_kernel);
+      w, g, m, v, n, lr_t, beta1, beta2, eps, grad_scale, is_kernel, lr_t_dev);
   ZKB_LAUNCH_CHECK("adam_clip_kernel");
   return ZKB_OK;
 }

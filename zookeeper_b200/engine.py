@@ -359,7 +359,8 @@ class BinaryNetEngine:
 
     def preprocess(self, images_u8: torch.Tensor, labels_i64: Optional[torch.Tensor], index: Optional[torch.Tensor],
                    training: bool, pad_size: int = 0, aug: Optional[torch.Tensor] = None, seed: int = 0,
-                   step: int = 0, binarize: bool = False, onehot: Optional[torch.Tensor] = None, batch: Optional[int] = None):
+                   step: int = 0, binarize: bool = False, onehot: Optional[torch.Tensor] = None, batch: Optional[int] = None,
+                   step_dev: Optional[torch.Tensor] = None):
         """Fused batch map of ``Preprocessing.__call__`` for the example's PadCropAndFlip
         (zookeeper/tf/preprocessing.py:59-75, examples/larq_experiment.py:24-37)."""
         if not hasattr(self, "_stream"):
@@ -369,7 +370,8 @@ class BinaryNetEngine:
         H, W, _ = self.input_shape
         self._call("zkb_preprocess_u8", zn.ptr(images_u8), zn.ptr(labels_i64), zn.ptr(index), zn.ptr(aug),
                    zn.ptr(self.x0), zn.ptr(self.labels) if labels_i64 is not None else 0, zn.ptr(onehot),
-                   B, IH, IW, C, H, W, pad_size, int(training), int(binarize), self.num_classes, seed, step)
+                   B, IH, IW, C, H, W, pad_size, int(training), int(binarize), self.num_classes, seed, step,
+                   zn.ptr(step_dev))
 
     def _all_reduce(self, t: torch.Tensor):
         self.dp.all_reduce_sum_(t)
@@ -535,17 +537,21 @@ class BinaryNetEngine:
         self._call("zkb_softmax_ce", zn.ptr(L.logits), L.cp, zn.ptr(self.labels), self.B, self.num_classes,
                    1.0 / (self.B * self.world), zn.ptr(L.ds), self.acc[nb4:].data_ptr(), zn.ptr(self.correct))
 
-    def optimizer_step(self):
-        self.step_count += 1
-        t = self.step_count
+    def _lr_t(self, t: int) -> float:
         # bias-corrected step size in fp32, as TF's ApplyAdam computes it from the fp32 beta powers
         f = np.float32
-        lr_t = float(f(self.lr) * np.sqrt(f(1) - f(self.b2) ** f(t), dtype=f) / (f(1) - f(self.b1) ** f(t)))
+        return float(f(self.lr) * np.sqrt(f(1) - f(self.b2) ** f(t), dtype=f) / (f(1) - f(self.b1) ** f(t)))
+
+    def optimizer_step(self, lr_dev: Optional[torch.Tensor] = None):
+        """Adam + clip.  ``lr_dev``: read the step size from device memory (captured graphs)."""
+        if lr_dev is None:
+            self.step_count += 1
+        lr_t = self._lr_t(max(self.step_count, 1))
         nk = self.n_kernel
         self._call("zkb_adam_clip", zn.ptr(self.params), zn.ptr(self.grads), zn.ptr(self.adam_m), zn.ptr(self.adam_v),
-                   nk, lr_t, self.b1, self.b2, self.eps, 1.0, 1)
+                   nk, lr_t, self.b1, self.b2, self.eps, 1.0, 1, zn.ptr(lr_dev))
         self._call("zkb_adam_clip", self.params[nk:].data_ptr(), self.grads[nk:].data_ptr(), self.adam_m[nk:].data_ptr(),
-                   self.adam_v[nk:].data_ptr(), self.n_beta, lr_t, self.b1, self.b2, self.eps, 1.0, 0)
+                   self.adam_v[nk:].data_ptr(), self.n_beta, lr_t, self.b1, self.b2, self.eps, 1.0, 0, zn.ptr(lr_dev))
 
     # ------------------------------------------------------------------ public steps
     def train_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, index: Optional[torch.Tensor] = None,
@@ -578,6 +584,57 @@ class BinaryNetEngine:
         if use_side:
             caller.wait_stream(self._main)
         self.launches_per_step = self._n_launch
+
+    # ------------------------------------------------------------------ CUDA-graph replay
+    def capture_train_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, pad_size: int, seed: int = 0) -> None:
+        """Capture one full train step (both streams, the all-reduce included) into a CUDA graph.
+
+        The ~90 launches of a step cost more host time than GPU time at small batches; a replay
+        is one launch.  What changes between steps lives in device memory and is refreshed before
+        each replay: the sample indices (``self.index_buf``), the step counter that keys the
+        augmentation RNG and Adam's bias-corrected step size.  ``images_u8`` / ``labels_i64`` are
+        the resident dataset pool and must stay alive and in place.  Run at least one ordinary
+        :meth:`train_step` first (first-use set-up must not happen inside a capture)."""
+        dev = self.device
+        self.index_buf = torch.zeros(self.B, dtype=torch.int32, device=dev)
+        self._dyn_step = torch.zeros(1, dtype=torch.int64, device=dev)
+        self._dyn_lr = torch.zeros(1, dtype=torch.float32, device=dev)
+        self._dyn_host = torch.zeros(2, dtype=torch.float64).pin_memory()   # [step, lr_t] staging
+        self._graph_pool = (images_u8, labels_i64)
+        graph = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize(dev)
+        saved_watch, self.watch = self.watch, None
+        try:
+            with torch.cuda.graph(graph, stream=self._main):
+                self._begin()
+                self.acc.zero_()
+                self.correct.zero_()
+                self.grads.zero_()
+                self.preprocess(images_u8, labels_i64, self.index_buf, True, pad_size, None, seed, 0,
+                                step_dev=self._dyn_step)
+                self.prepare_weights()
+                self.forward(training=True)
+                self.loss_and_grad()
+                self.backward(self._side if self.overlap else None)
+                if self.world > 1:
+                    self._all_reduce(self.grads)
+                self.optimizer_step(lr_dev=self._dyn_lr)
+        finally:
+            self.watch = saved_watch
+        self.launches_per_step = self._n_launch
+        self._graph = graph
+
+    def train_step_graph(self, index: torch.Tensor) -> None:
+        """Replay the captured step on the batch ``index`` (int32 device tensor of sample ids)."""
+        caller = torch.cuda.current_stream(self.device)
+        self.step_count += 1
+        self.index_buf.copy_(index, non_blocking=True)
+        self._dyn_step.fill_(self.step_count - 1)
+        self._dyn_lr.fill_(self._lr_t(self.step_count))
+        self._main.wait_stream(caller)
+        with torch.cuda.stream(self._main):
+            self._graph.replay()
+        caller.wait_stream(self._main)
 
     def eval_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, index: Optional[torch.Tensor] = None):
         """Validation pass (larq_experiment.py:133-139): centre crop/pad, moving statistics."""

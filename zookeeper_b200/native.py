@@ -31,7 +31,7 @@ D = c_double
 
 # name -> argument ctypes, in the order of include/zkb200.h
 SIGNATURES = {
-    "zkb_preprocess_u8": [P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, U, U, P],
+    "zkb_preprocess_u8": [P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, U, U, P, P],
     "zkb_sign_pack": [P, P, L, I, P],
     "zkb_bgemm_popc": [P, P, P, L, I, I, I, P],
     "zkb_conv_first_fwd": [P, P, P, I, I, I, I, I, I, P],
@@ -59,7 +59,7 @@ SIGNATURES = {
     "zkb_prep_conv_weights": [P, I, I, I, P, P, P, P],
     "zkb_prep_dense_weights": [P, I, I, I, P, P, P, P],
     "zkb_sign_f32": [P, P, L, P],
-    "zkb_adam_clip": [P, P, P, P, L, F, F, F, F, F, I, P],
+    "zkb_adam_clip": [P, P, P, P, L, F, F, F, F, F, I, P, P],
     "zkb_bn_train_sign_static": [P, I, L, I, P, F, F, I, P, P, P, P, P],
 }
 

@@ -225,6 +225,10 @@ class Sequential(Model):
             steps_per_epoch = len(train_data) // train_data.batch_size
         stream = train_data.index_stream()
         nb4 = 4 * eng.n_beta
+        pad = spec.pad_size if spec.random_crop else 0
+        seed = train_data.seed + rank
+        use_graph = os.environ.get("ZKB_NO_GRAPH", "0") != "1"
+        captured = False
         hist = {"loss": [], "accuracy": [], "images_per_sec": []}
         if validation_data is not None:
             hist.update({"val_loss": [], "val_accuracy": []})
@@ -233,11 +237,24 @@ class Sequential(Model):
             run_ok = torch.zeros(1, dtype=torch.int64, device=eng.device)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
-            for _ in range(steps_per_epoch):
-                idx = next(stream)[rank::world]
-                d_idx = torch.as_tensor(idx.astype(np.int32)).to(eng.device, non_blocking=True)
-                eng.train_step(d_img, d_lab, d_idx, pad_size=spec.pad_size if spec.random_crop else 0,
-                               seed=train_data.seed + rank)
+            # one upload of the epoch's sample indices; a step then takes its row on the device
+            epoch_idx = np.stack([next(stream)[rank::world] for _ in range(steps_per_epoch)]).astype(np.int32)
+            d_epoch_idx = torch.as_tensor(epoch_idx).to(eng.device, non_blocking=True)
+            for k in range(steps_per_epoch):
+                if captured:
+                    eng.train_step_graph(d_epoch_idx[k])
+                else:
+                    eng.train_step(d_img, d_lab, d_epoch_idx[k], pad_size=pad, seed=seed)
+                    if use_graph:
+                        # after one ordinary step (first-use set-up done) replay a captured graph:
+                        # a step becomes one launch instead of ~90
+                        try:
+                            eng.capture_train_step(d_img, d_lab, pad, seed)
+                            captured = True
+                        except Exception as exc:  # keep training without the graph
+                            use_graph = False
+                            if rank == 0:
+                                print(f"CUDA-graph capture unavailable ({exc}); continuing with per-kernel launches")
                 run_loss += eng.acc[nb4:nb4 + 1]
                 run_ok += eng.correct
             torch.cuda.synchronize()
