@@ -661,41 +661,70 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
 // Weight preparation: sign(W) in the layouts the GEMM engines read.
 // ------------------------------------------------------------------------------------------
 // conv: W f32 [ks,ks,Cin,Cout] (HWIO) -> fwd [Cout][tap][Cin], dgrad [Cin][tap_flipped][Cout] (bf16)
+// One 32x32 (ci, co) tile per block and tap, transposed through shared memory so that the read of
+// W and all three writes are coalesced.
 __global__ void __launch_bounds__(256)
 prep_conv_weights_kernel(const float* __restrict__ w, int ks, int Cin, int Cout,
                          uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad,
                          int8_t* __restrict__ w_fwd8) {
+  __shared__ uint8_t neg[32][33];   // 1 = negative weight
   const int taps = ks * ks;
-  const long long total = static_cast<long long>(taps) * Cin * Cout;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int co = static_cast<int>(i % Cout);
-    const long long t = i / Cout;
-    const int ci = static_cast<int>(t % Cin);
-    const int tap = static_cast<int>(t / Cin);
-    const uint16_t s = pm1_bf16(w[i] >= 0.0f);
-    w_fwd[(static_cast<long long>(co) * taps + tap) * Cin + ci] = s;
-    if (w_fwd8) w_fwd8[(static_cast<long long>(co) * taps + tap) * Cin + ci] = (s & 0x8000u) ? -1 : 1;
-    const int kh = tap / ks, kw = tap % ks;
-    const int ftap = (ks - 1 - kh) * ks + (ks - 1 - kw);
-    w_dgrad[(static_cast<long long>(ci) * taps + ftap) * Cout + co] = s;
+  const int tap = blockIdx.z;
+  const int ci0 = blockIdx.y * 32, co0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int kh = tap / ks, kw = tap % ks;
+  const int ftap = (ks - 1 - kh) * ks + (ks - 1 - kw);
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int ci = ci0 + ty + 8 * r, co = co0 + tx;
+    if (ci < Cin && co < Cout) {
+      const bool nonneg = w[(static_cast<long long>(tap) * Cin + ci) * Cout + co] >= 0.0f;
+      neg[ty + 8 * r][tx] = nonneg ? 0 : 1;
+      w_dgrad[(static_cast<long long>(ci) * taps + ftap) * Cout + co] = pm1_bf16(nonneg);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int co = co0 + ty + 8 * r, ci = ci0 + tx;
+    if (ci < Cin && co < Cout) {
+      const bool nonneg = neg[tx][ty + 8 * r] == 0;
+      const long long o = (static_cast<long long>(co) * taps + tap) * Cin + ci;
+      w_fwd[o] = pm1_bf16(nonneg);
+      if (w_fwd8) w_fwd8[o] = nonneg ? 1 : -1;
+    }
   }
 }
 
-// dense: W f32 [K][N] -> fwd [Npad][K] (rows >= N zero), dgrad [K][Npad] (cols >= N zero)
+// dense: W f32 [K][N] -> fwd [Npad][K] (rows >= N zero), dgrad [K][Npad] (cols >= N zero); same
+// tile transpose.
 __global__ void __launch_bounds__(256)
 prep_dense_weights_kernel(const float* __restrict__ w, int K, int N, int Npad,
                           uint16_t* __restrict__ w_fwd, uint16_t* __restrict__ w_dgrad,
                           int8_t* __restrict__ w_fwd8) {
-  const long long total = static_cast<long long>(K) * Npad;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int n = static_cast<int>(i % Npad);
-    const int k = static_cast<int>(i / Npad);
-    const uint16_t s = (n < N) ? pm1_bf16(w[static_cast<long long>(k) * N + n] >= 0.0f) : 0;
-    w_fwd[static_cast<long long>(n) * K + k] = s;
-    if (w_fwd8) w_fwd8[static_cast<long long>(n) * K + k] = (s == 0) ? 0 : ((s & 0x8000u) ? -1 : 1);
-    w_dgrad[i] = s;
+  __shared__ uint8_t code[32][33];  // 0 = +1, 1 = -1, 2 = padding
+  const int k0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int k = k0 + ty + 8 * r, n = n0 + tx;
+    if (k < K && n < Npad) {
+      uint8_t c = 2;
+      if (n < N) c = w[static_cast<long long>(k) * N + n] >= 0.0f ? 0 : 1;
+      code[ty + 8 * r][tx] = c;
+      w_dgrad[static_cast<long long>(k) * Npad + n] = c == 2 ? 0 : pm1_bf16(c == 0);
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {
+    const int n = n0 + ty + 8 * r, k = k0 + tx;
+    if (k < K && n < Npad) {
+      const uint8_t c = code[tx][ty + 8 * r];
+      const long long o = static_cast<long long>(n) * K + k;
+      w_fwd[o] = c == 2 ? 0 : pm1_bf16(c == 0);
+      if (w_fwd8) w_fwd8[o] = c == 2 ? 0 : (c == 0 ? 1 : -1);
+    }
   }
 }
 
@@ -989,8 +1018,8 @@ ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long l
 ZKB_API int zkb_prep_conv_weights(const float* w_hwio, int ksize, int Cin, int Cout, void* w_fwd,
                                   void* w_dgrad, void* w_fwd_i8, void* stream) {
   ZKB_REQUIRE(w_hwio && w_fwd && w_dgrad, "prep_conv_weights: null pointer");
-  const long long total = static_cast<long long>(ksize) * ksize * Cin * Cout;
-  prep_conv_weights_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  dim3 grid((Cout + 31) / 32, (Cin + 31) / 32, ksize * ksize);
+  prep_conv_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       w_hwio, ksize, Cin, Cout, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad),
       static_cast<int8_t*>(w_fwd_i8));
   ZKB_LAUNCH_CHECK("prep_conv_weights_kernel");
@@ -1001,8 +1030,8 @@ ZKB_API int zkb_prep_dense_weights(const float* w_k_n, int K, int N, int Npad, v
                                    void* w_dgrad, void* w_fwd_i8, void* stream) {
   ZKB_REQUIRE(w_k_n && w_fwd && w_dgrad, "prep_dense_weights: null pointer");
   ZKB_REQUIRE(Npad >= N, "prep_dense_weights: Npad < N");
-  const long long total = static_cast<long long>(K) * Npad;
-  prep_dense_weights_kernel<<<grid_for(total, 256, 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  dim3 grid((Npad + 31) / 32, (K + 31) / 32);
+  prep_dense_weights_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       w_k_n, K, N, Npad, static_cast<uint16_t*>(w_fwd), static_cast<uint16_t*>(w_dgrad),
       static_cast<int8_t*>(w_fwd_i8));
   ZKB_LAUNCH_CHECK("prep_dense_weights_kernel");
