@@ -2,7 +2,8 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 {
-echo "== pairs: parity tests (kernels)"; ZKB_KGEMM_PAIRS=1 timeout 300 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q 2>&1 | tail -15
-echo "== pairs off"; timeout 300 python scripts/bench_gemm.py fwd8 dgrad
-echo "== pairs on"; ZKB_KGEMM_PAIRS=1 timeout 300 python scripts/bench_gemm.py fwd8 dgrad
+for w in 2 3 4 8; do
+echo "== reduce waves=$w"; ZKB_REDUCE_WAVES=$w timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --breakdown 2> gpurun_out/bd_$w.txt | cut -c1-150
+grep -E "TOTAL zkb_(bn_bwd_reduce|bn_stats|maxpool)" gpurun_out/bd_$w.txt
+done
 } 2>&1 | tee gpurun_out/ab.log

@@ -5,6 +5,7 @@
 #include <cuda_bf16.h>
 
 #include <mutex>
+#include <stdlib.h>
 
 #include "zkb_host.h"
 
@@ -253,6 +254,53 @@ __device__ __forceinline__ void block_channel_reduce(const double (&a0)[VEC], co
   }
 }
 
+// Per-thread partial sums that stay exact for the integer maps: int16 inputs accumulate in
+// 32-bit integers (|x| <= 4608: 128 rows of x fit int32, 128 rows of x^2 fit uint32) and are
+// flushed to double every 128 rows; float inputs accumulate in float and flush every 32 rows.
+template <typename T, int VEC>
+struct StatAcc;
+template <int VEC>
+struct StatAcc<int16_t, VEC> {
+  static constexpr int kFlush = 128;
+  int s0[VEC];
+  unsigned s1[VEC];
+  __device__ __forceinline__ void clear() {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { s0[j] = 0; s1[j] = 0u; }
+  }
+  __device__ __forceinline__ void add(const Vec16<int16_t>& v) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      const int t = v.v[j];
+      s0[j] += t;
+      s1[j] += static_cast<unsigned>(t * t);
+    }
+  }
+  __device__ __forceinline__ void flush(double (&a0)[VEC], double (&a1)[VEC]) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { a0[j] += s0[j]; a1[j] += s1[j]; }
+    clear();
+  }
+};
+template <int VEC>
+struct StatAcc<float, VEC> {
+  static constexpr int kFlush = 32;
+  float s0[VEC], s1[VEC];
+  __device__ __forceinline__ void clear() {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { s0[j] = 0.f; s1[j] = 0.f; }
+  }
+  __device__ __forceinline__ void add(const Vec16<float>& v) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { s0[j] += v.v[j]; s1[j] = fmaf(v.v[j], v.v[j], s1[j]); }
+  }
+  __device__ __forceinline__ void flush(double (&a0)[VEC], double (&a1)[VEC]) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { a0[j] += s0[j]; a1[j] += s1[j]; }
+    clear();
+  }
+};
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_stats_kernel(const T* __restrict__ x, long long rows, int C, double* __restrict__ sum,
@@ -266,32 +314,30 @@ bn_stats_kernel(const T* __restrict__ x, long long rows, int C, double* __restri
 #pragma unroll
   for (int j = 0; j < VEC; ++j) a0[j] = a1[j] = 0.0;
   if (rl < lanes) {
-    float f0[VEC], f1[VEC];
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) f0[j] = f1[j] = 0.f;
+    StatAcc<T, VEC> acc;
+    acc.clear();
     int n = 0;
-    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
-         r += static_cast<long long>(gridDim.x) * lanes) {
-      Vec16<T> v;
-      v.load(x + r * C + cl * VEC);
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        const float t = v.get(j);
-        f0[j] += t;
-        f1[j] = fmaf(t, t, f1[j]);
-      }
-      // flush float partials to double every 32 rows (keeps integer inputs exact: 32*4608^2 < 2^30)
-      if (++n == 32) {
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-          a0[j] += f0[j]; a1[j] += f1[j];
-          f0[j] = f1[j] = 0.f;
-        }
-        n = 0;
-      }
+    const long long step = static_cast<long long>(gridDim.x) * lanes;
+    long long r = static_cast<long long>(blockIdx.x) * lanes + rl;
+    const T* px = x + cl * VEC;
+    // four independent 16-byte loads in flight per thread
+    for (; r + 3 * step < rows; r += 4 * step) {
+      Vec16<T> v0, v1, v2, v3;
+      v0.load(px + r * C);
+      v1.load(px + (r + step) * C);
+      v2.load(px + (r + 2 * step) * C);
+      v3.load(px + (r + 3 * step) * C);
+      acc.add(v0); acc.add(v1); acc.add(v2); acc.add(v3);
+      n += 4;
+      if (n >= StatAcc<T, VEC>::kFlush - 3) { acc.flush(a0, a1); n = 0; }
     }
-#pragma unroll
-    for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
+    for (; r < rows; r += step) {
+      Vec16<T> v;
+      v.load(px + r * C);
+      acc.add(v);
+      if (++n >= StatAcc<T, VEC>::kFlush - 3) { acc.flush(a0, a1); n = 0; }
+    }
+    acc.flush(a0, a1);
   }
   block_channel_reduce<VEC>(a0, a1, tpr, C, sum, sumsq);
 }
@@ -335,11 +381,19 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
   for (int j = 0; j < VEC; ++j) {
     mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j]; be[j] = beta[cl * VEC + j];
   }
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long r = i / tpr;
-    Vec16<T> v;
-    v.load(x + r * C + cl * VEC);
+  const long long gstride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < total;
+       i0 += 2 * gstride) {
+   // two independent rows per iteration: both loads are issued before either is consumed
+   Vec16<T> vv[2];
+   const bool has2 = i0 + gstride < total;
+   vv[0].load(x + (i0 / tpr) * C + cl * VEC);
+   if (has2) vv[1].load(x + ((i0 + gstride) / tpr) * C + cl * VEC);
+#pragma unroll
+   for (int u = 0; u < 2; ++u) {
+    if (u == 1 && !has2) break;
+    const long long r = (i0 + u * gstride) / tpr;
+    const Vec16<T>& v = vv[u];
     uint16_t s[VEC];
     float a[VEC];
 #pragma unroll
@@ -379,6 +433,7 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
       for (int j = 0; j < VEC; j += 4)
         *reinterpret_cast<float4*>(o + j) = make_float4(a[j], a[j + 1], a[j + 2], a[j + 3]);
     }
+   }
   }
 }
 
@@ -386,6 +441,40 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
 // 2x2/2 'valid' max-pool on integer conv outputs, first maximum in row-major window order wins
 // (strict > replacement), fused with the BatchNorm statistics of the pooled map.
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pool_one(const int16_t* __restrict__ y, int H, int W, int C, int PH,
+                                         int PW, long long r, int cl, int16_t* __restrict__ p_out,
+                                         uint8_t* __restrict__ arg_out, Vec16<int16_t>& best) {
+  constexpr int VEC = 8;
+  const int pw = static_cast<int>(r % PW);
+  const long long t = r / PW;
+  const int ph = static_cast<int>(t % PH);
+  const long long b = t / PH;
+  const int16_t* base = y + ((b * H + 2 * ph) * W + 2 * pw) * C + cl * VEC;
+  Vec16<int16_t> v01, v10, v11;
+  best.load(base);
+  v01.load(base + C);
+  v10.load(base + static_cast<long long>(W) * C);
+  v11.load(base + static_cast<long long>(W) * C + C);
+  uint8_t am[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    uint8_t k = 0;
+    if (v01.v[j] > best.v[j]) { best.v[j] = v01.v[j]; k = 1; }
+    if (v10.v[j] > best.v[j]) { best.v[j] = v10.v[j]; k = 2; }
+    if (v11.v[j] > best.v[j]) { best.v[j] = v11.v[j]; k = 3; }
+    am[j] = k;
+  }
+  uint32_t w[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e)
+    w[e] = (static_cast<uint32_t>(static_cast<uint16_t>(best.v[2 * e]))) |
+           (static_cast<uint32_t>(static_cast<uint16_t>(best.v[2 * e + 1])) << 16);
+  *reinterpret_cast<uint4*>(p_out + r * C + cl * VEC) = make_uint4(w[0], w[1], w[2], w[3]);
+  const uint32_t alo = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+  const uint32_t ahi = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+  *reinterpret_cast<uint2*>(arg_out + r * C + cl * VEC) = make_uint2(alo, ahi);
+}
+
 __global__ void __launch_bounds__(256)
 maxpool2_i16_kernel(const int16_t* __restrict__ y, int B, int H, int W, int C,
                     int16_t* __restrict__ p_out, uint8_t* __restrict__ arg_out,
@@ -398,56 +487,31 @@ maxpool2_i16_kernel(const int16_t* __restrict__ y, int B, int H, int W, int C,
   const int PH = H / 2, PW = W / 2;
   const long long rows = static_cast<long long>(B) * PH * PW;
   double a0[VEC], a1[VEC];
-  float f0[VEC], f1[VEC];
 #pragma unroll
-  for (int j = 0; j < VEC; ++j) { a0[j] = a1[j] = 0.0; f0[j] = f1[j] = 0.f; }
-  int n = 0;
+  for (int j = 0; j < VEC; ++j) a0[j] = a1[j] = 0.0;
   if (rl < lanes) {
-    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
-         r += static_cast<long long>(gridDim.x) * lanes) {
-      const int pw = static_cast<int>(r % PW);
-      const long long t = r / PW;
-      const int ph = static_cast<int>(t % PH);
-      const int b = static_cast<int>(t / PH);
-      const int16_t* base = y + ((static_cast<long long>(b) * H + 2 * ph) * W + 2 * pw) * C + cl * VEC;
-      Vec16<int16_t> v00, v01, v10, v11;
-      v00.load(base);
-      v01.load(base + C);
-      v10.load(base + static_cast<long long>(W) * C);
-      v11.load(base + static_cast<long long>(W) * C + C);
-      int16_t m[VEC];
-      uint8_t am[VEC];
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        int16_t best = v00.v[j];
-        uint8_t k = 0;
-        if (v01.v[j] > best) { best = v01.v[j]; k = 1; }
-        if (v10.v[j] > best) { best = v10.v[j]; k = 2; }
-        if (v11.v[j] > best) { best = v11.v[j]; k = 3; }
-        m[j] = best;
-        am[j] = k;
-        const float tf = static_cast<float>(best);
-        f0[j] += tf;
-        f1[j] = fmaf(tf, tf, f1[j]);
-      }
-      uint32_t w[4];
-#pragma unroll
-      for (int e = 0; e < 4; ++e)
-        w[e] = (static_cast<uint32_t>(static_cast<uint16_t>(m[2 * e]))) |
-               (static_cast<uint32_t>(static_cast<uint16_t>(m[2 * e + 1])) << 16);
-      *reinterpret_cast<uint4*>(p_out + r * C + cl * VEC) = make_uint4(w[0], w[1], w[2], w[3]);
-      const uint32_t alo = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
-      const uint32_t ahi = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
-      *reinterpret_cast<uint2*>(arg_out + r * C + cl * VEC) = make_uint2(alo, ahi);
-      if (++n == 32) {
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
-        n = 0;
-      }
+    StatAcc<int16_t, VEC> acc;
+    acc.clear();
+    int n = 0;
+    const long long step = static_cast<long long>(gridDim.x) * lanes;
+    long long r = static_cast<long long>(blockIdx.x) * lanes + rl;
+    // two pooled pixels (eight 16-byte loads) in flight per thread
+    for (; r + step < rows; r += 2 * step) {
+      Vec16<int16_t> m0, m1;
+      pool_one(y, H, W, C, PH, PW, r, cl, p_out, arg_out, m0);
+      pool_one(y, H, W, C, PH, PW, r + step, cl, p_out, arg_out, m1);
+      acc.add(m0); acc.add(m1);
+      n += 2;
+      if (n >= 126) { acc.flush(a0, a1); n = 0; }
     }
+    for (; r < rows; r += step) {
+      Vec16<int16_t> m0;
+      pool_one(y, H, W, C, PH, PW, r, cl, p_out, arg_out, m0);
+      acc.add(m0);
+      if (++n >= 126) { acc.flush(a0, a1); n = 0; }
+    }
+    acc.flush(a0, a1);
   }
-#pragma unroll
-  for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; }
   block_channel_reduce<VEC>(a0, a1, tpr, C, sum, sumsq);
 }
 
@@ -538,22 +602,34 @@ bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long 
       f0[j] = f1[j] = 0.f;
     }
     int n = 0;
-#pragma unroll 4
-    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows;
-         r += static_cast<long long>(gridDim.x) * lanes) {
-      const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
-      const float gg[4] = {gv.x, gv.y, gv.z, gv.w};
-      float xv[4];
-      load4(x + r * C + cl * VEC, xv);
+    const long long step = static_cast<long long>(gridDim.x) * lanes;
+    // four rows per iteration: all eight loads are issued before the first is consumed
+    for (long long r0 = static_cast<long long>(blockIdx.x) * lanes + rl; r0 < rows; r0 += 4 * step) {
+      float gg[4][4], xv[4][4];
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        const float xh = (xv[j] - mu[j]) * rs[j];
-        const float a = xh + be[j];
-        const float da = (ste && fabsf(a) > 1.0f) ? 0.f : gg[j];
-        f0[j] += da;
-        f1[j] = fmaf(da, xh, f1[j]);
+      for (int u = 0; u < 4; ++u) {
+        const long long r = r0 + u * step;
+        if (r < rows) {
+          load4(g + r * C + cl * VEC, gg[u]);
+          load4(x + r * C + cl * VEC, xv[u]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { gg[u][j] = 0.f; xv[u][j] = mu[j]; }   // contributes nothing
+        }
       }
-      if (++n == 64) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          const float xh = (xv[u][j] - mu[j]) * rs[j];
+          const float a = xh + be[j];
+          const float da = (ste && fabsf(a) > 1.0f) ? 0.f : gg[u][j];
+          f0[j] += da;
+          f1[j] = fmaf(da, xh, f1[j]);
+        }
+      }
+      n += 4;
+      if (n >= 64) {
 #pragma unroll
         for (int j = 0; j < VEC; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
         n = 0;
@@ -788,6 +864,15 @@ adam_clip_kernel(float* __restrict__ w, const float* __restrict__ g, float* __re
 // ============================================================================================
 using namespace zkb;
 
+static int reduce_waves() {
+  static int w = -1;
+  if (w < 0) {
+    const char* e = getenv("ZKB_REDUCE_WAVES");
+    w = (e && atoi(e) > 0) ? atoi(e) : 8;
+  }
+  return w;
+}
+
 static int grid_for(long long work_items, int block, int max_waves = 8) {
   const long long cap = static_cast<long long>(zkb_sm_count()) * max_waves;
   long long g = (work_items + block - 1) / block;
@@ -879,7 +964,7 @@ ZKB_API int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, dou
   ZKB_REQUIRE(sum && sumsq, "bn_stats: null accumulator");
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / vec);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 8);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
   const size_t smem = 2 * 256 * vec * sizeof(double);
   if (x_is_i16)
     bn_stats_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
@@ -935,7 +1020,7 @@ ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_
   if (B == 0) return ZKB_OK;
   const long long rows = static_cast<long long>(B) * (H / 2) * (W / 2);
   const int lanes = 256 / (C / 8);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, 8);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, reduce_waves());
   const size_t smem = 2 * 256 * 8 * sizeof(double);
   maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);
@@ -963,7 +1048,7 @@ ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long 
   ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax, "bn_bwd_reduce: null pointer");
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / 4);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 8);
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
   const size_t smem = 2 * 256 * 4 * sizeof(double);
   if (x_is_i16)
     bn_bwd_reduce_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
@@ -1130,7 +1215,7 @@ ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows
   ZKB_CUDA(cudaMemsetAsync(sc->sum, 0, sizeof(double) * C, st));
   ZKB_CUDA(cudaMemsetAsync(sc->sumsq, 0, sizeof(double) * C, st));
   const int lanes = 256 / (C / vec);
-  const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, 8);
+  const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
   const size_t smem = 2 * 256 * vec * sizeof(double);
   const int grid_a = grid_for(rows * (C / vec), 256, 16);
   if (x_is_i16) {
