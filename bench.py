@@ -103,7 +103,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -206,8 +206,26 @@ def global_work(eng, name):
     return None
 
 
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    """Libraries (NCCL prints its version banner) write to fd 1; the contract is ONE JSON line on
+    stdout.  Route fd 1 to stderr for the whole run and keep the real stdout for the result line."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def main():
     args = parse()
+    _claim_stdout()
     if args.impl == "reference":
         run_reference(args)
         return
@@ -452,7 +470,7 @@ def main():
                 "value": v, "unit": UNIT, "cores": cores, "kind": "port",
                 "sample": f"{len(times)} train steps of batch {CPU_SAMPLE_BATCH} (BASELINE.json configs[0]) of the "
                           f"torch-CPU fp32 restatement, {cores} threads"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 

@@ -148,14 +148,17 @@ int zkb_softmax_ce(const float* logits, int ld, const int* labels, int B, int nu
                    void* stream);
 /* BatchNorm backward.  g = gradient w.r.t. sign(a) (ste != 0: masked where |a| > 1, the ste_sign
  * backward) or w.r.t. a (ste == 0).  reduce: sum(da), sum(da*xhat); finalize: dbeta and the two
- * means; apply: dx = rstd*(da - mean(da) - xhat*mean(da*xhat)) written as f32 (out_mode 0), as
+ * means (dbeta = dbeta_scale * sum(da): 1/world when the sums were all-reduced for SyncBN and the
+ * gradient arena is summed across ranks afterwards); apply: dx = rstd*(da - mean(da) -
+ * xhat*mean(da*xhat)) written as f32 (out_mode 0), as
  * hi/lo bf16 (1), or hi/lo scattered through the 2x2 pool argmax into the [B,H,W,C] map (2).
  * Replaces: TF autodiff of BatchNormalization / ste_sign / MaxPool2D (model.fit, :147-153). */
 int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
                       const float* mean, const float* rstd, const float* beta, int ste,
                       double* sum_da, double* sum_dax, void* stream);
-int zkb_bn_bwd_finalize(const double* sum_da, const double* sum_dax, double count, int C,
-                        float* dbeta, float* mean_da, float* mean_dax, void* stream);
+int zkb_bn_bwd_finalize(const double* sum_da, const double* sum_dax, double count,
+                        double dbeta_scale, int C, float* dbeta, float* mean_da, float* mean_dax,
+                        void* stream);
 int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
                      const float* mean, const float* rstd, const float* beta, const float* mean_da,
                      const float* mean_dax, int ste, int out_mode, float* out_f32, void* out_hi,

@@ -2,7 +2,7 @@
 # One GPU visit: parity tests, smoke, bench with per-kernel breakdown.
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -30 | tee gpurun_out/pytest_gpu.log
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -30 | tee gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee gpurun_out/smoke.log
-timeout 900 python bench.py --steps 10 --warmup 3 --breakdown > gpurun_out/bench.json 2> gpurun_out/bench_breakdown.txt
-echo "bench exit=$?"; cat gpurun_out/bench.json; head -80 gpurun_out/bench_breakdown.txt
+timeout 900 python bench.py --steps 20 --warmup 5 --breakdown > gpurun_out/bench.json 2> gpurun_out/bench_breakdown.txt
+echo "bench exit=$?"; cat gpurun_out/bench.json; grep TOTAL gpurun_out/bench_breakdown.txt | head -14

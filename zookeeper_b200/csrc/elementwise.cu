@@ -643,12 +643,12 @@ bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long 
 
 // Per channel: dbeta = sum(da) into the gradient arena; means for the apply pass.
 __global__ void bn_bwd_finalize_kernel(const double* __restrict__ sum_da,
-                                       const double* __restrict__ sum_dax, double count, int C,
-                                       float* __restrict__ dbeta, float* __restrict__ mean_da,
-                                       float* __restrict__ mean_dax) {
+                                       const double* __restrict__ sum_dax, double count,
+                                       double dbeta_scale, int C, float* __restrict__ dbeta,
+                                       float* __restrict__ mean_da, float* __restrict__ mean_dax) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  if (dbeta) dbeta[c] = static_cast<float>(sum_da[c]);
+  if (dbeta) dbeta[c] = static_cast<float>(sum_da[c] * dbeta_scale);
   mean_da[c] = static_cast<float>(sum_da[c] / count);
   mean_dax[c] = static_cast<float>(sum_dax[c] / count);
 }
@@ -1060,12 +1060,13 @@ ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long 
   return ZKB_OK;
 }
 
-ZKB_API int zkb_bn_bwd_finalize(const double* sum_da, const double* sum_dax, double count, int C,
-                                float* dbeta, float* mean_da, float* mean_dax, void* stream) {
+ZKB_API int zkb_bn_bwd_finalize(const double* sum_da, const double* sum_dax, double count,
+                                double dbeta_scale, int C, float* dbeta, float* mean_da,
+                                float* mean_dax, void* stream) {
   ZKB_REQUIRE(sum_da && sum_dax && mean_da && mean_dax, "bn_bwd_finalize: null pointer");
   ZKB_REQUIRE(count > 0 && C > 0, "bn_bwd_finalize: bad count / C");
   bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      sum_da, sum_dax, count, C, dbeta, mean_da, mean_dax);
+      sum_da, sum_dax, count, dbeta_scale, C, dbeta, mean_da, mean_dax);
   ZKB_LAUNCH_CHECK("bn_bwd_finalize_kernel");
   return ZKB_OK;
 }

@@ -461,7 +461,8 @@ class BinaryNetEngine:
             self._all_reduce(L.sum_da)
             self._all_reduce(L.sum_dax)
             count *= self.world
-        self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, L.cp, zn.ptr(L.dbeta),
+        self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count,
+                   (1.0 / self.world) if self.sync_bn else 1.0, L.cp, zn.ptr(L.dbeta),
                    zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
         self._call("zkb_conv_first_bwd_wgrad", zn.ptr(self.x0), zn.ptr(L.wq), zn.ptr(L.ds), *geom, zn.ptr(L.mean),
                    zn.ptr(L.rstd), zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), zn.ptr(L.dkernel))
@@ -502,7 +503,8 @@ class BinaryNetEngine:
                 self._all_reduce(L.sum_da)
                 self._all_reduce(L.sum_dax)
                 count *= self.world
-            self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, L.cp, zn.ptr(L.dbeta),
+            self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count,
+                   (1.0 / self.world) if self.sync_bn else 1.0, L.cp, zn.ptr(L.dbeta),
                        zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
             if l.kind == "conv" and l.pool:
                 mode, of32, ohi, olo, arg = 2, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.arg)

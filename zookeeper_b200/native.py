@@ -54,7 +54,7 @@ SIGNATURES = {
     "zkb_maxpool2_i16": [P, I, I, I, I, P, P, P, P, P],
     "zkb_softmax_ce": [P, I, P, I, I, F, P, P, P, P],
     "zkb_bn_bwd_reduce": [P, P, I, L, I, P, P, P, I, P, P, P],
-    "zkb_bn_bwd_finalize": [P, P, D, I, P, P, P, P],
+    "zkb_bn_bwd_finalize": [P, P, D, D, I, P, P, P, P],
     "zkb_bn_bwd_apply": [P, P, I, L, I, P, P, P, P, P, I, I, P, P, P, P, I, I, P],
     "zkb_prep_conv_weights": [P, I, I, I, P, P, P, P],
     "zkb_prep_dense_weights": [P, I, I, I, P, P, P, P],
