@@ -442,6 +442,14 @@ def main():
                 roofline["traffic"] = json.load(f).get(f"{dominant[0]}[{dominant[1]}]")
         except OSError:
             pass
+        # the same launch timed alone (serial per-launch pass before the timed region): in the timed
+        # region the step runs on two streams and this kernel shares the SMs with a wgrad GEMM
+        ser_s = statistics.mean(per[dominant]) * 1e-3
+        roofline["serial"] = {"avg_launch_ms": ser_s * 1e3, "achieved": work[1] / ser_s / (1e12 if work[0] == "flop" else 1e9),
+                              "frac": work[1] / ser_s / (1e12 if work[0] == "flop" else 1e9) / roofline["peak"]}
+        if work[0] == "flop" and "grad" in dominant[0]:
+            roofline["note"] = ("algorithmic 2*M*N*K; the kernel issues twice that in bf16 MMAs (hi + lo split of dy, "
+                                "needed for the 1e-4 parity budget), i.e. issued/peak = 2 x frac")
         roofline.update({"kernel": f"{dominant[0]}[{dominant[1]}]", "avg_launch_ms": statistics.mean(dom_ms),
                          "launches_timed": len(dom_ms),
                          "peak_source": "MEASURED_PEAKS.json (sustained)" if peaks else "fallback",

@@ -167,7 +167,8 @@ def test_binary_conv_forward_is_bit_exact_with_zero_same_padding(native_lib, B, 
     assert float(ref[:, 0, 0].abs().max()) <= 4 * Cin
 
 
-@pytest.mark.parametrize("B,H,W,Cin,Cout", [(5, 13, 13, 128, 256), (3, 26, 26, 128, 128), (64, 6, 6, 512, 512)])
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(5, 13, 13, 128, 256), (3, 26, 26, 128, 128), (64, 6, 6, 512, 512),
+                                             (1, 6, 6, 256, 256), (3, 7, 5, 256, 128), (9, 6, 6, 512, 256)])
 def test_binary_conv_backward_gemms(native_lib, B, H, W, Cin, Cout):
     from zookeeper_b200 import native as zn
 
