@@ -19,6 +19,7 @@ Parameters, gradients and Adam moments live in flat f32 arenas: [all kernels | a
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -121,6 +122,9 @@ class BinaryNetEngine:
         self._main = torch.cuda.Stream(device=self.device, priority=hi_pri)
         self._side = torch.cuda.Stream(device=self.device, priority=lo_pri)
         self._side_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
+        self._wgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
+        self._dgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
+        self.serialize_gemms = os.environ.get("ZKB_SERIALIZE_GEMMS", "0") == "1"
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
@@ -485,6 +489,7 @@ class BinaryNetEngine:
         B = self.B
         n = len(self.L)
         main = torch.cuda.current_stream(self.device)
+        pending_wgrad = None
         for i in range(n - 1, -1, -1):
             L, l = self.L[i], self.L[i].spec
             self._tag = f"bwd{i}"
@@ -518,13 +523,24 @@ class BinaryNetEngine:
                 ev = self._side_events[i]
                 ev.record(main)          # dy_i is complete (and the gradient arena was zeroed) here
                 side.wait_event(ev)
+                if self.serialize_gemms and pending_wgrad is not None:
+                    # two GEMMs only time-slice the tensor pipe: let the previous layer's wgrad
+                    # finish before this dgrad starts, so that wgrad overlaps HBM-bound kernels only
+                    main.wait_event(pending_wgrad)
             if l.kind == "conv":
                 ih, iw = L.in_hw
                 # dgrad first: it is on the critical path (the next BatchNorm backward needs it)
                 self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                            B, ih, iw, l.cin, l.cout, l.ksize)
+                if side is not None and self.serialize_gemms:
+                    ev2 = self._dgrad_events[i]
+                    ev2.record(main)     # ... and start this layer's wgrad only after its dgrad
+                    side.wait_event(ev2)
                 self._call("zkb_bconv2d_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
                            B, ih, iw, l.cin, l.cout, l.ksize, on=side)
+                if side is not None:
+                    pending_wgrad = self._wgrad_events[i]
+                    pending_wgrad.record(side)
             else:
                 self._call("zkb_bdense_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                            B, l.cin, L.cp)
