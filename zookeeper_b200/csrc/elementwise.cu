@@ -231,26 +231,27 @@ struct Vec16<int16_t> {
 template <int VEC>
 __device__ __forceinline__ void block_channel_reduce(const double (&a0)[VEC], const double (&a1)[VEC],
                                                      int tpr, int C, double* acc0, double* acc1) {
-  extern __shared__ double s_red[];  // [2][blockDim.x * VEC]
+  // 4 KB of static shared memory, one vector slot at a time: small enough for these blocks to be
+  // co-resident with a GEMM CTA (which leaves ~30 KB of the SM's shared memory free) when the
+  // engine overlaps them with a wgrad kernel.
+  __shared__ double s_part[2][256];
   const int lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr;
-  const int rl = threadIdx.x / tpr;
-  double* s0 = s_red;
-  double* s1 = s_red + static_cast<size_t>(blockDim.x) * VEC;
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
-    s0[(rl * tpr + cl) * VEC + j] = a0[j];
-    s1[(rl * tpr + cl) * VEC + j] = a1[j];
-  }
-  __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    double t0 = 0.0, t1 = 0.0;
-    for (int r = 0; r < lanes; ++r) {
-      t0 += s0[r * tpr * VEC + c];
-      t1 += s1[r * tpr * VEC + c];
+    s_part[0][threadIdx.x] = a0[j];
+    s_part[1][threadIdx.x] = a1[j];
+    __syncthreads();
+    if (threadIdx.x < tpr) {   // thread cl sums its channel (cl*VEC + j) over the row lanes
+      double t0 = 0.0, t1 = 0.0;
+      for (int r = 0; r < lanes; ++r) {
+        t0 += s_part[0][r * tpr + cl];
+        t1 += s_part[1][r * tpr + cl];
+      }
+      atomicAdd(acc0 + cl * VEC + j, t0);
+      atomicAdd(acc1 + cl * VEC + j, t1);
     }
-    atomicAdd(acc0 + c, t0);
-    atomicAdd(acc1 + c, t1);
+    __syncthreads();
   }
 }
 
@@ -965,7 +966,7 @@ ZKB_API int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, dou
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / vec);
   const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
-  const size_t smem = 2 * 256 * vec * sizeof(double);
+  const size_t smem = 0;
   if (x_is_i16)
     bn_stats_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
         static_cast<const int16_t*>(x), rows, C, sum, sumsq);
@@ -1021,7 +1022,7 @@ ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_
   const long long rows = static_cast<long long>(B) * (H / 2) * (W / 2);
   const int lanes = 256 / (C / 8);
   const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, reduce_waves());
-  const size_t smem = 2 * 256 * 8 * sizeof(double);
+  const size_t smem = 0;
   maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);
   ZKB_LAUNCH_CHECK("maxpool2_i16_kernel");
@@ -1049,7 +1050,7 @@ ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long 
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / 4);
   const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
-  const size_t smem = 2 * 256 * 4 * sizeof(double);
+  const size_t smem = 0;
   if (x_is_i16)
     bn_bwd_reduce_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
         g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, ste, sum_da, sum_dax);
@@ -1217,7 +1218,7 @@ ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows
   ZKB_CUDA(cudaMemsetAsync(sc->sumsq, 0, sizeof(double) * C, st));
   const int lanes = 256 / (C / vec);
   const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
-  const size_t smem = 2 * 256 * vec * sizeof(double);
+  const size_t smem = 0;
   const int grid_a = grid_for(rows * (C / vec), 256, 16);
   if (x_is_i16) {
     bn_stats_kernel<int16_t><<<grid_s, 256, smem, st>>>(static_cast<const int16_t*>(x), rows, C,
@@ -1357,10 +1358,10 @@ struct FirstConv {
   }
 };
 
-// dynamic smem: [2 * 256 * 4 doubles for block_channel_reduce][K * Cout floats of sign(W)]
+// dynamic smem: [K * Cout floats of sign(W)] (also reused to combine the wgrad pixel lanes)
 __device__ __forceinline__ float* first_conv_weights_smem() {
-  extern __shared__ double s_red[];
-  return reinterpret_cast<float*>(s_red + 2 * 256 * 4);
+  extern __shared__ double s_dyn[];
+  return reinterpret_cast<float*>(s_dyn);
 }
 
 template <int KS, int CIN>
@@ -1581,7 +1582,7 @@ static int first_conv_check(const char* who, const void* x, const void* wq, int 
 static size_t first_conv_smem(int K, int Cout) {
   const size_t w = static_cast<size_t>(K) * Cout * sizeof(float);
   const size_t lanes_acc = static_cast<size_t>(256 / (Cout / 4)) * Cout * sizeof(float);
-  return 2 * 256 * 4 * sizeof(double) + (w > lanes_acc ? w : lanes_acc);
+  return w > lanes_acc ? w : lanes_acc;
 }
 
 static int first_conv_grid(int B, int H, int W, int Cout) {
