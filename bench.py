@@ -174,6 +174,10 @@ def algorithmic_work(eng, name, tag):
         M, N, K = B * oh * ow, l.cout, l.ksize * l.ksize * l.cin
     else:
         M, N, K = B, l.cout, l.cin
+    if name == "zkb_bconv2d_dgrad_first_bwd":
+        # the dgrad GEMM plus the first layer's recomputed conv / BatchNorm-backward sums in its
+        # epilogue (about 60 flop per output element: 9-tap conv, 2 + 18 accumulating FMAs)
+        return ("flop", 2.0 * M * N * K + 60.0 * B * L.in_hw[0] * L.in_hw[1] * l.cin)
     if name in ("zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
                 "zkb_bconv2d_wgrad", "zkb_bdense_wgrad"):
         return ("flop", 2.0 * M * N * K)  # split terms are implementation overhead, not counted

@@ -111,6 +111,34 @@ int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_ic_k,
                       int NB, int H, int W, int Cin, int Cout, int ksize, void* stream);
 int zkb_bdense_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_k_n, void* dx_f32,
                      int rows, int K, int N, void* stream);
+/* The second conv's dgrad with the WHOLE backward of the first layer in its epilogue: the gradient
+ * w.r.t. the first sign map ([NB,H,W,128] f32) is consumed from tensor memory and never stored.
+ * Per output channel the epilogue recomputes the first conv (3x3 'valid', one input channel, from
+ * x0 [NB,H0,W0] with H0 = H+2, W0 = W+2 and sign(W0) wq0_k_co [9][128]), BatchNorm (mean0, rstd0,
+ * beta0) and the ste_sign mask, and adds into acc (float64 [11][128], zeroed by the caller):
+ *   acc[0][c] = sum da     acc[1][c] = sum da * xhat     acc[2+k][c] = S1 = sum x_k * da   (9 taps k)
+ * zkb_conv_first_gram adds the Gram matrix of the input taps over all output pixels into gram
+ * (float64: G[9][9] = sum x_k x_k', then S2[9] = sum x_k; zeroed by the caller) -- the part of the
+ * first layer that does not depend on the gradient.  zkb_conv_first_stats_from_gram adds the conv
+ * output's per-channel sum / sum of squares (what zkb_bn_finalize consumes) computed from it, and
+ * zkb_conv_first_bwd_finalize writes dbeta0 = dbeta_scale * sum da and ADDS the kernel gradient
+ *   dW0[k][c] = rstd_c * (S1 - mean(da) * S2[k] - mean(da*xhat) * S3),
+ *   S3 = sum x_k * xhat_c = rstd_c * (sum_k' w_k'c G[k][k'] - mean_c * S2[k])
+ * into dw0_k_co; count is the number of pixels the two means run over (all replicas' under
+ * synchronised BatchNorm, after an all-reduce of acc[0..1][*]).  Cin == 128, ksize == 3.
+ * Replaces: TF autodiff of Conv2D -> BatchNormalization -> ste_sign input quantizer -> QuantConv2D
+ * (examples/larq_experiment.py:62-78 under model.fit, :147-153). */
+int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, int NB,
+                                int H, int W, int Cin, int Cout, int ksize, const float* x0, int H0,
+                                int W0, const float* wq0_k_co, const float* mean0, const float* rstd0,
+                                const float* beta0, double* acc, void* stream);
+int zkb_conv_first_gram(const float* x0, int NB, int H0, int W0, double* gram, void* stream);
+int zkb_conv_first_stats_from_gram(const double* gram, const float* wq0_k_co, int Cout, double* sum,
+                                   double* sumsq, void* stream);
+int zkb_conv_first_bwd_finalize(const double* acc, const double* gram, const float* wq0_k_co,
+                                const float* mean0, const float* rstd0, double count,
+                                double dbeta_scale, float* dbeta0, float* dw0_k_co, int Cout,
+                                void* stream);
 /* Backward w.r.t. the latent kernel: dw f32 in HWIO / [K][ldw], ACCUMULATED into (zero it first;
  * partial tiles are combined with float atomics).  n_out <= N columns are written. */
 int zkb_bconv2d_wgrad(const void* act_pm1, const void* dy_hi, const void* dy_lo, float* dw_hwio,

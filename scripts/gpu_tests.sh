@@ -1,0 +1,7 @@
+#!/bin/bash
+# GPU parity tests + smoke + overlapped-step timeline.
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -30 | tee gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee gpurun_out/smoke.log
+timeout 300 python scripts/timeline.py > gpurun_out/timeline.txt 2>&1; tail -30 gpurun_out/timeline.txt

@@ -213,6 +213,36 @@ def test_dense_backward_gemms_and_padded_head(native_lib):
         assert ((dw.double() - ref_dw).norm() / ref_dw.norm()).item() < 1e-5
 
 
+@pytest.mark.parametrize("B,H,W", [(3, 28, 28), (2, 5, 40), (64, 28, 28)])
+def test_first_conv_gram_gives_the_batch_statistics(native_lib, B, H, W):
+    """zkb_conv_first_gram + zkb_conv_first_stats_from_gram against the direct sums of the conv
+    output (float64), and against zkb_conv_first_bn_stats (the kernel they stand in for)."""
+    from zookeeper_b200 import native as zn
+
+    rng = np.random.default_rng(B)
+    x = torch.tensor(rng.uniform(-1, 1, (B, H, W, 1)).astype(np.float32)).cuda()
+    wq = torch.tensor(np.where(rng.standard_normal((9, 128)) >= 0, 1.0, -1.0).astype(np.float32)).cuda()
+    gram = torch.zeros(90, dtype=torch.float64, device="cuda")
+    zn.call("zkb_conv_first_gram", zn.ptr(x), B, H, W, zn.ptr(gram), 0)
+    taps = torch.stack([x[:, kh:kh + H - 2, kw:kw + W - 2, 0].double().reshape(-1)
+                        for kh in range(3) for kw in range(3)])                 # [9, pixels]
+    # (the kernel sums up to 32 products per thread in float before going to float64)
+    tol = 2e-8 * taps.shape[1] + 1e-6
+    np.testing.assert_allclose(gram[:81].reshape(9, 9).cpu().numpy(), (taps @ taps.T).cpu().numpy(), rtol=0, atol=tol)
+    np.testing.assert_allclose(gram[81:].cpu().numpy(), taps.sum(1).cpu().numpy(), rtol=0, atol=tol)
+
+    s1, q1, s2, q2 = (torch.zeros(128, dtype=torch.float64, device="cuda") for _ in range(4))
+    zn.call("zkb_conv_first_stats_from_gram", zn.ptr(gram), zn.ptr(wq), 128, zn.ptr(s1), zn.ptr(q1), 0)
+    zn.call("zkb_conv_first_bn_stats", zn.ptr(x), zn.ptr(wq), B, H, W, 1, 128, 3, zn.ptr(s2), zn.ptr(q2), 0)
+    y = taps.T @ wq.double()                                                     # [pixels, 128]
+    torch.cuda.synchronize()
+    n = y.shape[0]
+    np.testing.assert_allclose(s1.cpu().numpy(), y.sum(0).cpu().numpy(), rtol=0, atol=1e-6 * n)
+    np.testing.assert_allclose(q1.cpu().numpy(), (y * y).sum(0).cpu().numpy(), rtol=1e-6)
+    np.testing.assert_allclose(s1.cpu().numpy(), s2.cpu().numpy(), rtol=1e-5, atol=1e-5 * n)
+    np.testing.assert_allclose(q1.cpu().numpy(), q2.cpu().numpy(), rtol=1e-5)
+
+
 def test_full_size_train_step_properties(native_lib):
     """configs[1] (batch 4096): too large for the CPU oracle, so check properties that do not depend
     on size: integer layer outputs respect |y| <= K and the +-1 parity, pooled = max of its window,

@@ -103,6 +103,36 @@ def test_train_step_matches_oracle(native_lib, B):
             assert np.median(err) < 1e-4 and (err > 1e-2).mean() < 0.05, f"beta step {k}"
 
 
+@pytest.mark.parametrize("B", [5, 64])
+def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, monkeypatch):
+    """zkb_bconv2d_dgrad_first_bwd (+ finalize) against zkb_bconv2d_dgrad -> conv_first_bwd_reduce ->
+    bn_bwd_finalize -> conv_first_bwd_wgrad on the same state: all gradients equal up to float
+    summation order."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    params = O.glorot_uniform_params(O.binarynet_layers((28, 28, 1), 128, 1024, 10), 0)
+    rng = np.random.default_rng(7)
+    img = torch.as_tensor(rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)).cuda()
+    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
+    grads = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("ZKB_FUSE_FIRST_BWD", fused)
+        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+        assert eng.fuse_first_backward == (fused == "1")
+        assert (eng.L[0].ds is None) == (fused == "1")
+        eng.load_params(params)
+        eng.train_step(img, lab, None, pad_size=32, seed=3, apply_update=False)
+        torch.cuda.synchronize()
+        grads.append(eng.get_grads())
+    a, b = grads
+    for k in a:
+        if k in ("kernel0", "beta0"):
+            assert _rel(a[k], b[k]) < 2e-6, f"{k}: {_rel(a[k], b[k]):.3g}"
+        else:       # same kernels on both sides (float atomics: summation order may differ)
+            assert _rel(a[k], b[k]) < 1e-6, k
+
+
 def test_second_step_from_engine_state(native_lib):
     """Step 2 (Adam t = 2, non-zero moments, re-prepared sign weights, in-kernel augmentation RNG).
 

@@ -1565,6 +1565,95 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
   }
 }
 
+// Gram matrix of the 3x3 input taps over all output pixels of a 'valid' one-channel conv:
+// G[k][k'] = sum_p x_k(p) x_k'(p), S2[k] = sum_p x_k(p)  (gram = G[81] then S2[9], float64,
+// accumulated into).  Everything about the first layer that is quadratic in the input and does not
+// involve the incoming gradient follows from these 90 numbers: per-channel sum / sum of squares of
+// the conv output (y_c = sum_k w_kc x_k) and sum_p x_k(p) y_c(p).
+__global__ void __launch_bounds__(256)
+conv_first_gram_kernel(const float* __restrict__ x, int B, int H, int W, double* __restrict__ gram) {
+  const int OH = H - 2, OW = W - 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned n_rows = static_cast<unsigned>(B) * OH;
+  float g[45], s[9];
+#pragma unroll
+  for (int i = 0; i < 45; ++i) g[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) s[i] = 0.f;
+  double gd[45], sd[9];
+#pragma unroll
+  for (int i = 0; i < 45; ++i) gd[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) sd[i] = 0.0;
+  int n = 0;
+  for (unsigned row = blockIdx.x * 8 + warp; row < n_rows; row += gridDim.x * 8) {
+    const unsigned b = row / OH, oh = row - b * OH;
+    const float* base = x + (static_cast<size_t>(b) * H + oh) * W;
+    for (int ow = lane; ow < OW; ow += 32) {
+      float xv[9];
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) xv[kh * 3 + kw] = __ldg(base + kh * W + ow + kw);
+      int t = 0;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        s[k] += xv[k];
+#pragma unroll
+        for (int k2 = k; k2 < 9; ++k2) { g[t] = fmaf(xv[k], xv[k2], g[t]); ++t; }
+      }
+      if (++n == 32) {   // bound the float partial sums
+#pragma unroll
+        for (int i = 0; i < 45; ++i) { gd[i] += g[i]; g[i] = 0.f; }
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { sd[i] += s[i]; s[i] = 0.f; }
+        n = 0;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 45; ++i) gd[i] += g[i];
+#pragma unroll
+  for (int i = 0; i < 9; ++i) sd[i] += s[i];
+  __shared__ double red[8][54];
+#pragma unroll
+  for (int i = 0; i < 54; ++i) {
+    double v = i < 45 ? gd[i] : sd[i - 45];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 54) {
+    double v = 0.0;
+    for (int w = 0; w < 8; ++w) v += red[w][threadIdx.x];
+    const int i = threadIdx.x;
+    if (i >= 45) {
+      atomicAdd(gram + 81 + (i - 45), v);
+    } else {
+      int k = 0, rem = i;            // upper-triangle index -> (k, k2)
+      while (rem >= 9 - k) { rem -= 9 - k; ++k; }
+      const int k2 = k + rem;
+      atomicAdd(gram + k * 9 + k2, v);
+      if (k2 != k) atomicAdd(gram + k2 * 9 + k, v);
+    }
+  }
+}
+
+// sum_c = sum_k w_kc S2[k];  sumsq_c = sum_kk' w_kc w_k'c G[k][k']   (accumulated into sum / sumsq)
+__global__ void conv_first_stats_from_gram_kernel(const double* __restrict__ gram,
+                                                  const float* __restrict__ wq, int Cout,
+                                                  double* __restrict__ sum, double* __restrict__ sumsq) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= Cout) return;
+  double w[9], a = 0.0, q = 0.0;
+  for (int k = 0; k < 9; ++k) { w[k] = wq[k * Cout + c]; a += w[k] * gram[81 + k]; }
+  for (int k = 0; k < 9; ++k)
+    for (int k2 = 0; k2 < 9; ++k2) q += w[k] * w[k2] * gram[k * 9 + k2];
+  sum[c] += a;
+  sumsq[c] += q;
+}
+
 }  // namespace zkb
 
 static int first_conv_check(const char* who, const void* x, const void* wq, int B, int H, int W,
@@ -1616,6 +1705,30 @@ ZKB_API int zkb_conv_first_bn_stats(const float* x, const float* wq_k_co, int B,
   ZKB_REQUIRE(sum && sumsq, "conv_first_bn_stats: null accumulator");
   if (B == 0) return ZKB_OK;
   ZKB_FIRST_DISPATCH(conv_first_bn_stats_kernel, x, wq_k_co, B, H, W, Cout, sum, sumsq);
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_gram(const float* x, int B, int H, int W, double* gram, void* stream) {
+  ZKB_REQUIRE(x && gram, "conv_first_gram: null pointer");
+  ZKB_REQUIRE(B >= 0 && H >= 3 && W >= 3, "conv_first_gram: bad shape");
+  ZKB_REQUIRE(static_cast<long long>(B) * H * W < (1ll << 31), "conv_first_gram: B*H*W must stay below 2^31");
+  if (B == 0) return ZKB_OK;
+  const long long rows = static_cast<long long>(B) * (H - 2);
+  long long grid = (rows + 31) / 32;          // about 4 rows per warp
+  const long long cap = static_cast<long long>(zkb_sm_count()) * 8;
+  if (grid > cap) grid = cap;
+  conv_first_gram_kernel<<<static_cast<int>(grid), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, B, H, W, gram);
+  ZKB_LAUNCH_CHECK("conv_first_gram_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_stats_from_gram(const double* gram, const float* wq_k_co, int Cout, double* sum,
+                                           double* sumsq, void* stream) {
+  ZKB_REQUIRE(gram && wq_k_co && sum && sumsq, "conv_first_stats_from_gram: null pointer");
+  ZKB_REQUIRE(Cout > 0, "conv_first_stats_from_gram: Cout must be positive");
+  conv_first_stats_from_gram_kernel<<<(Cout + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      gram, wq_k_co, Cout, sum, sumsq);
+  ZKB_LAUNCH_CHECK("conv_first_stats_from_gram_kernel");
   return ZKB_OK;
 }
 

@@ -42,6 +42,17 @@ struct KGemmParams {
   int out_kind;  // 0: f32, 1: int16 (exact integers expected)
   int is_i8;     // operands are signed int8 (+-1 / 0), accumulators int32 (kind::i8)
   int dbg;       // measurement switches (scripts/bench_gemm.py): 1 = no MMA issue, 2 = no TMA loads
+  // Fused first-layer backward (swap mode, 128 output channels, one input channel, 3x3): the
+  // epilogue consumes D^T = ds0 straight from tensor memory -- BatchNorm-backward sums and the
+  // weight-gradient sums of the first layer -- and stores nothing.
+  int l0_fused;
+  int l0_H, l0_W;            // image size (the dgrad output is the (H-2) x (W-2) map)
+  const float* l0_x;         // preprocessed images [B, H, W]
+  const float* l0_wq;        // sign(W0) [9][128]
+  const float* l0_mean;
+  const float* l0_rstd;
+  const float* l0_beta;
+  double* l0_acc;            // [11][128]: sum da, sum da*xhat, S1[k] = sum x_k*da (9 taps)
   int swap;      // 1: operand roles swapped -- the MMA computes D^T[128 out channels, 256 pixels]
                  //    so that narrow (128-column) layers still issue 256-wide MMAs; f32 output only
   void* out;
@@ -90,7 +101,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     tma_prefetch_desc(&tmA0);
     if (p.a_terms == 2) tma_prefetch_desc(&tmA1);
     tma_prefetch_desc(&tmB);
-    tma_prefetch_desc(&tmOut);
+    if (!p.l0_fused) tma_prefetch_desc(&tmOut);
   }
   if (warp == 1) tmem_alloc_512(smem_u32(&ctl->tmem_base));
   tc_fence_before();
@@ -270,6 +281,17 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
                                         1024 + static_cast<size_t>(ew) * 4096);
     const uint32_t my_row = stage_box + static_cast<uint32_t>(lane) * 128u;
     const uint32_t sw = static_cast<uint32_t>(lane & 7);
+    // fused first-layer backward: this thread owns output channel l0_c for the whole kernel
+    const int l0_c = q * 32 + lane;
+    float l0_w[9], l0_mu = 0.f, l0_rs = 0.f, l0_be = 0.f;
+    double l0_d[11];
+    if (p.l0_fused) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) l0_w[k] = p.l0_wq[k * 128 + l0_c];
+#pragma unroll
+      for (int i = 0; i < 11; ++i) l0_d[i] = 0.0;
+      l0_mu = p.l0_mean[l0_c]; l0_rs = p.l0_rstd[l0_c]; l0_be = p.l0_beta[l0_c];
+    }
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -291,6 +313,57 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
           uint32_t r[32];
           tmem_ld_32x32(tbase + static_cast<uint32_t>(u * 32), r);
           tmem_ld_wait();
+          if (p.l0_fused) {
+            // r[j] = gradient w.r.t. sign(a0) at pixel pix0 + j, channel l0_c.  Recompute the
+            // first conv at that pixel (9 taps, same FMA order as the forward kernels), apply the
+            // ste mask and accumulate everything the first layer's backward needs.
+            float f[11];
+#pragma unroll
+            for (int i = 0; i < 11; ++i) f[i] = 0.f;
+            const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
+            unsigned b = static_cast<unsigned>(pix0) / hw;
+            const unsigned rem = static_cast<unsigned>(pix0) - b * hw;
+            unsigned oh = rem / static_cast<unsigned>(p.OW);
+            unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
+            const float* base = p.l0_x + (static_cast<size_t>(b) * p.l0_H + oh) * p.l0_W + ow;
+            float win[3][3];   // sliding 3x3 window along the image row: 3 new taps per pixel
+            bool fresh = true;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (pix0 + j < p.M) {
+                if (fresh) {
+#pragma unroll
+                  for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+                    for (int kw = 0; kw < 2; ++kw) win[kh][kw] = __ldg(base + kh * p.l0_W + kw);
+                  fresh = false;
+                }
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh) win[kh][2] = __ldg(base + kh * p.l0_W + 2);
+                float y = 0.f;
+#pragma unroll
+                for (int k = 0; k < 9; ++k) y = fmaf(win[k / 3][k % 3], l0_w[k], y);
+                const float xh = (y - l0_mu) * l0_rs;
+                const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
+                f[0] += da;
+                f[1] = fmaf(da, xh, f[1]);
+#pragma unroll
+                for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(win[k / 3][k % 3], da, f[2 + k]);
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh) { win[kh][0] = win[kh][1]; win[kh][1] = win[kh][2]; }
+              }
+              ++base;
+              if (++ow == static_cast<unsigned>(p.OW)) {   // next image row (or next image)
+                ow = 0;
+                base += 2;
+                fresh = true;
+                if (++oh == static_cast<unsigned>(p.OH)) { oh = 0; base += 2 * p.l0_W; }
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
+            continue;
+          }
           if (lane == 0) tma_store_wait_read_all();
           __syncwarp();
           const uint32_t lane_chunk = static_cast<uint32_t>(lane >> 2);
@@ -367,12 +440,42 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
       as ^= 1;
       if (as == 0) aphase ^= 1u;
     }
+    if (p.l0_fused) {
+#pragma unroll
+      for (int i = 0; i < 11; ++i) atomicAdd(p.l0_acc + i * 128 + l0_c, l0_d[i]);
+    }
     if (lane == 0) tma_store_wait_all();
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc_512(tmem_base);
+}
+
+// Per channel c and tap k: dbeta = sum da; dW0[k][c] = rstd_c * (S1 - mean(da) * S2[k] -
+// mean(da*xhat) * S3[k][c]) from the sums the fused epilogue left.  S2[k] = sum x_k and
+// S3[k][c] = sum x_k * xhat_c = rstd_c * (sum_k' w_k'c G[k][k'] - mean_c S2[k]) do not depend on the
+// gradient: they come from the Gram matrix of the input taps (gram = G[9][9] then S2[9]).
+__global__ void conv_first_fused_finalize_kernel(const double* __restrict__ acc,
+                                                 const double* __restrict__ gram,
+                                                 const float* __restrict__ wq,
+                                                 const float* __restrict__ mean,
+                                                 const float* __restrict__ rstd, double count,
+                                                 double dbeta_scale, float* __restrict__ dbeta,
+                                                 float* __restrict__ dw) {
+  const int c = threadIdx.x;   // 128 threads
+  const double mean_da = acc[c] / count;
+  const double mean_dax = acc[128 + c] / count;
+  const double rs = rstd[c], mu = mean[c];
+  dbeta[c] = static_cast<float>(acc[c] * dbeta_scale);
+  for (int k = 0; k < 9; ++k) {
+    double wg = 0.0;
+    for (int k2 = 0; k2 < 9; ++k2) wg += static_cast<double>(wq[k2 * 128 + c]) * gram[k * 9 + k2];
+    const double s2 = gram[81 + k];
+    const double s3 = rs * (wg - mu * s2);
+    const double s1 = acc[(2 + k) * 128 + c];
+    dw[k * 128 + c] += static_cast<float>(rs * (s1 - mean_da * s2 - mean_dax * s3));
+  }
 }
 
 // --------------------------------------------------------------------------------------------
@@ -818,16 +921,22 @@ static int pick_block_n(int N) {
 
 // A_hi/A_lo: bf16.  im2col != 0: NHWC activation [NB,H,W,C], K = ksize*ksize*C, M = NB*H*W.
 // Bmat: bf16 [N][K] row-major.  out: f32 or int16 [M][ldo].
+struct FirstLayerFuse {   // see KGemmParams::l0_fused
+  const float *x, *wq, *mean, *rstd, *beta;
+  double* acc;
+  int H, W;
+};
+
 static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, void* out,
                         int out_kind, long long ldo, long long M, int N, int K, int im2col, int NB,
                         int H, int W, int C, int ksize, int pad, cudaStream_t stream,
-                        int elem_bytes = 2) {
+                        int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr) {
   const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
   const CUtensorMapDataType dt =
       elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   ZKB_REQUIRE(elem_bytes == 2 || (elem_bytes == 1 && !A_lo && out_kind == 1),
               "kgemm: int8 operands are for the single-term integer forward only");
-  ZKB_REQUIRE(A_hi && Bmat && out, "kgemm: null pointer");
+  ZKB_REQUIRE(A_hi && Bmat && (out || l0), "kgemm: null pointer");
   ZKB_REQUIRE(M > 0 && N > 0 && K > 0, "kgemm: empty problem M=%lld N=%d K=%d", M, N, K);
   ZKB_REQUIRE(K % kelems == 0, "kgemm: K=%d must be a multiple of %d", K, kelems);
   ZKB_REQUIRE(M < (1ll << 31) - 256, "kgemm: M=%lld too large", M);
@@ -836,6 +945,8 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   ZKB_REQUIRE((ldo * (out_kind == 0 ? 4 : 2)) % 16 == 0 &&
                   (reinterpret_cast<uintptr_t>(out) & 15) == 0,
               "kgemm: output rows must be 16-byte aligned");
+  ZKB_REQUIRE(!l0 || (out_kind == 0 && elem_bytes == 2 && N == 128 && im2col),
+              "kgemm: the fused first-layer backward needs a 128-channel f32 dgrad");
   KGemmParams p{};
   p.M = static_cast<int>(M);
   p.N = N;
@@ -850,6 +961,12 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   // MMAs are 256 wide (see KGemmParams::swap)
   p.swap = (out_kind == 0 && elem_bytes == 2 && N % 128 == 0 && N < 256) ? 1 : 0;
   if (const char* e = getenv("ZKB_KGEMM_SWAP")) p.swap = (atoi(e) && out_kind == 0 && elem_bytes == 2 && N % 128 == 0) ? 1 : 0;
+  if (l0) {
+    p.swap = 1;
+    p.l0_fused = 1;
+    p.l0_x = l0->x; p.l0_wq = l0->wq; p.l0_mean = l0->mean; p.l0_rstd = l0->rstd; p.l0_beta = l0->beta;
+    p.l0_acc = l0->acc; p.l0_H = l0->H; p.l0_W = l0->W;
+  }
   if (p.swap) {
     p.block_n = 256;
     p.stage_bytes = kATileBytes + p.a_terms * 2 * kATileBytes;
@@ -915,8 +1032,10 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   if (rc) return rc;
 
   // output through TMA stores: boxes of 128 bytes x 32 rows
-  CUtensorMap tmOut;
-  if (out_kind == 0)
+  CUtensorMap tmOut{};
+  if (l0)
+    rc = ZKB_OK;            // nothing is stored: the epilogue reduces D in registers
+  else if (out_kind == 0)
     rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, N, M,
                            static_cast<uint64_t>(ldo) * 4, 32, 32);
   else
@@ -1081,6 +1200,35 @@ ZKB_API int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* 
   return launch_kgemm(dy_hi, dy_lo, wq_ic_k, dx_f32, 0, Cin, static_cast<long long>(NB) * H * W, Cin,
                       ksize * ksize * Cout, 1, NB, H, W, Cout, ksize, ksize / 2,
                       static_cast<cudaStream_t>(stream));
+}
+
+ZKB_API int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, const void* wq_ic_k,
+                                        int NB, int H, int W, int Cin, int Cout, int ksize,
+                                        const float* x0, int H0, int W0, const float* wq0_k_co,
+                                        const float* mean0, const float* rstd0, const float* beta0,
+                                        double* acc, void* stream) {
+  ZKB_REQUIRE(ksize == 3 && Cin == 128, "bconv2d_dgrad_first_bwd: built for 3x3 kernels into 128 channels");
+  ZKB_REQUIRE(H0 == H + 2 && W0 == W + 2,
+              "bconv2d_dgrad_first_bwd: first layer must be a 'valid' 3x3 conv (image %dx%d, map %dx%d)",
+              H0, W0, H, W);
+  ZKB_REQUIRE(x0 && wq0_k_co && mean0 && rstd0 && beta0 && acc, "bconv2d_dgrad_first_bwd: null pointer");
+  FirstLayerFuse l0{x0, wq0_k_co, mean0, rstd0, beta0, acc, H0, W0};
+  return launch_kgemm(dy_hi, dy_lo, wq_ic_k, nullptr, 0, Cin, static_cast<long long>(NB) * H * W, Cin,
+                      ksize * ksize * Cout, 1, NB, H, W, Cout, ksize, ksize / 2,
+                      static_cast<cudaStream_t>(stream), 2, &l0);
+}
+
+ZKB_API int zkb_conv_first_bwd_finalize(const double* acc, const double* gram, const float* wq0_k_co,
+                                        const float* mean0, const float* rstd0, double count,
+                                        double dbeta_scale, float* dbeta0, float* dw0_k_co, int Cout,
+                                        void* stream) {
+  ZKB_REQUIRE(acc && gram && wq0_k_co && mean0 && rstd0 && dbeta0 && dw0_k_co,
+              "conv_first_bwd_finalize: null pointer");
+  ZKB_REQUIRE(Cout == 128 && count > 0, "conv_first_bwd_finalize: Cout must be 128, count > 0");
+  conv_first_fused_finalize_kernel<<<1, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      acc, gram, wq0_k_co, mean0, rstd0, count, dbeta_scale, dbeta0, dw0_k_co);
+  ZKB_LAUNCH_CHECK("conv_first_fused_finalize_kernel");
+  return ZKB_OK;
 }
 
 ZKB_API int zkb_bdense_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_k_n, void* dx_f32,

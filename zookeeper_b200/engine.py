@@ -125,6 +125,9 @@ class BinaryNetEngine:
         self._wgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._dgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self.serialize_gemms = os.environ.get("ZKB_SERIALIZE_GEMMS", "0") == "1"
+        # first layer's backward inside layer 1's dgrad epilogue (ZKB_FUSE_FIRST_BWD=0: separate kernels)
+        self.fuse_first_backward = (os.environ.get("ZKB_FUSE_FIRST_BWD", "1") != "0"
+                                    and self._can_fuse_first_backward())
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
@@ -171,7 +174,11 @@ class BinaryNetEngine:
         self.moving_mean = torch.zeros(self.n_beta, dtype=f32, device=dev)
         self.moving_var = torch.ones(self.n_beta, dtype=f32, device=dev)
         # per-step accumulators (zeroed by one memset): fwd sums, bwd sums, loss, correct
-        self.acc = torch.zeros(4 * self.n_beta + 2, dtype=torch.float64, device=dev)
+        # (+ the fused first-layer path: 11 sums per channel from the dgrad epilogue, and the
+        # Gram matrix of the input taps G[9][9] + S2[9])
+        self.acc = torch.zeros(4 * self.n_beta + 2 + 11 * 128 + 90, dtype=torch.float64, device=dev)
+        self.l0_acc = self.acc[4 * self.n_beta + 2: 4 * self.n_beta + 2 + 11 * 128]
+        self.l0_gram = self.acc[4 * self.n_beta + 2 + 11 * 128:]
         self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
         self.stat = torch.zeros(4 * self.n_beta, dtype=f32, device=dev)  # mean, rstd, mean_da, mean_dax
         self.x0 = torch.zeros(B, H, W, C, dtype=f32, device=dev)
@@ -212,7 +219,9 @@ class BinaryNetEngine:
                 L.bn_rows = B * h * w
                 L.s = torch.zeros(B, h, w, L.cp, dtype=bf16, device=dev)
                 L.s8 = torch.zeros(B, h, w, L.cp, dtype=torch.int8, device=dev) if self.forward_int8 else None
-                L.ds = torch.zeros(B, h, w, L.cp, dtype=f32, device=dev)
+                # with the fused first-layer backward the gradient of the first sign map lives only
+                # in tensor memory (1.4 GB of HBM at batch 4096 never allocated)
+                L.ds = None if (i == 0 and self.fuse_first_backward) else torch.zeros(B, h, w, L.cp, dtype=f32, device=dev)
                 if i == 0:
                     L.wq = torch.zeros(l.ksize * l.ksize * l.cin, l.cout, dtype=f32, device=dev)
                 else:
@@ -441,7 +450,14 @@ class BinaryNetEngine:
         H, W, C = self.input_shape
         geom = (self.B, H, W, C, l.cout, l.ksize)
         if training:
-            self._call("zkb_conv_first_bn_stats", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(L.sum), zn.ptr(L.sumsq))
+            if self.fuse_first_backward:
+                # batch statistics of the first conv from the Gram matrix of its 9 input taps (the
+                # backward needs the same 90 numbers): one pass over the 12.8 MB of images
+                self._call("zkb_conv_first_gram", zn.ptr(self.x0), self.B, H, W, self.l0_gram.data_ptr())
+                self._call("zkb_conv_first_stats_from_gram", self.l0_gram.data_ptr(), zn.ptr(L.wq), l.cout,
+                           zn.ptr(L.sum), zn.ptr(L.sumsq))
+            else:
+                self._call("zkb_conv_first_bn_stats", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(L.sum), zn.ptr(L.sumsq))
             count = float(L.bn_rows)
             if self.sync_bn:
                 self._pending_bn_sync(L)
@@ -453,6 +469,34 @@ class BinaryNetEngine:
             mean, rstd = L.mm, L.eval_rstd
         self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
                    zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
+
+    def _can_fuse_first_backward(self) -> bool:
+        """zkb_bconv2d_dgrad_first_bwd is built for: 3x3 'valid' conv of one input channel into 128
+        channels (no pooling), followed by a 3x3 'same' conv -- the MNIST topology of the example."""
+        if len(self.layers) < 2:
+            return False
+        a, b = self.layers[0], self.layers[1]
+        return (a.kind == "conv" and a.ksize == 3 and a.padding == "valid" and a.cin == 1 and a.cout == 128
+                and not a.pool and b.kind == "conv" and b.ksize == 3 and b.padding == "same")
+
+    def _fused_first_layer_backward(self, L1):
+        """Layer 1's dgrad GEMM whose epilogue is the whole backward of layer 0 (BatchNorm sums,
+        ste mask, weight-gradient sums), then a one-block finalize."""
+        L0 = self.L[0]
+        H, W, _ = self.input_shape
+        ih, iw = L1.in_hw
+        l = L1.spec
+        self._call("zkb_bconv2d_dgrad_first_bwd", zn.ptr(L1.dy_hi), zn.ptr(L1.dy_lo), zn.ptr(L1.w_dgrad),
+                   self.B, ih, iw, l.cin, l.cout, l.ksize, zn.ptr(self.x0), H, W, zn.ptr(L0.wq),
+                   zn.ptr(L0.mean), zn.ptr(L0.rstd), zn.ptr(L0.beta), self.l0_acc.data_ptr())
+        count = float(L0.bn_rows)
+        if self.sync_bn:
+            self._all_reduce(self.l0_acc[:256])      # sum da, sum da*xhat; the tap sums stay local
+            count *= self.world
+        self._tag = "bwd0"
+        self._call("zkb_conv_first_bwd_finalize", self.l0_acc.data_ptr(), self.l0_gram.data_ptr(), zn.ptr(L0.wq),
+                   zn.ptr(L0.mean), zn.ptr(L0.rstd), count, (1.0 / self.world) if self.sync_bn else 1.0,
+                   zn.ptr(L0.dbeta), zn.ptr(L0.dkernel), L0.spec.cout)
 
     def _first_layer_backward(self, L):
         l = L.spec
@@ -494,7 +538,8 @@ class BinaryNetEngine:
             L, l = self.L[i], self.L[i].spec
             self._tag = f"bwd{i}"
             if i == 0:
-                self._first_layer_backward(L)
+                if not self.fuse_first_backward:
+                    self._first_layer_backward(L)
                 continue
             last = i == n - 1
             x = L.p if (l.kind == "conv" and l.pool) else L.y
@@ -530,8 +575,12 @@ class BinaryNetEngine:
             if l.kind == "conv":
                 ih, iw = L.in_hw
                 # dgrad first: it is on the critical path (the next BatchNorm backward needs it)
-                self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
-                           B, ih, iw, l.cin, l.cout, l.ksize)
+                if i == 1 and self.fuse_first_backward:
+                    self._fused_first_layer_backward(L)
+                    self._tag = f"bwd{i}"
+                else:
+                    self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
+                               B, ih, iw, l.cin, l.cout, l.ksize)
                 if side is not None and self.serialize_gemms:
                     ev2 = self._dgrad_events[i]
                     ev2.record(main)     # ... and start this layer's wgrad only after its dgrad
