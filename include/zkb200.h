@@ -111,6 +111,16 @@ int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_ic_k,
                       int NB, int H, int W, int Cin, int Cout, int ksize, void* stream);
 int zkb_bdense_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_k_n, void* dx_f32,
                      int rows, int K, int N, void* stream);
+/* zkb_bconv2d_dgrad that also leaves the BatchNorm-backward sums of the layer below (what
+ * zkb_bn_bwd_reduce would compute from dx_f32 in a second pass): x_i16 [NB,H,W,Cin] is that layer's
+ * pre-BatchNorm integer map (after pooling, if it pools), mean/rstd/beta its statistics; per channel
+ * sum_da += sum of da, sum_dax += sum of da*xhat with da = dx masked by |xhat + beta| <= 1.  The
+ * epilogue reads each dx tile back from its shared-memory staging box column-wise, so the sums cost
+ * one int16 read of x instead of an f32 read of dx plus x.  Cin % 128 == 0. */
+int zkb_bconv2d_dgrad_bn(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, void* dx_f32,
+                         int NB, int H, int W, int Cin, int Cout, int ksize, const void* x_i16,
+                         const float* mean, const float* rstd, const float* beta, double* sum_da,
+                         double* sum_dax, void* stream);
 /* The second conv's dgrad with the WHOLE backward of the first layer in its epilogue: the gradient
  * w.r.t. the first sign map ([NB,H,W,128] f32) is consumed from tensor memory and never stored.
  * Per output channel the epilogue recomputes the first conv (3x3 'valid', one input channel, from

@@ -133,6 +133,33 @@ def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, monke
             assert _rel(a[k], b[k]) < 1e-6, k
 
 
+def test_bn_backward_sums_from_dgrad_epilogue_equal_the_reduction_kernel(native_lib, monkeypatch):
+    """zkb_bconv2d_dgrad_bn against zkb_bconv2d_dgrad + zkb_bn_bwd_reduce inside a full step."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    B = 48
+    params = O.glorot_uniform_params(O.binarynet_layers((28, 28, 1), 128, 1024, 10), 0)
+    rng = np.random.default_rng(11)
+    img = torch.as_tensor(rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)).cuda()
+    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
+    out = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("ZKB_FUSE_BN_BWD", fused)
+        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+        assert eng.fuse_bn_backward_sums == (fused == "1")
+        assert [eng._sums_come_from_dgrad(i) for i in range(9)] == [False] + [fused == "1"] * 4 + [False] * 4
+        eng.load_params(params)
+        eng.train_step(img, lab, None, pad_size=32, seed=3, apply_update=False)
+        torch.cuda.synchronize()
+        sums = torch.cat([torch.cat([L.sum_da, L.sum_dax]) for L in eng.L[1:5]]).cpu().numpy()
+        out.append((sums, eng.get_grads()))
+    (sa, ga), (sb, gb) = out
+    assert _rel(sa, sb) < 1e-5          # float partial sums in a different order
+    for k in ga:
+        assert _rel(ga[k], gb[k]) < 1e-5, k
+
+
 def test_second_step_from_engine_state(native_lib):
     """Step 2 (Adam t = 2, non-zero moments, re-prepared sign weights, in-kernel augmentation RNG).
 

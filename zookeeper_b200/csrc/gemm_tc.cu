@@ -53,6 +53,14 @@ struct KGemmParams {
   const float* l0_rstd;
   const float* l0_beta;
   double* l0_acc;            // [11][128]: sum da, sum da*xhat, S1[k] = sum x_k*da (9 taps)
+  // BatchNorm-backward sums of the layer BELOW, fused into the f32 dgrad epilogue (swap mode and
+  // CTA pairs): D[row][c] is the gradient w.r.t. that layer's sign output, bn_x its pre-BatchNorm
+  // int16 map of the same shape; per channel sum da and sum da*xhat (da = D masked by |a| <= 1)
+  // are added into bn_sum_da / bn_sum_dax -- what bn_bwd_reduce_kernel computes from D in HBM.
+  int bn_fused;
+  const int16_t* bn_x;
+  const float *bn_mean, *bn_rstd, *bn_beta;
+  double *bn_sum_da, *bn_sum_dax;
   int swap;      // 1: operand roles swapped -- the MMA computes D^T[128 out channels, 256 pixels]
                  //    so that narrow (128-column) layers still issue 256-wide MMAs; f32 output only
   void* out;
@@ -72,6 +80,91 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
   uintptr_t a = reinterpret_cast<uintptr_t>(p);
   a = (a + 1023) & ~static_cast<uintptr_t>(1023);
   return reinterpret_cast<uint8_t*>(a);
+}
+
+// One epilogue unit of the fused first-layer backward: r[j] = gradient w.r.t. sign(a0) at pixel
+// pix0 + j of this thread's channel.  kGuard = false (every unit but the last of the problem) has
+// no per-pixel predicate, so the image loads of all 32 pixels can be scheduled ahead of their use.
+template <bool kGuard>
+__device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uint32_t (&r)[32], int pix0,
+                                                 const float (&l0_w)[9], float l0_mu, float l0_rs,
+                                                 float l0_be, double (&l0_d)[11]) {
+            float f[11];
+#pragma unroll
+            for (int i = 0; i < 11; ++i) f[i] = 0.f;
+            const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
+            unsigned b = static_cast<unsigned>(pix0) / hw;
+            const unsigned rem = static_cast<unsigned>(pix0) - b * hw;
+            unsigned oh = rem / static_cast<unsigned>(p.OW);
+            unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
+            const float* base = p.l0_x + (static_cast<size_t>(b) * p.l0_H + oh) * p.l0_W + ow;
+            float win[3][3];   // sliding 3x3 window along the image row: 3 new taps per pixel
+            bool fresh = true;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (!kGuard || pix0 + j < p.M) {
+                if (fresh) {
+#pragma unroll
+                  for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+                    for (int kw = 0; kw < 2; ++kw) win[kh][kw] = __ldg(base + kh * p.l0_W + kw);
+                  fresh = false;
+                }
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh) win[kh][2] = __ldg(base + kh * p.l0_W + 2);
+                float y = 0.f;
+#pragma unroll
+                for (int k = 0; k < 9; ++k) y = fmaf(win[k / 3][k % 3], l0_w[k], y);
+                const float xh = (y - l0_mu) * l0_rs;
+                const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
+                f[0] += da;
+                f[1] = fmaf(da, xh, f[1]);
+#pragma unroll
+                for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(win[k / 3][k % 3], da, f[2 + k]);
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh) { win[kh][0] = win[kh][1]; win[kh][1] = win[kh][2]; }
+              }
+              ++base;
+              if (++ow == static_cast<unsigned>(p.OW)) {   // next image row (or next image)
+                ow = 0;
+                base += 2;
+                fresh = true;
+                if (++oh == static_cast<unsigned>(p.OH)) { oh = 0; base += 2 * p.l0_W; }
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
+}
+
+// Column `lane` of the 32 x 32 f32 box a warp has just staged (row j at stage_box + 128 j, 16-byte
+// chunks XOR-swizzled by j & 7): the gradient of 32 consecutive rows at one channel.  Adds this
+// thread's share of the BatchNorm-backward sums (same arithmetic as bn_bwd_reduce_kernel).
+__device__ __forceinline__ void bn_sums_from_box(const KGemmParams& p, uint32_t stage_box, int row0,
+                                                 int ch, int lane, float mu, float rs, float be,
+                                                 double& acc_da, double& acc_dax) {
+  const uint32_t chunk = static_cast<uint32_t>(lane >> 2), byte = static_cast<uint32_t>(lane & 3) * 4u;
+  // Rows at or beyond M hold exact zeros in the box (TMA zero-fills the operand rows), so they add
+  // nothing; only their x address is clamped.  All 32 loads are issued before the first is used.
+  const int last = p.M - 1 - row0;
+  const int16_t* xcol = p.bn_x + static_cast<size_t>(row0) * p.ldo + ch;
+  int16_t xs[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) xs[j] = __ldg(xcol + static_cast<size_t>(j < last ? j : last) * p.ldo);
+  float sa = 0.f, sb = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    float g;
+    asm volatile("ld.shared.f32 %0, [%1];"
+                 : "=f"(g)
+                 : "r"(stage_box + static_cast<uint32_t>(j) * 128u +
+                       ((chunk ^ static_cast<uint32_t>(j & 7)) << 4) + byte));
+    const float xh = (static_cast<float>(xs[j]) - mu) * rs;
+    const float da = (fabsf(xh + be) > 1.0f) ? 0.f : g;
+    sa += da;
+    sb = fmaf(da, xh, sb);
+  }
+  acc_da += sa;
+  acc_dax += sb;
 }
 
 __global__ void __launch_bounds__(320, 1)
@@ -292,6 +385,12 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
       for (int i = 0; i < 11; ++i) l0_d[i] = 0.0;
       l0_mu = p.l0_mean[l0_c]; l0_rs = p.l0_rstd[l0_c]; l0_be = p.l0_beta[l0_c];
     }
+    // fused BatchNorm-backward sums (swap mode): the grid is a multiple of tiles_n, so this CTA's
+    // tn -- and with it this thread's channel -- is the same for every tile
+    const int bn_ch = (static_cast<int>(blockIdx.x) % p.tiles_n) * 128 + q * 32 + lane;
+    float bn_mu = 0.f, bn_rs = 0.f, bn_be = 0.f;
+    double bn_da = 0.0, bn_dax = 0.0;
+    if (p.bn_fused) { bn_mu = p.bn_mean[bn_ch]; bn_rs = p.bn_rstd[bn_ch]; bn_be = p.bn_beta[bn_ch]; }
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -317,52 +416,29 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
             // r[j] = gradient w.r.t. sign(a0) at pixel pix0 + j, channel l0_c.  Recompute the
             // first conv at that pixel (9 taps, same FMA order as the forward kernels), apply the
             // ste mask and accumulate everything the first layer's backward needs.
-            float f[11];
+            if (pix0 + 32 <= p.M)
+              first_layer_unit<false>(p, r, pix0, l0_w, l0_mu, l0_rs, l0_be, l0_d);
+            else
+              first_layer_unit<true>(p, r, pix0, l0_w, l0_mu, l0_rs, l0_be, l0_d);
+            continue;
+          }
+          if (p.bn_fused) {   // thread = channel: r[j] is the gradient at pixel pix0 + j
+            // (pixels at or beyond M: r[j] is an exact zero, only the x address is clamped)
+            const int last = p.M - 1 - pix0;
+            const int16_t* xcol = p.bn_x + static_cast<size_t>(pix0) * p.ldo + ch0 + lane;
+            int16_t xs[32];
 #pragma unroll
-            for (int i = 0; i < 11; ++i) f[i] = 0.f;
-            const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
-            unsigned b = static_cast<unsigned>(pix0) / hw;
-            const unsigned rem = static_cast<unsigned>(pix0) - b * hw;
-            unsigned oh = rem / static_cast<unsigned>(p.OW);
-            unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
-            const float* base = p.l0_x + (static_cast<size_t>(b) * p.l0_H + oh) * p.l0_W + ow;
-            float win[3][3];   // sliding 3x3 window along the image row: 3 new taps per pixel
-            bool fresh = true;
+            for (int j = 0; j < 32; ++j) xs[j] = __ldg(xcol + static_cast<size_t>(j < last ? j : last) * p.ldo);
+            float sa = 0.f, sb = 0.f;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              if (pix0 + j < p.M) {
-                if (fresh) {
-#pragma unroll
-                  for (int kh = 0; kh < 3; ++kh)
-#pragma unroll
-                    for (int kw = 0; kw < 2; ++kw) win[kh][kw] = __ldg(base + kh * p.l0_W + kw);
-                  fresh = false;
-                }
-#pragma unroll
-                for (int kh = 0; kh < 3; ++kh) win[kh][2] = __ldg(base + kh * p.l0_W + 2);
-                float y = 0.f;
-#pragma unroll
-                for (int k = 0; k < 9; ++k) y = fmaf(win[k / 3][k % 3], l0_w[k], y);
-                const float xh = (y - l0_mu) * l0_rs;
-                const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
-                f[0] += da;
-                f[1] = fmaf(da, xh, f[1]);
-#pragma unroll
-                for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(win[k / 3][k % 3], da, f[2 + k]);
-#pragma unroll
-                for (int kh = 0; kh < 3; ++kh) { win[kh][0] = win[kh][1]; win[kh][1] = win[kh][2]; }
-              }
-              ++base;
-              if (++ow == static_cast<unsigned>(p.OW)) {   // next image row (or next image)
-                ow = 0;
-                base += 2;
-                fresh = true;
-                if (++oh == static_cast<unsigned>(p.OH)) { oh = 0; base += 2 * p.l0_W; }
-              }
+              const float xh = (static_cast<float>(xs[j]) - bn_mu) * bn_rs;
+              const float da = (fabsf(xh + bn_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
+              sa += da;
+              sb = fmaf(da, xh, sb);
             }
-#pragma unroll
-            for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
-            continue;
+            bn_da += sa;
+            bn_dax += sb;
           }
           if (lane == 0) tma_store_wait_read_all();
           __syncwarp();
@@ -443,6 +519,10 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     if (p.l0_fused) {
 #pragma unroll
       for (int i = 0; i < 11; ++i) atomicAdd(p.l0_acc + i * 128 + l0_c, l0_d[i]);
+    }
+    if (p.bn_fused) {
+      atomicAdd(p.bn_sum_da + bn_ch, bn_da);
+      atomicAdd(p.bn_sum_dax + bn_ch, bn_dax);
     }
     if (lane == 0) tma_store_wait_all();
   }
@@ -631,6 +711,20 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
                                         1024 + static_cast<size_t>(ew) * 4096);
     const uint32_t my_row = stage_box + static_cast<uint32_t>(lane) * 128u;
     const uint32_t sw = static_cast<uint32_t>(lane & 7);
+    // fused BatchNorm-backward sums: the number of clusters is a multiple of tiles_n, so tn is the
+    // same for every tile of this cluster and the 4 units of this warp are 4 fixed channel groups
+    const int bn_n0 = (cluster_id % p.tiles_n) * 256;
+    float bn_mu[4], bn_rs[4], bn_be[4];
+    double bn_da[4], bn_dax[4];
+#pragma unroll
+    for (int sl = 0; sl < 4; ++sl) {
+      bn_da[sl] = bn_dax[sl] = 0.0;
+      bn_mu[sl] = bn_rs[sl] = bn_be[sl] = 0.f;
+      if (p.bn_fused) {
+        const int ch = bn_n0 + (half + 2 * sl) * 32 + lane;
+        bn_mu[sl] = p.bn_mean[ch]; bn_rs[sl] = p.bn_rstd[ch]; bn_be[sl] = p.bn_beta[ch];
+      }
+    }
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -642,7 +736,10 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
       tc_fence_after();
       const uint32_t tbase =
           tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(as) * 256u;
-      for (int u = half; u < units; u += 2) {
+#pragma unroll
+      for (int sl = 0; sl < 4; ++sl) {   // (unrolled: the fused-sum accumulators stay in registers)
+        const int u = half + 2 * sl;
+        if (u >= units) break;
         const int c0 = u * unit_cols;
         if (row0 >= p.M || n0 + c0 >= p.N) continue;   // nothing of this box would be stored
         uint32_t r[32];
@@ -682,12 +779,23 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
           tma_store_2d(&tmOut, stage_box, n0 + c0, row0);
           tma_store_commit();
         }
+        if (p.bn_fused)
+          bn_sums_from_box(p, stage_box, row0, n0 + c0 + lane, lane, bn_mu[sl], bn_rs[sl], bn_be[sl],
+                           bn_da[sl], bn_dax[sl]);
       }
       tc_fence_before();
       // release the accumulator stage on the leader's barrier (remote arrive from the peer CTA)
       mbar_arrive_cluster(mapa_shared(smem_u32(&ctl->tempty[as]), 0));
       as ^= 1;
       if (as == 0) aphase ^= 1u;
+    }
+    if (p.bn_fused) {
+#pragma unroll
+      for (int sl = 0; sl < 4; ++sl) {
+        const int ch = bn_n0 + (half + 2 * sl) * 32 + lane;
+        atomicAdd(p.bn_sum_da + ch, bn_da[sl]);
+        atomicAdd(p.bn_sum_dax + ch, bn_dax[sl]);
+      }
     }
     if (lane == 0) tma_store_wait_all();
   }
@@ -927,10 +1035,21 @@ struct FirstLayerFuse {   // see KGemmParams::l0_fused
   int H, W;
 };
 
+struct BnBackwardFuse {   // see KGemmParams::bn_fused
+  const int16_t* x;
+  const float *mean, *rstd, *beta;
+  double *sum_da, *sum_dax;
+};
+
+extern "C" int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                                 const float* mean, const float* rstd, const float* beta, int ste,
+                                 double* sum_da, double* sum_dax, void* stream);
+
 static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, void* out,
                         int out_kind, long long ldo, long long M, int N, int K, int im2col, int NB,
                         int H, int W, int C, int ksize, int pad, cudaStream_t stream,
-                        int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr) {
+                        int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr,
+                        const BnBackwardFuse* bn = nullptr) {
   const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
   const CUtensorMapDataType dt =
       elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -979,6 +1098,15 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   if (use_pairs) {
     p.block_n = 256;
     p.stage_bytes = p.a_terms * kATileBytes + kATileBytes;   // A tile(s) + this CTA's half of B
+  }
+  if (bn) {
+    ZKB_REQUIRE(out_kind == 0 && elem_bytes == 2 && !l0 && ldo == N,
+                "kgemm: fused BatchNorm-backward sums need a dense f32 dgrad output");
+    if (p.swap || use_pairs) {
+      p.bn_fused = 1;
+      p.bn_x = bn->x; p.bn_mean = bn->mean; p.bn_rstd = bn->rstd; p.bn_beta = bn->beta;
+      p.bn_sum_da = bn->sum_da; p.bn_sum_dax = bn->sum_dax;
+    }
   }
   p.num_stages = (kSmemBudget - kEpiStagingBytes) / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
@@ -1053,13 +1181,19 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     ZKB_CUDA(cudaFuncSetAttribute(kgemm2_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   227 * 1024));
     int clusters = tiles < sms / 2 ? tiles : sms / 2;
+    // (fused sums: every cluster keeps one tn, see the epilogue)
+    if (p.bn_fused && clusters > p.tiles_n) clusters -= clusters % p.tiles_n;
     kgemm2_bf16_kernel<<<clusters * 2, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
     ZKB_LAUNCH_CHECK("kgemm2_bf16_kernel");
     return ZKB_OK;
   }
-  const int grid = tiles < sms ? tiles : sms;
+  int grid = tiles < sms ? tiles : sms;
+  if (p.bn_fused && grid > p.tiles_n) grid -= grid % p.tiles_n;
   kgemm_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
   ZKB_LAUNCH_CHECK("kgemm_bf16_kernel");
+  if (bn && !p.bn_fused)   // tile shapes without the fused epilogue: the stand-alone reduction
+    return zkb_bn_bwd_reduce(static_cast<const float*>(out), bn->x, 1, M, N, bn->mean, bn->rstd,
+                             bn->beta, 1, bn->sum_da, bn->sum_dax, stream);
   return ZKB_OK;
 }
 
@@ -1200,6 +1334,18 @@ ZKB_API int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* 
   return launch_kgemm(dy_hi, dy_lo, wq_ic_k, dx_f32, 0, Cin, static_cast<long long>(NB) * H * W, Cin,
                       ksize * ksize * Cout, 1, NB, H, W, Cout, ksize, ksize / 2,
                       static_cast<cudaStream_t>(stream));
+}
+
+ZKB_API int zkb_bconv2d_dgrad_bn(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, void* dx_f32,
+                                 int NB, int H, int W, int Cin, int Cout, int ksize,
+                                 const void* x_i16, const float* mean, const float* rstd,
+                                 const float* beta, double* sum_da, double* sum_dax, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_dgrad_bn: ksize must be odd");
+  ZKB_REQUIRE(x_i16 && mean && rstd && beta && sum_da && sum_dax, "bconv2d_dgrad_bn: null pointer");
+  BnBackwardFuse bn{static_cast<const int16_t*>(x_i16), mean, rstd, beta, sum_da, sum_dax};
+  return launch_kgemm(dy_hi, dy_lo, wq_ic_k, dx_f32, 0, Cin, static_cast<long long>(NB) * H * W, Cin,
+                      ksize * ksize * Cout, 1, NB, H, W, Cout, ksize, ksize / 2,
+                      static_cast<cudaStream_t>(stream), 2, nullptr, &bn);
 }
 
 ZKB_API int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, const void* wq_ic_k,

@@ -128,6 +128,8 @@ class BinaryNetEngine:
         # first layer's backward inside layer 1's dgrad epilogue (ZKB_FUSE_FIRST_BWD=0: separate kernels)
         self.fuse_first_backward = (os.environ.get("ZKB_FUSE_FIRST_BWD", "1") != "0"
                                     and self._can_fuse_first_backward())
+        # BatchNorm-backward sums of layer i-1 inside layer i's dgrad epilogue (conv layers)
+        self.fuse_bn_backward_sums = os.environ.get("ZKB_FUSE_BN_BWD", "1") != "0"
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
@@ -479,6 +481,14 @@ class BinaryNetEngine:
         return (a.kind == "conv" and a.ksize == 3 and a.padding == "valid" and a.cin == 1 and a.cout == 128
                 and not a.pool and b.kind == "conv" and b.ksize == 3 and b.padding == "same")
 
+    def _sums_come_from_dgrad(self, i: int) -> bool:
+        """Layer i's BatchNorm-backward sums are produced by the dgrad of layer i+1 (a conv whose
+        input is layer i's sign map, channel count a multiple of 128)."""
+        if not self.fuse_bn_backward_sums or i < 1 or i + 1 >= len(self.layers):
+            return False
+        nxt = self.layers[i + 1]
+        return nxt.kind == "conv" and self.layers[i].kind == "conv" and self.L[i].cp % 128 == 0
+
     def _fused_first_layer_backward(self, L1):
         """Layer 1's dgrad GEMM whose epilogue is the whole backward of layer 0 (BatchNorm sums,
         ste mask, weight-gradient sums), then a one-block finalize."""
@@ -546,8 +556,9 @@ class BinaryNetEngine:
             is_i16 = 1
             rows = L.bn_rows
             ste = 0 if last else 1
-            self._call("zkb_bn_bwd_reduce", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
-                       zn.ptr(L.beta), ste, zn.ptr(L.sum_da), zn.ptr(L.sum_dax))
+            if not self._sums_come_from_dgrad(i):
+                self._call("zkb_bn_bwd_reduce", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
+                           zn.ptr(L.beta), ste, zn.ptr(L.sum_da), zn.ptr(L.sum_dax))
             count = float(rows)
             if self.sync_bn:
                 self._all_reduce(L.sum_da)
@@ -578,6 +589,11 @@ class BinaryNetEngine:
                 if i == 1 and self.fuse_first_backward:
                     self._fused_first_layer_backward(L)
                     self._tag = f"bwd{i}"
+                elif self._sums_come_from_dgrad(i - 1):
+                    px = prev.p if prev.spec.pool else prev.y
+                    self._call("zkb_bconv2d_dgrad_bn", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
+                               B, ih, iw, l.cin, l.cout, l.ksize, zn.ptr(px), zn.ptr(prev.mean), zn.ptr(prev.rstd),
+                               zn.ptr(prev.beta), zn.ptr(prev.sum_da), zn.ptr(prev.sum_dax))
                 else:
                     self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                                B, ih, iw, l.cin, l.cout, l.ksize)

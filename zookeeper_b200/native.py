@@ -46,6 +46,7 @@ SIGNATURES = {
     "zkb_bdense_fwd_i8": [P, P, P, L, I, I, I, P],
     "zkb_bconv2d_dgrad": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_dgrad": [P, P, P, P, I, I, I, P],
+    "zkb_bconv2d_dgrad_bn": [P, P, P, P, I, I, I, I, I, I, P, P, P, P, P, P, P],
     "zkb_bconv2d_dgrad_first_bwd": [P, P, P, I, I, I, I, I, I, P, I, I, P, P, P, P, P, P],
     "zkb_conv_first_bwd_finalize": [P, P, P, P, P, D, D, P, P, I, P],
     "zkb_conv_first_gram": [P, I, I, I, P, P],
