@@ -105,6 +105,15 @@ int zkb_bconv2d_fwd_i8(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, 
                        int Cin, int Cout, int ksize, void* stream);
 int zkb_bdense_fwd_i8(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy, int rows,
                       int K, int N, void* stream);
+/* The int8 forward that also leaves the BatchNorm batch statistics of its output: per channel
+ * sum += sum of y, sumsq += sum of y*y over all rows (float64 accumulators holding exact integers,
+ * zeroed by the caller) -- what zkb_bn_stats would compute from y_i16 in a second pass.  The
+ * epilogue reads each staged int16 box back column-wise before the TMA store leaves. */
+int zkb_bconv2d_fwd_i8_stats(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H,
+                             int W, int Cin, int Cout, int ksize, double* sum, double* sumsq,
+                             void* stream);
+int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,
+                            int rows, int K, int N, double* sum, double* sumsq, void* stream);
 /* Backward w.r.t. the input (before the STE mask): dx f32 [NB,H,W,Cin] / [rows,K].
  * Replaces: TF autodiff of the layers above (model.fit, examples/larq_experiment.py:147-153). */
 int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, void* dx_f32,

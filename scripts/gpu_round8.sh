@@ -1,0 +1,12 @@
+#!/bin/bash
+# parity tests, smoke, bench per-kernel vs graph replay
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -30 | tee gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee gpurun_out/smoke.log
+pr() { python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"; }
+for i in 1 2; do
+timeout 900 python bench.py --steps 20 --warmup 5 2>/dev/null > gpurun_out/bench2.json; echo -n "per-kernel: "; pr < gpurun_out/bench2.json
+timeout 900 python bench.py --steps 20 --warmup 5 --graph 2>/dev/null > gpurun_out/bench_graph.json; echo -n "graph: "; pr < gpurun_out/bench_graph.json
+done
+timeout 300 python scripts/timeline.py > gpurun_out/timeline.txt 2>&1; head -30 gpurun_out/timeline.txt

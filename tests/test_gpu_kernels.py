@@ -243,6 +243,48 @@ def test_first_conv_gram_gives_the_batch_statistics(native_lib, B, H, W):
     np.testing.assert_allclose(q1.cpu().numpy(), q2.cpu().numpy(), rtol=1e-5)
 
 
+@pytest.mark.parametrize("rows,K,N", [(300, 1024, 1024), (96, 256, 64), (4100, 512, 256)])
+def test_forward_gemm_leaves_exact_batch_statistics(native_lib, rows, K, N):
+    """zkb_bdense_fwd_i8_stats == zkb_bdense_fwd_i8 + zkb_bn_stats, bit for bit (integer sums)."""
+    from zookeeper_b200 import native as zn
+
+    g = torch.Generator(device="cuda").manual_seed(rows)
+    a = (torch.randint(0, 2, (rows, K), device="cuda", generator=g, dtype=torch.int8) * 2 - 1)
+    w = (torch.randint(0, 2, (N, K), device="cuda", generator=g, dtype=torch.int8) * 2 - 1)
+    y1 = torch.zeros(rows, N, dtype=torch.int16, device="cuda")
+    y2 = torch.zeros_like(y1)
+    s1, q1, s2, q2 = (torch.zeros(N, dtype=torch.float64, device="cuda") for _ in range(4))
+    zn.call("zkb_bdense_fwd_i8_stats", zn.ptr(a), zn.ptr(w), zn.ptr(y1), N, rows, K, N, zn.ptr(s1), zn.ptr(q1), 0)
+    zn.call("zkb_bdense_fwd_i8", zn.ptr(a), zn.ptr(w), zn.ptr(y2), N, rows, K, N, 0)
+    zn.call("zkb_bn_stats", zn.ptr(y2), 1, rows, N, zn.ptr(s2), zn.ptr(q2), 0)
+    torch.cuda.synchronize()
+    ref = a.double() @ w.double().T
+    assert torch.equal(y1, y2) and torch.equal(y1.double(), ref)
+    assert torch.equal(s1, ref.sum(0)) and torch.equal(q1, (ref * ref).sum(0))
+    assert torch.equal(s1, s2) and torch.equal(q1, q2)
+
+
+def test_conv_forward_gemm_leaves_exact_batch_statistics(native_lib):
+    from zookeeper_b200 import native as zn
+
+    B, H, W, Cin, Cout = 5, 13, 13, 128, 256
+    s8 = (torch.randint(0, 2, (B, H, W, Cin), device="cuda", dtype=torch.int8) * 2 - 1)
+    w = torch.randn(3, 3, Cin, Cout, device="cuda")
+    wf = torch.empty(Cout, 9 * Cin, dtype=torch.bfloat16, device="cuda")
+    wd = torch.empty(Cin, 9 * Cout, dtype=torch.bfloat16, device="cuda")
+    wf8 = torch.empty(Cout, 9 * Cin, dtype=torch.int8, device="cuda")
+    zn.call("zkb_prep_conv_weights", zn.ptr(w), 3, Cin, Cout, zn.ptr(wf), zn.ptr(wd), zn.ptr(wf8), 0)
+    y1 = torch.zeros(B, H, W, Cout, dtype=torch.int16, device="cuda")
+    y2 = torch.zeros_like(y1)
+    s1, q1 = (torch.zeros(Cout, dtype=torch.float64, device="cuda") for _ in range(2))
+    zn.call("zkb_bconv2d_fwd_i8_stats", zn.ptr(s8), zn.ptr(wf8), zn.ptr(y1), B, H, W, Cin, Cout, 3, zn.ptr(s1), zn.ptr(q1), 0)
+    zn.call("zkb_bconv2d_fwd_i8", zn.ptr(s8), zn.ptr(wf8), zn.ptr(y2), B, H, W, Cin, Cout, 3, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(y1, y2)
+    yd = y2.double().reshape(-1, Cout)
+    assert torch.equal(s1, yd.sum(0)) and torch.equal(q1, (yd * yd).sum(0))
+
+
 def test_full_size_train_step_properties(native_lib):
     """configs[1] (batch 4096): too large for the CPU oracle, so check properties that do not depend
     on size: integer layer outputs respect |y| <= K and the +-1 parity, pooled = max of its window,

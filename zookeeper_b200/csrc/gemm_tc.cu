@@ -57,6 +57,11 @@ struct KGemmParams {
   // CTA pairs): D[row][c] is the gradient w.r.t. that layer's sign output, bn_x its pre-BatchNorm
   // int16 map of the same shape; per channel sum da and sum da*xhat (da = D masked by |a| <= 1)
   // are added into bn_sum_da / bn_sum_dax -- what bn_bwd_reduce_kernel computes from D in HBM.
+  // BatchNorm-forward statistics fused into the int16 epilogue (non-swap, one CTA per tile): per
+  // output channel sum y and sum y^2 over all rows, exact integers, added into st_sum / st_sumsq
+  // (float64) -- what bn_stats_kernel computes from y in a second pass.
+  int st_fused;
+  double *st_sum, *st_sumsq;
   int bn_fused;
   const int16_t* bn_x;
   const float *bn_mean, *bn_rstd, *bn_beta;
@@ -391,6 +396,8 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     float bn_mu = 0.f, bn_rs = 0.f, bn_be = 0.f;
     double bn_da = 0.0, bn_dax = 0.0;
     if (p.bn_fused) { bn_mu = p.bn_mean[bn_ch]; bn_rs = p.bn_rstd[bn_ch]; bn_be = p.bn_beta[bn_ch]; }
+    // fused forward statistics: 2 units of 64 columns per warp and tile, a column pair per lane
+    long long st_s[2][2] = {{0, 0}, {0, 0}}, st_q[2][2] = {{0, 0}, {0, 0}};
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -463,7 +470,10 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
         if (as == 0) aphase ^= 1u;
         continue;
       }
-      for (int u = half; u < units; u += 2) {
+#pragma unroll
+      for (int sl = 0; sl < 4; ++sl) {
+        const int u = half + 2 * sl;
+        if (u >= units) break;
         const int c0 = u * unit_cols;
         uint32_t r[32];
         tmem_ld_32x32(tbase + static_cast<uint32_t>(c0), r);
@@ -510,11 +520,44 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
           tma_store_2d(&tmOut, stage_box, n0 + c0, row0);
           tma_store_commit();
         }
+        if (p.st_fused && sl < 2) {
+          // columns 2*lane, 2*lane+1 of the staged 32 x 64 int16 box (rows >= M are exact zeros)
+          const uint32_t col = stage_box + ((static_cast<uint32_t>(lane >> 2)) << 4) +
+                               static_cast<uint32_t>(lane & 3) * 4u;
+          int s0 = 0, s1 = 0, q0 = 0, q1 = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            uint32_t w2;
+            asm volatile("ld.shared.b32 %0, [%1];"
+                         : "=r"(w2)
+                         : "r"((col ^ (static_cast<uint32_t>(j & 7) << 4)) + static_cast<uint32_t>(j) * 128u));
+            const int a = static_cast<int16_t>(w2 & 0xFFFFu), b = static_cast<int>(w2) >> 16;
+            s0 += a; s1 += b;
+            q0 += a * a; q1 += b * b;      // 32 rows x 4608^2 < 2^31
+          }
+          st_s[sl][0] += s0; st_s[sl][1] += s1;
+          st_q[sl][0] += q0; st_q[sl][1] += q1;
+        }
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&ctl->tempty[as]));
       as ^= 1;
       if (as == 0) aphase ^= 1u;
+    }
+    if (p.st_fused) {
+      const int n0c = (static_cast<int>(blockIdx.x) % p.tiles_n) * p.block_n;   // this CTA's tn is fixed
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl) {
+        const int ch = n0c + (half + 2 * sl) * 64 + 2 * lane;
+        if ((half + 2 * sl) * 64 < p.block_n && ch < p.N) {
+          atomicAdd(p.st_sum + ch, static_cast<double>(st_s[sl][0]));
+          atomicAdd(p.st_sumsq + ch, static_cast<double>(st_q[sl][0]));
+          if (ch + 1 < p.N) {
+            atomicAdd(p.st_sum + ch + 1, static_cast<double>(st_s[sl][1]));
+            atomicAdd(p.st_sumsq + ch + 1, static_cast<double>(st_q[sl][1]));
+          }
+        }
+      }
     }
     if (p.l0_fused) {
 #pragma unroll
@@ -858,8 +901,9 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   const int tc = wi % p.ci_tiles;
   wi /= p.ci_tiles;
   const int groups = (p.taps + p.tpi - 1) / p.tpi;
-  const int tap0 = (wi % groups) * p.tpi;
-  const int split = wi / groups;
+  const int group = wi % groups;     // all tap groups of a split are neighbours in launch order:
+  const int split = wi / groups;     // they read the same pixels at about the same time (L2 reuse)
+  const int tap0 = group * p.tpi;
   const int tcount = (p.taps - tap0) < p.tpi ? (p.taps - tap0) : p.tpi;  // taps of this item
 
   const long long total_chunks = (p.P + p.kpix - 1) / p.kpix;
@@ -1041,6 +1085,12 @@ struct BnBackwardFuse {   // see KGemmParams::bn_fused
   double *sum_da, *sum_dax;
 };
 
+struct StatsFuse {   // see KGemmParams::st_fused
+  double *sum, *sumsq;
+};
+
+extern "C" int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum,
+                            double* sumsq, void* stream);
 extern "C" int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
                                  const float* mean, const float* rstd, const float* beta, int ste,
                                  double* sum_da, double* sum_dax, void* stream);
@@ -1049,7 +1099,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
                         int out_kind, long long ldo, long long M, int N, int K, int im2col, int NB,
                         int H, int W, int C, int ksize, int pad, cudaStream_t stream,
                         int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr,
-                        const BnBackwardFuse* bn = nullptr) {
+                        const BnBackwardFuse* bn = nullptr, const StatsFuse* st = nullptr) {
   const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
   const CUtensorMapDataType dt =
       elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -1106,6 +1156,15 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
       p.bn_fused = 1;
       p.bn_x = bn->x; p.bn_mean = bn->mean; p.bn_rstd = bn->rstd; p.bn_beta = bn->beta;
       p.bn_sum_da = bn->sum_da; p.bn_sum_dax = bn->sum_dax;
+    }
+  }
+  if (st) {
+    ZKB_REQUIRE(out_kind == 1 && ldo == N && st->sum && st->sumsq,
+                "kgemm: fused statistics need a dense int16 output and both accumulators");
+    if (!p.swap && !use_pairs) {
+      p.st_fused = 1;
+      p.st_sum = st->sum;
+      p.st_sumsq = st->sumsq;
     }
   }
   p.num_stages = (kSmemBudget - kEpiStagingBytes) / p.stage_bytes;
@@ -1185,12 +1244,14 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     if (p.bn_fused && clusters > p.tiles_n) clusters -= clusters % p.tiles_n;
     kgemm2_bf16_kernel<<<clusters * 2, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
     ZKB_LAUNCH_CHECK("kgemm2_bf16_kernel");
+    if (st) return zkb_bn_stats(out, 1, M, N, st->sum, st->sumsq, stream);
     return ZKB_OK;
   }
   int grid = tiles < sms ? tiles : sms;
-  if (p.bn_fused && grid > p.tiles_n) grid -= grid % p.tiles_n;
+  if ((p.bn_fused || p.st_fused) && grid > p.tiles_n) grid -= grid % p.tiles_n;
   kgemm_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
   ZKB_LAUNCH_CHECK("kgemm_bf16_kernel");
+  if (st && !p.st_fused) return zkb_bn_stats(out, 1, M, N, st->sum, st->sumsq, stream);
   if (bn && !p.bn_fused)   // tile shapes without the fused epilogue: the stand-alone reduction
     return zkb_bn_bwd_reduce(static_cast<const float*>(out), bn->x, 1, M, N, bn->mean, bn->rstd,
                              bn->beta, 1, bn->sum_da, bn->sum_dax, stream);
@@ -1255,14 +1316,24 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   p.out = out;
   p.ldo = ldo;
   const long long chunks = (P + p.kpix - 1) / p.kpix;
-  const int groups = (p.taps + p.tpi - 1) / p.tpi;
-  const int out_tiles = groups * p.ci_tiles * p.n_tiles;
   const int sms = zkb_sm_count();
-  // Short work items: the wgrad kernels run on a low-priority stream next to the dependent
-  // backward chain, and a high-priority kernel can only take an SM when a wgrad CTA retires.
-  int waves = 2;
-  if (const char* e = getenv("ZKB_WGRAD_WAVES")) waves = atoi(e) > 0 ? atoi(e) : waves;
-  long long splits = (static_cast<long long>(waves) * sms + out_tiles - 1) / out_tiles;
+  // Split the reduction over pixels so that the grid fills FULL waves (one CTA per SM): a few
+  // CTAs spilling into one more wave cost a whole extra work item of time (measured 10-13 %), and
+  // one long wave beats two short ones (fewer pipeline fills and atomic epilogues; measured in the
+  // step, r1) unless the output tiles divide the SMs badly.
+  const int out_tiles = ((p.taps + p.tpi - 1) / p.tpi) * p.ci_tiles * p.n_tiles;
+  int waves = 0;
+  if (const char* e = getenv("ZKB_WGRAD_WAVES")) waves = atoi(e) > 0 ? atoi(e) : 0;
+  if (waves == 0) {
+    double best = 0.0;
+    for (int w = 1; w <= 3; ++w) {
+      const long long g = (static_cast<long long>(w) * sms / out_tiles) * out_tiles;
+      const double fill = static_cast<double>(g) / (static_cast<double>(w) * sms);
+      if (fill > best + 0.05) { best = fill; waves = w; }   // more waves only for a clearly better fill
+    }
+    if (waves == 0) waves = 1;
+  }
+  long long splits = (static_cast<long long>(waves) * sms) / out_tiles;
   if (splits > chunks) splits = chunks;
   if (splits < 1) splits = 1;
   p.chunks_per_split = static_cast<int>((chunks + splits - 1) / splits);
@@ -1314,6 +1385,23 @@ ZKB_API int zkb_bconv2d_fwd_i8(const void* act_i8, const void* wq_oc_k_i8, void*
   return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout,
                       static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
                       Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1);
+}
+
+ZKB_API int zkb_bconv2d_fwd_i8_stats(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB,
+                                     int H, int W, int Cin, int Cout, int ksize, double* sum,
+                                     double* sumsq, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_fwd_i8_stats: ksize must be odd");
+  StatsFuse st{sum, sumsq};
+  return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout,
+                      static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
+                      Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1, nullptr, nullptr, &st);
+}
+
+ZKB_API int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,
+                                    int rows, int K, int N, double* sum, double* sumsq, void* stream) {
+  StatsFuse st{sum, sumsq};
+  return launch_kgemm(act_i8, nullptr, wq_n_k_i8, y_i16, 1, ldy, rows, N, K, 0, 0, 0, 0, 0, 0, 0,
+                      static_cast<cudaStream_t>(stream), 1, nullptr, nullptr, &st);
 }
 
 ZKB_API int zkb_bdense_fwd_i8(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,

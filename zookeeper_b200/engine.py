@@ -124,12 +124,15 @@ class BinaryNetEngine:
         self._side_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._wgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._dgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
+        self._prep_fork, self._prep_join, self._prep_pending = torch.cuda.Event(), torch.cuda.Event(), False
         self.serialize_gemms = os.environ.get("ZKB_SERIALIZE_GEMMS", "0") == "1"
         # first layer's backward inside layer 1's dgrad epilogue (ZKB_FUSE_FIRST_BWD=0: separate kernels)
         self.fuse_first_backward = (os.environ.get("ZKB_FUSE_FIRST_BWD", "1") != "0"
                                     and self._can_fuse_first_backward())
         # BatchNorm-backward sums of layer i-1 inside layer i's dgrad epilogue (conv layers)
         self.fuse_bn_backward_sums = os.environ.get("ZKB_FUSE_BN_BWD", "1") != "0"
+        # BatchNorm batch statistics inside the forward GEMM epilogue (layers that do not pool)
+        self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
@@ -423,13 +426,20 @@ class BinaryNetEngine:
         for L in self.L:
             l = L.spec
             self._tag = f"fwd{L.idx}"
+            if L.idx >= 1 and self._prep_pending:       # binary-layer weights prepared on the side stream
+                torch.cuda.current_stream(self.device).wait_event(self._prep_join)
+                self._prep_pending = False
             if l.kind == "conv":
                 oh, ow = L.out_hw
                 if L.idx == 0:
                     self._first_layer_forward(L, training)
                 else:
                     ih, iw = L.in_hw
-                    if self.forward_int8:
+                    fused_stats = self.forward_int8 and self.fuse_forward_stats and training and not l.pool
+                    if fused_stats:
+                        self._call("zkb_bconv2d_fwd_i8_stats", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), B, ih, iw,
+                                   l.cin, l.cout, l.ksize, zn.ptr(L.sum), zn.ptr(L.sumsq))
+                    elif self.forward_int8:
                         self._call("zkb_bconv2d_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), B, ih, iw, l.cin, l.cout, l.ksize)
                     else:
                         self._call("zkb_bconv2d_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), B, ih, iw, l.cin, l.cout, l.ksize)
@@ -438,13 +448,17 @@ class BinaryNetEngine:
                                    zn.ptr(L.sum), zn.ptr(L.sumsq))
                         self._bn_forward(L, L.p, True, L.bn_rows, True, training)
                     else:
-                        self._bn_forward(L, L.y, True, L.bn_rows, False, training)
+                        self._bn_forward(L, L.y, True, L.bn_rows, fused_stats, training)
             else:
-                if self.forward_int8:
+                fused_stats = self.forward_int8 and self.fuse_forward_stats and training
+                if fused_stats:
+                    self._call("zkb_bdense_fwd_i8_stats", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp,
+                               zn.ptr(L.sum), zn.ptr(L.sumsq))
+                elif self.forward_int8:
                     self._call("zkb_bdense_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
                 else:
                     self._call("zkb_bdense_fwd", zn.ptr(prev.s), zn.ptr(L.w_fwd), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
-                self._bn_forward(L, L.y, True, B, False, training)
+                self._bn_forward(L, L.y, True, B, fused_stats, training)
             prev = L
 
     def _first_layer_forward(self, L, training: bool):
@@ -525,17 +539,28 @@ class BinaryNetEngine:
         self._call("zkb_conv_first_bwd_wgrad", zn.ptr(self.x0), zn.ptr(L.wq), zn.ptr(L.ds), *geom, zn.ptr(L.mean),
                    zn.ptr(L.rstd), zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), zn.ptr(L.dkernel))
 
-    def prepare_weights(self):
+    def prepare_weights(self, side=None):
+        """sign(W) in the operand layouts of the GEMMs.  With ``side`` (a second stream) the binary
+        layers' weights are prepared there, next to the first layer's forward on the current
+        stream; :meth:`forward` waits for them before the first binary GEMM."""
+        self._tag = "prep"
+        main = torch.cuda.current_stream(self.device)
+        if side is not None:
+            self._prep_fork.record(main)     # after the previous step's Adam
+            side.wait_event(self._prep_fork)
         for L in self.L:
             l = L.spec
             if L.idx == 0:
                 self._call("zkb_sign_f32", zn.ptr(L.kernel), zn.ptr(L.wq), L.kernel.numel())
             elif l.kind == "conv":
                 self._call("zkb_prep_conv_weights", zn.ptr(L.kernel), l.ksize, l.cin, l.cout, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad),
-                           zn.ptr(L.w_fwd8))
+                           zn.ptr(L.w_fwd8), on=side)
             else:
                 self._call("zkb_prep_dense_weights", zn.ptr(L.kernel), l.cin, l.cout, L.cp, zn.ptr(L.w_fwd), zn.ptr(L.w_dgrad),
-                           zn.ptr(L.w_fwd8))
+                           zn.ptr(L.w_fwd8), on=side)
+        if side is not None:
+            self._prep_join.record(side)
+            self._prep_pending = True
 
     def backward(self, side=None):
         """Backward pass.  With ``side`` (a low-priority stream) the wgrad GEMMs are issued there:
@@ -656,7 +681,7 @@ class BinaryNetEngine:
             self.grads.zero_()
             if not preprocessed:
                 self.preprocess(images_u8, labels_i64, index, True, pad_size, aug, seed, self.step_count)
-            self.prepare_weights()
+            self.prepare_weights(self._side if use_side else None)
             self.forward(training=True)
             self.loss_and_grad()
             self.backward(self._side if use_side else None)
@@ -695,7 +720,7 @@ class BinaryNetEngine:
                 self.grads.zero_()
                 self.preprocess(images_u8, labels_i64, self.index_buf, True, pad_size, None, seed, 0,
                                 step_dev=self._dyn_step)
-                self.prepare_weights()
+                self.prepare_weights(self._side if self.overlap else None)
                 self.forward(training=True)
                 self.loss_and_grad()
                 self.backward(self._side if self.overlap else None)
