@@ -114,6 +114,22 @@ int zkb_bconv2d_fwd_i8_stats(const void* act_i8, const void* wq_oc_k_i8, void* y
                              void* stream);
 int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,
                             int rows, int K, int N, double* sum, double* sumsq, void* stream);
+/* Inference (validation pass, examples/larq_experiment.py:133-139, 151-152): BatchNormalization with
+ * moving statistics followed by ste_sign is a step function of the integer conv/dense output, so
+ * the two fold into one threshold per output channel.  zkb_bn_sign_thresholds writes thr[c] = the
+ * smallest integer y with (float(y) - mean[c]) * rstd[c] + beta[c] >= 0 (the float expression of
+ * zkb_bn_apply_sign; INT_MAX / INT_MIN if never / always).  The *_sign forwards compare the int32
+ * accumulator with thr in the epilogue and store int8 +1 / -1 ([NB,H,W,Cout] / [rows,lds]); no
+ * int16 map is written.  Cout (N) must be a multiple of the tile width min(256, Cout).
+ * zkb_maxpool2_sign_i8: 2x2/2 max-pool of such signs (= sign of the normalised pooled maximum,
+ * because rstd > 0); C % 16 == 0. */
+int zkb_bn_sign_thresholds(const float* mean, const float* rstd, const float* beta, int C,
+                           int* thr_i32, void* stream);
+int zkb_bconv2d_fwd_i8_sign(const void* act_i8, const void* wq_oc_k_i8, const int* thr, void* s_out_i8,
+                            int NB, int H, int W, int Cin, int Cout, int ksize, void* stream);
+int zkb_bdense_fwd_i8_sign(const void* act_i8, const void* wq_n_k_i8, const int* thr, void* s_out_i8,
+                           long long lds, int rows, int K, int N, void* stream);
+int zkb_maxpool2_sign_i8(const void* s_i8, int B, int H, int W, int C, void* out_i8, void* stream);
 /* Backward w.r.t. the input (before the STE mask): dx f32 [NB,H,W,Cin] / [rows,K].
  * Replaces: TF autodiff of the layers above (model.fit, examples/larq_experiment.py:147-153). */
 int zkb_bconv2d_dgrad(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, void* dx_f32,

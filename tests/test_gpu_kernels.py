@@ -285,6 +285,60 @@ def test_conv_forward_gemm_leaves_exact_batch_statistics(native_lib):
     assert torch.equal(s1, yd.sum(0)) and torch.equal(q1, (yd * yd).sum(0))
 
 
+def test_sign_thresholds_reproduce_the_float_batchnorm_sign(native_lib):
+    """thr[c] from zkb_bn_sign_thresholds: y >= thr[c]  <=>  zkb_bn_apply_sign gives +1, for every
+    int16 y (edge channels included: never / always +1, huge and tiny rstd)."""
+    from zookeeper_b200 import native as zn
+
+    C = 128
+    rng = np.random.default_rng(0)
+    mean = rng.normal(0, 50, C).astype(np.float32)
+    rstd = (1.0 / np.sqrt(rng.uniform(1.0, 4000.0, C))).astype(np.float32)
+    beta = rng.normal(0, 1, C).astype(np.float32)
+    mean[0], beta[0] = 1e9, 0.0            # never +1
+    mean[1], beta[1] = -1e9, 0.0           # always +1
+    rstd[2], beta[2] = 1e-6, 1e-3          # beta decides alone
+    rstd[3], mean[3], beta[3] = 30.0, 0.4999, 0.0
+    d = lambda a: torch.tensor(a).cuda()
+    dm, dr, db = d(mean), d(rstd), d(beta)
+    thr = torch.zeros(C, dtype=torch.int32, device="cuda")
+    zn.call("zkb_bn_sign_thresholds", zn.ptr(dm), zn.ptr(dr), zn.ptr(db), C, zn.ptr(thr), 0)
+    ys = torch.arange(-32768, 32768, dtype=torch.int16, device="cuda")
+    y = ys[:, None].expand(-1, C).contiguous()
+    s8 = torch.zeros(y.shape, dtype=torch.int8, device="cuda")
+    zn.call("zkb_bn_apply_sign", zn.ptr(y), 1, y.shape[0], C, zn.ptr(dm), zn.ptr(dr), zn.ptr(db), 0, 0, zn.ptr(s8), 0)
+    torch.cuda.synchronize()
+    want = s8 > 0
+    got = y.int() >= thr[None, :]
+    assert torch.equal(want, got)
+    assert int(thr[0]) == 2**31 - 1 and int(thr[1]) == -2**31
+
+
+def test_sign_pool_and_threshold_gemm(native_lib):
+    """zkb_bdense_fwd_i8_sign == (zkb_bdense_fwd_i8 >= thr); zkb_maxpool2_sign_i8 == max of 4."""
+    from zookeeper_b200 import native as zn
+
+    rows, K, N = 333, 512, 256
+    g = torch.Generator(device="cuda").manual_seed(3)
+    a = (torch.randint(0, 2, (rows, K), device="cuda", generator=g, dtype=torch.int8) * 2 - 1)
+    w = (torch.randint(0, 2, (N, K), device="cuda", generator=g, dtype=torch.int8) * 2 - 1)
+    thr = torch.randint(-40, 40, (N,), device="cuda", generator=g, dtype=torch.int32)
+    thr[0], thr[1] = 2**31 - 1, -2**31
+    s = torch.zeros(rows, N, dtype=torch.int8, device="cuda")
+    zn.call("zkb_bdense_fwd_i8_sign", zn.ptr(a), zn.ptr(w), zn.ptr(thr), zn.ptr(s), N, rows, K, N, 0)
+    torch.cuda.synchronize()
+    y = (a.float() @ w.float().T).int()
+    assert torch.equal(s, torch.where(y >= thr[None, :], 1, -1).to(torch.int8))
+
+    B, H, W, C = 3, 13, 26, 64
+    t = (torch.randint(0, 2, (B, H, W, C), device="cuda", generator=g, dtype=torch.int8) * 2 - 1)
+    out = torch.zeros(B, H // 2, W // 2, C, dtype=torch.int8, device="cuda")
+    zn.call("zkb_maxpool2_sign_i8", zn.ptr(t), B, H, W, C, zn.ptr(out), 0)
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.max_pool2d(t.permute(0, 3, 1, 2).float(), 2).permute(0, 2, 3, 1).to(torch.int8)
+    assert torch.equal(out, ref)
+
+
 def test_full_size_train_step_properties(native_lib):
     """configs[1] (batch 4096): too large for the CPU oracle, so check properties that do not depend
     on size: integer layer outputs respect |y| <= K and the +-1 parity, pooled = max of its window,

@@ -213,6 +213,45 @@ def test_eval_step_matches_oracle(native_lib):
     assert _rel(eng.logits(), ref) < 1e-4
 
 
+@pytest.mark.parametrize("B", [16, 200])
+def test_folded_inference_is_bit_identical_to_the_batchnorm_path(native_lib, monkeypatch, B):
+    """eval_step with BatchNorm + sign folded into integer thresholds inside the GEMM epilogues
+    (the default) against eval_step through the int16 maps and zkb_bn_apply_sign: same logits, bit
+    for bit, and both match the oracle's predict()."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    layers_o = O.binarynet_layers((28, 28, 1), 128, 1024, 10)
+    params = O.glorot_uniform_params(layers_o, 0)
+    rng = np.random.default_rng(B)
+    moving = {}
+    for i, l in enumerate(layers_o):
+        # means near the typical |y| scale so that thresholds cut through the populated range
+        moving[f"moving_mean{i}"] = rng.normal(0, 3.0, l.cout).astype(np.float32)
+        moving[f"moving_var{i}"] = rng.uniform(20.0, 400.0, l.cout).astype(np.float32)
+    for k in list(params):
+        if k.startswith("beta"):
+            params[k] = rng.normal(0, 0.5, params[k].shape).astype(np.float32)
+    img = rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)
+    lab = rng.integers(0, 10, (B,)).astype(np.int64)
+    outs = []
+    for fold in ("1", "0"):
+        monkeypatch.setenv("ZKB_FOLD_EVAL", fold)
+        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+        assert eng.fold_eval == (fold == "1")
+        eng.load_params(params, moving)
+        eng.eval_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda())
+        torch.cuda.synchronize()
+        outs.append((eng.L[-1].logits.cpu().numpy().copy(), [L.s8.cpu().numpy().copy() for L in eng.L[:-1]],
+                     eng.last_loss(), eng.last_accuracy()))
+    for i, (a, b) in enumerate(zip(outs[0][1], outs[1][1])):
+        assert np.array_equal(a, b), f"layer {i}: folded signs differ"
+    assert np.array_equal(outs[0][0], outs[1][0])
+    assert outs[0][2:] == outs[1][2:]
+    ref = O.predict(params, moving, layers_o, O.preprocess(img, (28, 28), False))
+    assert _rel(outs[0][0][:, :10], ref) < 1e-4
+
+
 def test_cifar_shaped_config_matches_oracle(native_lib):
     """BASELINE.json configs[2]: the same BinaryNet factory on 32x32x3 inputs (first conv K = 27,
     odd 15x15 -> 7x7 pooling drops the trailing row/column, flatten 3*3*512)."""

@@ -438,6 +438,56 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
   }
 }
 
+// Inference: sign((y - mean) * rstd + beta) for an integer y is a step function of y (rstd > 0),
+// so BatchNorm + sign fold into one integer threshold per channel: the smallest y whose affine
+// value -- the SAME float expression bn_apply_sign_kernel evaluates -- is >= 0.  Found by bisection
+// over the int16 range; INT_MAX / INT_MIN when the sign never / always is +1.
+__global__ void bn_sign_threshold_kernel(const float* __restrict__ mean, const float* __restrict__ rstd,
+                                         const float* __restrict__ beta, int C, int* __restrict__ thr) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float mu = mean[c], rs = rstd[c], be = beta[c];
+  auto plus = [&](int y) { return (static_cast<float>(y) - mu) * rs + be >= 0.0f; };
+  int lo = -32768, hi = 32767;      // invariant: !plus(lo - 1) (virtually), plus(hi + 1) (virtually)
+  if (!plus(hi)) { thr[c] = 0x7FFFFFFF; return; }
+  if (plus(lo)) { thr[c] = static_cast<int>(0x80000000u); return; }
+  while (hi - lo > 1) {             // !plus(lo), plus(hi)
+    const int mid = lo + (hi - lo) / 2;
+    if (plus(mid)) hi = mid; else lo = mid;
+  }
+  thr[c] = hi;
+}
+
+// 2x2/2 max-pool of int8 signs: +1 if any of the four is +1 (= sign(BN(max y)) for rstd > 0).
+__global__ void __launch_bounds__(256)
+maxpool2_sign_i8_kernel(const int8_t* __restrict__ s, int B, int H, int W, int C,
+                        int8_t* __restrict__ out) {
+  const int PH = H / 2, PW = W / 2, tpr = C / 16;
+  const long long total = static_cast<long long>(B) * PH * PW * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cl = static_cast<int>(i % tpr);
+    long long r = i / tpr;
+    const int pw = static_cast<int>(r % PW);
+    r /= PW;
+    const int ph = static_cast<int>(r % PH);
+    const long long b = r / PH;
+    const int8_t* base = s + ((b * H + 2 * ph) * W + 2 * pw) * C + cl * 16;
+    const uint4 a = *reinterpret_cast<const uint4*>(base);
+    const uint4 bq = *reinterpret_cast<const uint4*>(base + C);
+    const uint4 cq = *reinterpret_cast<const uint4*>(base + static_cast<long long>(W) * C);
+    const uint4 d = *reinterpret_cast<const uint4*>(base + static_cast<long long>(W) * C + C);
+    // bytes are 0x01 (+1) or 0xFF (-1): the bitwise AND of the four is 0x01 as soon as one of
+    // them is +1 and 0xFF only if all are -1, i.e. it is their maximum
+    uint4 m;
+    m.x = a.x & bq.x & cq.x & d.x;
+    m.y = a.y & bq.y & cq.y & d.y;
+    m.z = a.z & bq.z & cq.z & d.z;
+    m.w = a.w & bq.w & cq.w & d.w;
+    *reinterpret_cast<uint4*>(out + ((b * PH + ph) * PW + pw) * C + cl * 16) = m;
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // 2x2/2 'valid' max-pool on integer conv outputs, first maximum in row-major window order wins
 // (strict > replacement), fused with the BatchNorm statistics of the pooled map.
@@ -990,6 +1040,28 @@ ZKB_API int zkb_bn_finalize(const double* sum, const double* sumsq, double count
   return ZKB_OK;
 }
 
+ZKB_API int zkb_bn_sign_thresholds(const float* mean, const float* rstd, const float* beta, int C,
+                                   int* thr_i32, void* stream) {
+  ZKB_REQUIRE(mean && rstd && beta && thr_i32, "bn_sign_thresholds: null pointer");
+  ZKB_REQUIRE(C > 0, "bn_sign_thresholds: C must be positive");
+  bn_sign_threshold_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(mean, rstd, beta, C,
+                                                                                         thr_i32);
+  ZKB_LAUNCH_CHECK("bn_sign_threshold_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_maxpool2_sign_i8(const void* s_i8, int B, int H, int W, int C, void* out_i8, void* stream) {
+  ZKB_REQUIRE(s_i8 && out_i8, "maxpool2_sign_i8: null pointer");
+  ZKB_REQUIRE(B >= 0 && H >= 2 && W >= 2 && C > 0 && C % 16 == 0, "maxpool2_sign_i8: bad shape (C %% 16 == 0)");
+  ZKB_REQUIRE(ZKB_ALIGNED16(s_i8) && ZKB_ALIGNED16(out_i8), "maxpool2_sign_i8: pointers must be 16-byte aligned");
+  if (B == 0) return ZKB_OK;
+  const long long work = static_cast<long long>(B) * (H / 2) * (W / 2) * (C / 16);
+  maxpool2_sign_i8_kernel<<<grid_for(work, 256, 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const int8_t*>(s_i8), B, H, W, C, static_cast<int8_t*>(out_i8));
+  ZKB_LAUNCH_CHECK("maxpool2_sign_i8_kernel");
+  return ZKB_OK;
+}
+
 ZKB_API int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C, const float* mean,
                               const float* rstd, const float* beta, void* s_out_bf16, float* a_out,
                               void* s_out_i8, void* stream) {
@@ -1435,8 +1507,9 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
     uint16_t s[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) s[j] = pm1_bf16((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f);
-    *reinterpret_cast<uint2*>(s_out + pix * Cout + cl * 4) =
-        make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
+    if (s_out)
+      *reinterpret_cast<uint2*>(s_out + pix * Cout + cl * 4) =
+          make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
     if (s8_out) {
       uint32_t w8 = 0;
 #pragma unroll
@@ -1737,7 +1810,7 @@ ZKB_API int zkb_conv_first_bn_sign(const float* x, const float* wq_k_co, int B, 
                                    const float* beta, void* s_out_bf16, void* s_out_i8, void* stream) {
   int rc = first_conv_check("conv_first_bn_sign", x, wq_k_co, B, H, W, Cin, Cout, ksize);
   if (rc) return rc;
-  ZKB_REQUIRE(mean && rstd && beta && s_out_bf16, "conv_first_bn_sign: null pointer");
+  ZKB_REQUIRE(mean && rstd && beta && (s_out_bf16 || s_out_i8), "conv_first_bn_sign: null pointer");
   if (B == 0) return ZKB_OK;
   ZKB_FIRST_DISPATCH(conv_first_bn_sign_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
                      static_cast<uint16_t*>(s_out_bf16), static_cast<int8_t*>(s_out_i8));

@@ -62,6 +62,9 @@ struct KGemmParams {
   // (float64) -- what bn_stats_kernel computes from y in a second pass.
   int st_fused;
   double *st_sum, *st_sumsq;
+  // out_kind 2 (inference): BatchNorm + sign folded into one integer threshold per output channel;
+  // the epilogue writes int8 +1 where the int32 accumulator >= sign_thr[c], else -1.
+  const int* sign_thr;
   int bn_fused;
   const int16_t* bn_x;
   const float *bn_mean, *bn_rstd, *bn_beta;
@@ -373,7 +376,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     const int ew = warp - 2;
     const int q = warp & 3;        // TMEM lane quarter this warp may read
     const int half = ew >> 2;
-    const int unit_cols = p.out_kind == 0 ? 32 : 64;
+    const int unit_cols = p.out_kind == 0 ? 32 : (p.out_kind == 1 ? 64 : 128);
     const int units = (p.block_n + unit_cols - 1) / unit_cols;
     const uint32_t stage_box = smem_u32(smem + static_cast<size_t>(p.num_stages) * p.stage_bytes +
                                         1024 + static_cast<size_t>(ew) * 4096);
@@ -480,7 +483,29 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
         tmem_ld_wait();
         if (lane == 0) tma_store_wait_read_all();   // previous box of this warp has left smem
         __syncwarp();
-        if (p.out_kind == 0) {
+        if (p.out_kind == 2) {
+          // 128 int8 signs per row: four accumulator loads of 32 columns, two 16-byte chunks each
+#pragma unroll
+          for (int h = 0; h < 4; ++h) {
+            if (h > 0) {
+              if (c0 + 32 * h >= p.block_n) break;
+              tmem_ld_32x32(tbase + static_cast<uint32_t>(c0 + 32 * h), r);
+              tmem_ld_wait();
+            }
+            const int4* thr = reinterpret_cast<const int4*>(p.sign_thr + n0 + c0 + 32 * h);
+            uint32_t w[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int4 t = __ldg(thr + e);    // same address in every lane: one broadcast load
+              w[e] = ((static_cast<int>(r[4 * e]) >= t.x) ? 0x01u : 0xFFu) |
+                     ((static_cast<int>(r[4 * e + 1]) >= t.y) ? 0x0100u : 0xFF00u) |
+                     ((static_cast<int>(r[4 * e + 2]) >= t.z) ? 0x010000u : 0xFF0000u) |
+                     ((static_cast<int>(r[4 * e + 3]) >= t.w) ? 0x01000000u : 0xFF000000u);
+            }
+            st_shared_v4(my_row + ((static_cast<uint32_t>(2 * h) ^ sw) << 4), w[0], w[1], w[2], w[3]);
+            st_shared_v4(my_row + ((static_cast<uint32_t>(2 * h + 1) ^ sw) << 4), w[4], w[5], w[6], w[7]);
+          }
+        } else if (p.out_kind == 0) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             st_shared_v4(my_row + ((static_cast<uint32_t>(j) ^ sw) << 4), r[4 * j], r[4 * j + 1],
@@ -1099,19 +1124,22 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
                         int out_kind, long long ldo, long long M, int N, int K, int im2col, int NB,
                         int H, int W, int C, int ksize, int pad, cudaStream_t stream,
                         int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr,
-                        const BnBackwardFuse* bn = nullptr, const StatsFuse* st = nullptr) {
+                        const BnBackwardFuse* bn = nullptr, const StatsFuse* st = nullptr,
+                        const int* sign_thr = nullptr) {
   const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
   const CUtensorMapDataType dt =
       elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  ZKB_REQUIRE(elem_bytes == 2 || (elem_bytes == 1 && !A_lo && out_kind == 1),
+  ZKB_REQUIRE(elem_bytes == 2 || (elem_bytes == 1 && !A_lo && (out_kind == 1 || out_kind == 2)),
               "kgemm: int8 operands are for the single-term integer forward only");
   ZKB_REQUIRE(A_hi && Bmat && (out || l0), "kgemm: null pointer");
   ZKB_REQUIRE(M > 0 && N > 0 && K > 0, "kgemm: empty problem M=%lld N=%d K=%d", M, N, K);
   ZKB_REQUIRE(K % kelems == 0, "kgemm: K=%d must be a multiple of %d", K, kelems);
   ZKB_REQUIRE(M < (1ll << 31) - 256, "kgemm: M=%lld too large", M);
-  ZKB_REQUIRE(out_kind == 0 || out_kind == 1, "kgemm: out_kind must be 0 (f32) or 1 (i16)");
+  ZKB_REQUIRE(out_kind >= 0 && out_kind <= 2, "kgemm: out_kind must be 0 (f32), 1 (i16) or 2 (i8 sign)");
+  ZKB_REQUIRE(out_kind != 2 || (sign_thr && elem_bytes == 1 && (reinterpret_cast<uintptr_t>(sign_thr) & 15) == 0),
+              "kgemm: the sign output needs int8 operands and 16-byte aligned thresholds");
   ZKB_REQUIRE(ldo >= N, "kgemm: ldo=%lld < N=%d", ldo, N);
-  ZKB_REQUIRE((ldo * (out_kind == 0 ? 4 : 2)) % 16 == 0 &&
+  ZKB_REQUIRE((ldo * (out_kind == 0 ? 4 : (out_kind == 1 ? 2 : 1))) % 16 == 0 &&
                   (reinterpret_cast<uintptr_t>(out) & 15) == 0,
               "kgemm: output rows must be 16-byte aligned");
   ZKB_REQUIRE(!l0 || (out_kind == 0 && elem_bytes == 2 && N == 128 && im2col),
@@ -1157,6 +1185,12 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
       p.bn_x = bn->x; p.bn_mean = bn->mean; p.bn_rstd = bn->rstd; p.bn_beta = bn->beta;
       p.bn_sum_da = bn->sum_da; p.bn_sum_dax = bn->sum_dax;
     }
+  }
+  if (out_kind == 2) {
+    ZKB_REQUIRE(N % p.block_n == 0, "kgemm: sign output needs N=%d to be a multiple of the %d-column tile",
+                N, p.block_n);
+    ZKB_REQUIRE(!p.swap && !use_pairs, "kgemm: sign output is built for the one-CTA int8 forward");
+    p.sign_thr = sign_thr;
   }
   if (st) {
     ZKB_REQUIRE(out_kind == 1 && ldo == N && st->sum && st->sumsq,
@@ -1225,9 +1259,12 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   else if (out_kind == 0)
     rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, N, M,
                            static_cast<uint64_t>(ldo) * 4, 32, 32);
-  else
+  else if (out_kind == 1)
     rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, N, M,
                            static_cast<uint64_t>(ldo) * 2, 64, 32);
+  else
+    rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, out, N, M,
+                           static_cast<uint64_t>(ldo), 128, 32);
   if (rc) return rc;
 
   // layout: [stages][1 KB: barriers + TMEM slot][8 x 4 KB staging boxes] (+1 KB alignment slack)
@@ -1402,6 +1439,22 @@ ZKB_API int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, v
   StatsFuse st{sum, sumsq};
   return launch_kgemm(act_i8, nullptr, wq_n_k_i8, y_i16, 1, ldy, rows, N, K, 0, 0, 0, 0, 0, 0, 0,
                       static_cast<cudaStream_t>(stream), 1, nullptr, nullptr, &st);
+}
+
+ZKB_API int zkb_bconv2d_fwd_i8_sign(const void* act_i8, const void* wq_oc_k_i8, const int* thr,
+                                    void* s_out_i8, int NB, int H, int W, int Cin, int Cout,
+                                    int ksize, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_fwd_i8_sign: ksize must be odd");
+  return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, s_out_i8, 2, Cout,
+                      static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
+                      Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1, nullptr, nullptr,
+                      nullptr, thr);
+}
+
+ZKB_API int zkb_bdense_fwd_i8_sign(const void* act_i8, const void* wq_n_k_i8, const int* thr,
+                                   void* s_out_i8, long long lds, int rows, int K, int N, void* stream) {
+  return launch_kgemm(act_i8, nullptr, wq_n_k_i8, s_out_i8, 2, lds, rows, N, K, 0, 0, 0, 0, 0, 0, 0,
+                      static_cast<cudaStream_t>(stream), 1, nullptr, nullptr, nullptr, thr);
 }
 
 ZKB_API int zkb_bdense_fwd_i8(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,

@@ -133,6 +133,9 @@ class BinaryNetEngine:
         self.fuse_bn_backward_sums = os.environ.get("ZKB_FUSE_BN_BWD", "1") != "0"
         # BatchNorm batch statistics inside the forward GEMM epilogue (layers that do not pool)
         self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
+        # inference: BatchNorm + sign as integer thresholds inside the GEMM epilogue
+        self.fold_eval = self.forward_int8 and os.environ.get("ZKB_FOLD_EVAL", "1") != "0"
+        self._eval_ready = False
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
@@ -260,6 +263,7 @@ class BinaryNetEngine:
     # ------------------------------------------------------------------ parameters in / out
     def load_params(self, params: Dict[str, np.ndarray], moving: Optional[Dict[str, np.ndarray]] = None):
         """Inject weights in Keras layout: ``kernel{i}`` HWIO / [K, N], ``beta{i}`` [C]."""
+        self._eval_ready = False
         for L in self.L:
             k = torch.as_tensor(np.ascontiguousarray(params[f"kernel{L.idx}"]), dtype=torch.float32)
             if k.numel() != L.kernel.numel():
@@ -276,6 +280,7 @@ class BinaryNetEngine:
 
     def init_glorot(self, seed: int = 0):
         """Keras default (Glorot uniform) initialisation from ``numpy.random.default_rng(seed)``."""
+        self._eval_ready = False
         rng = np.random.default_rng(seed)
         params = {}
         for i, l in enumerate(self.layers):
@@ -652,6 +657,7 @@ class BinaryNetEngine:
 
     def optimizer_step(self, lr_dev: Optional[torch.Tensor] = None):
         """Adam + clip.  ``lr_dev``: read the step size from device memory (captured graphs)."""
+        self._eval_ready = False
         if lr_dev is None:
             self.step_count += 1
         lr_t = self._lr_t(max(self.step_count, 1))
@@ -669,6 +675,7 @@ class BinaryNetEngine:
 
         Everything is enqueued on the current CUDA stream; nothing synchronises with the host.
         Read :meth:`last_loss` / :meth:`last_accuracy` afterwards (that read synchronises)."""
+        self._eval_ready = False
         # per-launch timing of everything (watch is True) wants a serial schedule
         use_side = self.overlap and self.watch is not True
         caller = torch.cuda.current_stream(self.device)
@@ -735,6 +742,7 @@ class BinaryNetEngine:
     def train_step_graph(self, index: torch.Tensor) -> None:
         """Replay the captured step on the batch ``index`` (int32 device tensor of sample ids)."""
         caller = torch.cuda.current_stream(self.device)
+        self._eval_ready = False
         self.step_count += 1
         self.index_buf.copy_(index, non_blocking=True)
         self._dyn_step.fill_(self.step_count - 1)
@@ -749,14 +757,62 @@ class BinaryNetEngine:
         self._begin()
         self.acc.zero_()
         self.correct.zero_()
-        for L in self.L:
-            L.eval_rstd = torch.rsqrt(L.mv + BN_EPS)
+        if not self._eval_ready:
+            # weights and moving statistics only change in training steps: sign(W) layouts, the
+            # inference rstd and the folded thresholds are prepared once per run of eval steps
+            for L in self.L:
+                L.eval_rstd = torch.rsqrt(L.mv + BN_EPS)
+            self.prepare_weights()
+            if self.fold_eval:
+                for L in self.L[1:-1]:
+                    if not hasattr(L, "thr"):
+                        L.thr = torch.zeros(L.cp, dtype=torch.int32, device=self.device)
+                    self._call("zkb_bn_sign_thresholds", zn.ptr(L.mm), zn.ptr(L.eval_rstd), zn.ptr(L.beta), L.cp,
+                               zn.ptr(L.thr))
+            self._eval_ready = True
         self.preprocess(images_u8, labels_i64, index, False)
-        self.prepare_weights()
-        self.forward(training=False)
+        if self.fold_eval:
+            self._forward_eval_folded()
+        else:
+            self.forward(training=False)
         L = self.L[-1]
         self._call("zkb_softmax_ce", zn.ptr(L.logits), L.cp, zn.ptr(self.labels), self.B, self.num_classes,
                    1.0 / self.B, 0, self.acc[4 * self.n_beta:].data_ptr(), zn.ptr(self.correct))
+
+    def _forward_eval_folded(self):
+        """Inference forward with BatchNorm + sign folded into one integer threshold per channel
+        (SURVEY.md 8f.1): every hidden binary layer is ONE int8 GEMM whose epilogue compares the
+        int32 accumulator with the threshold and stores int8 signs -- no int16 map, no BatchNorm
+        pass; pooling layers take the maximum of the four signs (equal to the sign of the
+        normalised maximum because rstd > 0).  Bit-identical to ``forward(training=False)``."""
+        B = self.B
+        prev = None
+        last = len(self.L) - 1
+        for L in self.L:
+            l = L.spec
+            self._tag = f"fwd{L.idx}"
+            if L.idx == 0:
+                H, W, C = self.input_shape
+                self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), B, H, W, C, l.cout, l.ksize,
+                           zn.ptr(L.mm), zn.ptr(L.eval_rstd), zn.ptr(L.beta), 0, zn.ptr(L.s8))
+            elif L.idx == last:
+                self._call("zkb_bdense_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
+                self._call("zkb_bn_apply_sign", zn.ptr(L.y), 1, B, L.cp, zn.ptr(L.mm), zn.ptr(L.eval_rstd), zn.ptr(L.beta),
+                           0, zn.ptr(L.logits), 0)
+            else:
+                if l.kind == "conv":
+                    ih, iw = L.in_hw
+                    oh, ow = L.out_hw
+                    # pooling layers: full-resolution signs go into the (unused) int16 map's memory
+                    out = L.y.view(torch.int8) if l.pool else L.s8
+                    self._call("zkb_bconv2d_fwd_i8_sign", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.thr), zn.ptr(out),
+                               B, ih, iw, l.cin, l.cout, l.ksize)
+                    if l.pool:
+                        self._call("zkb_maxpool2_sign_i8", zn.ptr(out), B, oh, ow, L.cp, zn.ptr(L.s8))
+                else:
+                    self._call("zkb_bdense_fwd_i8_sign", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.thr), zn.ptr(L.s8),
+                               L.cp, B, l.cin, L.cp)
+            prev = L
 
     def last_loss(self) -> float:
         """Mean cross-entropy of the last step over this replica's batch (synchronises)."""

@@ -44,6 +44,10 @@ SIGNATURES = {
     "zkb_bdense_fwd": [P, P, P, L, I, I, I, P],
     "zkb_bconv2d_fwd_i8": [P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_fwd_i8": [P, P, P, L, I, I, I, P],
+    "zkb_bconv2d_fwd_i8_sign": [P, P, P, P, I, I, I, I, I, I, P],
+    "zkb_bdense_fwd_i8_sign": [P, P, P, P, L, I, I, I, P],
+    "zkb_bn_sign_thresholds": [P, P, P, I, P, P],
+    "zkb_maxpool2_sign_i8": [P, I, I, I, I, P, P],
     "zkb_bconv2d_fwd_i8_stats": [P, P, P, I, I, I, I, I, I, P, P, P],
     "zkb_bdense_fwd_i8_stats": [P, P, P, L, I, I, I, P, P, P],
     "zkb_bconv2d_dgrad": [P, P, P, P, I, I, I, I, I, I, P],
