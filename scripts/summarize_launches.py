@@ -12,6 +12,11 @@ for r in csv.DictReader(lines):
     if r.get("Metric Name") == "gpu__time_duration.sum":
         name = re.sub(r"\(.*", "", r["Kernel Name"]).replace("void ", "").strip()
         rows.append((name, float(r["Metric Value"].replace(",", "")) / 1e3, r["Grid Size"], r["Block Size"]))
+if len(sys.argv) > 2 and sys.argv[2] == "--last-step":
+    # one train step = the launches from one preprocess_kernel up to the next one
+    marks = [i for i, r in enumerate(rows) if r[0].endswith("preprocess_kernel")]
+    if len(marks) >= 2:
+        rows = rows[marks[-2]: marks[-1]]
 tot = sum(t for _, t, _, _ in rows)
 agg = defaultdict(lambda: [0, 0.0])
 for n, t, _, _ in rows:
