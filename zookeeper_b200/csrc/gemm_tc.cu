@@ -91,57 +91,46 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
 }
 
 // One epilogue unit of the fused first-layer backward: r[j] = gradient w.r.t. sign(a0) at pixel
-// pix0 + j of this thread's channel.  kGuard = false (every unit but the last of the problem) has
-// no per-pixel predicate, so the image loads of all 32 pixels can be scheduled ahead of their use.
-template <bool kGuard>
+// pix0 + j of this thread's channel.  Lane j works out where pixel pix0 + j's 3x3 window starts in
+// the image batch (the div/mod once per unit, SIMD across the warp); the pixel loop then gets that
+// offset with one shuffle and loads the nine taps with warp-uniform addresses (L1 broadcasts).
+// Pixels at or beyond M have r[j] == 0 exactly (zero-filled operand columns): they add nothing and
+// only their address is clamped.
 __device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uint32_t (&r)[32], int pix0,
-                                                 const float (&l0_w)[9], float l0_mu, float l0_rs,
-                                                 float l0_be, double (&l0_d)[11]) {
-            float f[11];
+                                                 int lane, const float (&l0_w)[9], float l0_mu,
+                                                 float l0_rs, float l0_be, double (&l0_d)[11]) {
+  unsigned pj = static_cast<unsigned>(pix0 + lane);
+  if (pj >= static_cast<unsigned>(p.M)) pj = static_cast<unsigned>(p.M) - 1u;
+  const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
+  const unsigned b = pj / hw;
+  const unsigned rem = pj - b * hw;
+  const unsigned oh = rem / static_cast<unsigned>(p.OW);
+  const unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
+  const unsigned my_off = (b * static_cast<unsigned>(p.l0_H) + oh) * static_cast<unsigned>(p.l0_W) + ow;
+  float f[11];
 #pragma unroll
-            for (int i = 0; i < 11; ++i) f[i] = 0.f;
-            const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
-            unsigned b = static_cast<unsigned>(pix0) / hw;
-            const unsigned rem = static_cast<unsigned>(pix0) - b * hw;
-            unsigned oh = rem / static_cast<unsigned>(p.OW);
-            unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
-            const float* base = p.l0_x + (static_cast<size_t>(b) * p.l0_H + oh) * p.l0_W + ow;
-            float win[3][3];   // sliding 3x3 window along the image row: 3 new taps per pixel
-            bool fresh = true;
+  for (int i = 0; i < 11; ++i) f[i] = 0.f;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              if (!kGuard || pix0 + j < p.M) {
-                if (fresh) {
+  for (int j = 0; j < 32; ++j) {
+    const float* q0 = p.l0_x + __shfl_sync(0xffffffffu, my_off, j);
+    const float* q1 = q0 + p.l0_W;
+    const float* q2 = q1 + p.l0_W;
+    float xv[9];
+    xv[0] = __ldg(q0); xv[1] = __ldg(q0 + 1); xv[2] = __ldg(q0 + 2);
+    xv[3] = __ldg(q1); xv[4] = __ldg(q1 + 1); xv[5] = __ldg(q1 + 2);
+    xv[6] = __ldg(q2); xv[7] = __ldg(q2 + 1); xv[8] = __ldg(q2 + 2);
+    float y = 0.f;
 #pragma unroll
-                  for (int kh = 0; kh < 3; ++kh)
+    for (int k = 0; k < 9; ++k) y = fmaf(xv[k], l0_w[k], y);   // same FMA order as the forward
+    const float xh = (y - l0_mu) * l0_rs;
+    const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
+    f[0] += da;
+    f[1] = fmaf(da, xh, f[1]);
 #pragma unroll
-                    for (int kw = 0; kw < 2; ++kw) win[kh][kw] = __ldg(base + kh * p.l0_W + kw);
-                  fresh = false;
-                }
+    for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(xv[k], da, f[2 + k]);
+  }
 #pragma unroll
-                for (int kh = 0; kh < 3; ++kh) win[kh][2] = __ldg(base + kh * p.l0_W + 2);
-                float y = 0.f;
-#pragma unroll
-                for (int k = 0; k < 9; ++k) y = fmaf(win[k / 3][k % 3], l0_w[k], y);
-                const float xh = (y - l0_mu) * l0_rs;
-                const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
-                f[0] += da;
-                f[1] = fmaf(da, xh, f[1]);
-#pragma unroll
-                for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(win[k / 3][k % 3], da, f[2 + k]);
-#pragma unroll
-                for (int kh = 0; kh < 3; ++kh) { win[kh][0] = win[kh][1]; win[kh][1] = win[kh][2]; }
-              }
-              ++base;
-              if (++ow == static_cast<unsigned>(p.OW)) {   // next image row (or next image)
-                ow = 0;
-                base += 2;
-                fresh = true;
-                if (++oh == static_cast<unsigned>(p.OH)) { oh = 0; base += 2 * p.l0_W; }
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
+  for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
 }
 
 // Column `lane` of the 32 x 32 f32 box a warp has just staged (row j at stage_box + 128 j, 16-byte
@@ -426,10 +415,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
             // r[j] = gradient w.r.t. sign(a0) at pixel pix0 + j, channel l0_c.  Recompute the
             // first conv at that pixel (9 taps, same FMA order as the forward kernels), apply the
             // ste mask and accumulate everything the first layer's backward needs.
-            if (pix0 + 32 <= p.M)
-              first_layer_unit<false>(p, r, pix0, l0_w, l0_mu, l0_rs, l0_be, l0_d);
-            else
-              first_layer_unit<true>(p, r, pix0, l0_w, l0_mu, l0_rs, l0_be, l0_d);
+            first_layer_unit(p, r, pix0, lane, l0_w, l0_mu, l0_rs, l0_be, l0_d);
             continue;
           }
           if (p.bn_fused) {   // thread = channel: r[j] is the gradient at pixel pix0 + j
