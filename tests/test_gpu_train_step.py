@@ -160,6 +160,39 @@ def test_bn_backward_sums_from_dgrad_epilogue_equal_the_reduction_kernel(native_
         assert _rel(ga[k], gb[k]) < 1e-5, k
 
 
+@pytest.mark.parametrize("B", [37, 64])
+def test_half_batch_forward_pipeline_equals_the_whole_batch_forward(native_lib, monkeypatch, B):
+    """_forward_pipelined (two half-batches on two streams) against forward(): identical integer
+    maps, signs, statistics and loss; gradients equal up to float summation order."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    params = O.glorot_uniform_params(O.binarynet_layers((28, 28, 1), 128, 1024, 10), 0)
+    rng = np.random.default_rng(B)
+    img = torch.as_tensor(rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)).cuda()
+    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
+    out = []
+    for pipe in ("1", "0"):
+        monkeypatch.setenv("ZKB_PIPELINE_FWD", pipe)
+        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+        assert eng._can_pipeline_forward() == (pipe == "1")
+        eng.load_params(params)
+        for step in range(2):      # the second step also exercises buffer reuse across steps
+            eng.train_step(img, lab, None, pad_size=32, seed=3, apply_update=False)
+        torch.cuda.synchronize()
+        maps = [L.y.cpu().numpy().copy() for L in eng.L[1:]] + [L.s8.cpu().numpy().copy() for L in eng.L[:-1]]
+        stats = torch.cat([torch.cat([L.mean, L.rstd]) for L in eng.L]).cpu().numpy()
+        out.append((maps, stats, eng.last_loss(), eng.get_grads(), eng.get_moving()))
+    (ma, sa, la, ga, va), (mb, sb, lb, gb, vb) = out
+    for k, (a, b) in enumerate(zip(ma, mb)):
+        assert np.array_equal(a, b), f"map {k} differs"
+    assert np.array_equal(sa, sb) and la == lb
+    for k in va:
+        assert np.array_equal(va[k], vb[k]), k
+    for k in ga:
+        assert _rel(ga[k], gb[k]) < 1e-5, k
+
+
 def test_second_step_from_engine_state(native_lib):
     """Step 2 (Adam t = 2, non-zero moments, re-prepared sign weights, in-kernel augmentation RNG).
 

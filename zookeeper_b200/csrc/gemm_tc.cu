@@ -21,6 +21,10 @@
 #include "zkb_host.h"
 #include "zkb_ptx.cuh"
 
+#ifndef ZKB_KGEMM_PLAIN_REGS
+#define ZKB_KGEMM_PLAIN_REGS 112   // register cap of the plain kgemm kernel (see kgemm_bf16_kernel)
+#endif
+
 namespace zkb {
 
 static constexpr int kMaxStages = 8;
@@ -164,10 +168,13 @@ __device__ __forceinline__ void bn_sums_from_box(const KGemmParams& p, uint32_t 
   acc_dax += sb;
 }
 
-__global__ void __launch_bounds__(320, 1)
-kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
-                  const KGemmParams p) {
+// kFirstLayer: the instantiation whose swap epilogue is the fused first-layer backward.  It needs
+// 168 registers per thread; the plain instantiation stays small enough that HBM-bound kernels of
+// another stream can share an SM with a resident GEMM CTA.
+template <bool kFirstLayer>
+__device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtensorMap& tmA1,
+                                           const CUtensorMap& tmB, const CUtensorMap& tmOut,
+                                           const KGemmParams& p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_1024(smem_raw);
   SharedCtl* ctl = reinterpret_cast<SharedCtl*>(smem + static_cast<size_t>(p.num_stages) * p.stage_bytes);
@@ -191,7 +198,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     tma_prefetch_desc(&tmA0);
     if (p.a_terms == 2) tma_prefetch_desc(&tmA1);
     tma_prefetch_desc(&tmB);
-    if (!p.l0_fused) tma_prefetch_desc(&tmOut);
+    if (!kFirstLayer) tma_prefetch_desc(&tmOut);
   }
   if (warp == 1) tmem_alloc_512(smem_u32(&ctl->tmem_base));
   tc_fence_before();
@@ -373,9 +380,9 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
     const uint32_t sw = static_cast<uint32_t>(lane & 7);
     // fused first-layer backward: this thread owns output channel l0_c for the whole kernel
     const int l0_c = q * 32 + lane;
-    float l0_w[9], l0_mu = 0.f, l0_rs = 0.f, l0_be = 0.f;
-    double l0_d[11];
-    if (p.l0_fused) {
+    float l0_w[kFirstLayer ? 9 : 1], l0_mu = 0.f, l0_rs = 0.f, l0_be = 0.f;
+    double l0_d[kFirstLayer ? 11 : 1];
+    if constexpr (kFirstLayer) {
 #pragma unroll
       for (int k = 0; k < 9; ++k) l0_w[k] = p.l0_wq[k * 128 + l0_c];
 #pragma unroll
@@ -411,7 +418,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
           uint32_t r[32];
           tmem_ld_32x32(tbase + static_cast<uint32_t>(u * 32), r);
           tmem_ld_wait();
-          if (p.l0_fused) {
+          if constexpr (kFirstLayer) {
             // r[j] = gradient w.r.t. sign(a0) at pixel pix0 + j, channel l0_c.  Recompute the
             // first conv at that pixel (9 taps, same FMA order as the forward kernels), apply the
             // ste mask and accumulate everything the first layer's backward needs.
@@ -570,7 +577,7 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
         }
       }
     }
-    if (p.l0_fused) {
+    if constexpr (kFirstLayer) {
 #pragma unroll
       for (int i = 0; i < 11; ++i) atomicAdd(p.l0_acc + i * 128 + l0_c, l0_d[i]);
     }
@@ -584,6 +591,20 @@ kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constan
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc_512(tmem_base);
+}
+
+__global__ void __maxnreg__(ZKB_KGEMM_PLAIN_REGS)
+kgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                  const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+                  const KGemmParams p) {
+  kgemm_body<false>(tmA0, tmA1, tmB, tmOut, p);
+}
+
+__global__ void __launch_bounds__(320, 1)
+kgemm_first_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                        const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+                        const KGemmParams p) {
+  kgemm_body<true>(tmA0, tmA1, tmB, tmOut, p);
 }
 
 // Per channel c and tap k: dbeta = sum da; dW0[k][c] = rstd_c * (S1 - mean(da) * S2[k] -
@@ -1257,6 +1278,8 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + 1024 + kEpiStagingBytes + 1024;
   ZKB_CUDA(cudaFuncSetAttribute(kgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 227 * 1024));
+  ZKB_CUDA(cudaFuncSetAttribute(kgemm_first_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                227 * 1024));
   const int tiles = p.tiles_m * p.tiles_n;
   const int sms = zkb_sm_count();
   if (use_pairs) {
@@ -1272,7 +1295,10 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   }
   int grid = tiles < sms ? tiles : sms;
   if ((p.bn_fused || p.st_fused) && grid > p.tiles_n) grid -= grid % p.tiles_n;
-  kgemm_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
+  if (p.l0_fused)
+    kgemm_first_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
+  else
+    kgemm_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
   ZKB_LAUNCH_CHECK("kgemm_bf16_kernel");
   if (st && !p.st_fused) return zkb_bn_stats(out, 1, M, N, st->sum, st->sumsq, stream);
   if (bn && !p.bn_fused)   // tile shapes without the fused epilogue: the stand-alone reduction

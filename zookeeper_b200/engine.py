@@ -135,6 +135,11 @@ class BinaryNetEngine:
         self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
         # inference: BatchNorm + sign as integer thresholds inside the GEMM epilogue
         self.fold_eval = self.forward_int8 and os.environ.get("ZKB_FOLD_EVAL", "1") != "0"
+        # training forward as two half-batches on two streams (see _forward_pipelined); off by
+        # default: measured r1, the HBM-bound kernels slow down 3x next to a resident GEMM CTA and
+        # the step does not get shorter (14.3 against 14.1 ms)
+        self.pipeline_forward = os.environ.get("ZKB_PIPELINE_FWD", "0") == "1"
+        self._pipe_events = {k: torch.cuda.Event() for k in ("fin", "s1", "g0", "p0")}
         self._eval_ready = False
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
@@ -466,6 +471,107 @@ class BinaryNetEngine:
                 self._bn_forward(L, L.y, True, B, fused_stats, training)
             prev = L
 
+    def _forward_pipelined(self, side):
+        """Training forward with the batch cut in two halves that follow each other through the
+        layers on two streams: while the tensor cores work on one half's GEMM, the HBM-bound
+        kernels of the other half (max-pool, BatchNorm + sign) run next to it.  Batch statistics
+        are sums, so both halves add into the same accumulators and a layer is normalised only
+        after both halves have passed its GEMM (and pooling).  Results are identical to
+        :meth:`forward` (same kernels on the same data).  Convolution layers only; the three
+        small dense layers run whole on the main stream."""
+        main = torch.cuda.current_stream(self.device)
+        B = self.B
+        n = (B // 2, B - B // 2)
+        off = (0, B // 2)
+        ev = self._pipe_events
+
+        def part(t, h):
+            return zn.ptr(t[off[h]: off[h] + n[h]]) if t is not None else 0
+
+        # ---- layer 0: statistics over the whole batch, sign per half
+        L = self.L[0]
+        l = L.spec
+        H, W, C = self.input_shape
+        self._tag = "fwd0"
+        self._call("zkb_conv_first_gram", zn.ptr(self.x0), B, H, W, self.l0_gram.data_ptr())
+        self._call("zkb_conv_first_stats_from_gram", self.l0_gram.data_ptr(), zn.ptr(L.wq), l.cout,
+                   zn.ptr(L.sum), zn.ptr(L.sumsq))
+        count = float(L.bn_rows)
+        if self.sync_bn:
+            self._pending_bn_sync(L)
+            count *= self.world
+        self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, 1, L.cp,
+                   zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
+        ev["fin"].record(main)
+        side.wait_event(ev["fin"])
+        for h, st in ((0, None), (1, side)):
+            self._call("zkb_conv_first_bn_sign", part(self.x0, h), zn.ptr(L.wq), n[h], H, W, C, l.cout, l.ksize,
+                       zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.beta), part(L.s, h), part(L.s8, h), on=st)
+        ev["s1"].record(side)                      # second half's signs are ready
+        prev = L
+        if self._prep_pending:
+            main.wait_event(self._prep_join)
+            self._prep_pending = False
+        # ---- binary conv layers
+        i = 1
+        while i < len(self.L) and self.L[i].spec.kind == "conv":
+            L = self.L[i]
+            l = L.spec
+            self._tag = f"fwd{i}"
+            ih, iw = L.in_hw
+            oh, ow = L.out_hw
+            for h in (0, 1):
+                if h == 1:
+                    main.wait_event(ev["s1"])      # the other half's input signs (side stream)
+                if l.pool:
+                    self._call("zkb_bconv2d_fwd_i8", part(prev.s8, h), zn.ptr(L.w_fwd8), part(L.y, h), n[h], ih, iw,
+                               l.cin, l.cout, l.ksize)
+                else:
+                    self._call("zkb_bconv2d_fwd_i8_stats", part(prev.s8, h), zn.ptr(L.w_fwd8), part(L.y, h), n[h], ih, iw,
+                               l.cin, l.cout, l.ksize, zn.ptr(L.sum), zn.ptr(L.sumsq))
+                if l.pool and h == 0:
+                    ev["g0"].record(main)          # first half pools next to the second half's GEMM
+                    side.wait_event(ev["g0"])
+                    self._call("zkb_maxpool2_i16", part(L.y, 0), n[0], oh, ow, L.cp, part(L.p, 0), part(L.arg, 0),
+                               zn.ptr(L.sum), zn.ptr(L.sumsq), on=side)
+                    ev["p0"].record(side)
+            if l.pool:
+                self._call("zkb_maxpool2_i16", part(L.y, 1), n[1], oh, ow, L.cp, part(L.p, 1), part(L.arg, 1),
+                           zn.ptr(L.sum), zn.ptr(L.sumsq))
+                main.wait_event(ev["p0"])
+            count = float(L.bn_rows)
+            if self.sync_bn:
+                self._pending_bn_sync(L)
+                count *= self.world
+            self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, 1, L.cp,
+                       zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
+            ev["fin"].record(main)
+            side.wait_event(ev["fin"])
+            x = L.p if l.pool else L.y
+            rows = L.bn_rows // B
+            for h, st in ((0, None), (1, side)):
+                self._call("zkb_bn_apply_sign", part(x, h), 1, rows * n[h], L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
+                           zn.ptr(L.beta), part(L.s, h), 0, part(L.s8, h), on=st)
+            ev["s1"].record(side)
+            prev = L
+            i += 1
+        main.wait_event(ev["s1"])
+        # ---- dense layers: whole batch on the main stream
+        for L in self.L[i:]:
+            l = L.spec
+            self._tag = f"fwd{L.idx}"
+            if self.fuse_forward_stats:
+                self._call("zkb_bdense_fwd_i8_stats", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp,
+                           zn.ptr(L.sum), zn.ptr(L.sumsq))
+            else:
+                self._call("zkb_bdense_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
+            self._bn_forward(L, L.y, True, B, self.fuse_forward_stats, True)
+            prev = L
+
+    def _can_pipeline_forward(self) -> bool:
+        return (self.pipeline_forward and self.forward_int8 and self.fuse_first_backward and self.fuse_forward_stats
+                and self.B >= 2 and self.layers[-1].kind == "dense")
+
     def _first_layer_forward(self, L, training: bool):
         l = L.spec
         H, W, C = self.input_shape
@@ -689,7 +795,10 @@ class BinaryNetEngine:
             if not preprocessed:
                 self.preprocess(images_u8, labels_i64, index, True, pad_size, aug, seed, self.step_count)
             self.prepare_weights(self._side if use_side else None)
-            self.forward(training=True)
+            if use_side and self._can_pipeline_forward():
+                self._forward_pipelined(self._side)
+            else:
+                self.forward(training=True)
             self.loss_and_grad()
             self.backward(self._side if use_side else None)
             if self.world > 1:
@@ -728,7 +837,10 @@ class BinaryNetEngine:
                 self.preprocess(images_u8, labels_i64, self.index_buf, True, pad_size, None, seed, 0,
                                 step_dev=self._dyn_step)
                 self.prepare_weights(self._side if self.overlap else None)
-                self.forward(training=True)
+                if self.overlap and self._can_pipeline_forward():
+                    self._forward_pipelined(self._side)
+                else:
+                    self.forward(training=True)
                 self.loss_and_grad()
                 self.backward(self._side if self.overlap else None)
                 if self.world > 1:
