@@ -1,0 +1,11 @@
+#!/bin/bash
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -30 | tee gpurun_out/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee gpurun_out/smoke.log
+echo "=== fwd8 (128-channel layer in swap mode)"; timeout 300 python scripts/bench_gemm.py fwd8
+echo "=== fwd8, swap off"; ZKB_KGEMM_SWAP=0 timeout 300 python scripts/bench_gemm.py fwd8 | head -1
+pr() { python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"; }
+for i in 1 2; do
+timeout 900 python bench.py --steps 20 --warmup 5 2>/dev/null > gpurun_out/bench2.json; echo -n "step: "; pr < gpurun_out/bench2.json
+done

@@ -445,6 +445,25 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           }
           if (lane == 0) tma_store_wait_read_all();
           __syncwarp();
+          if (p.out_kind == 1) {
+            // int16 output (the int8 forward of a 128-channel layer): rows of 32 channels = 64
+            // bytes, no swizzle; for a given pixel the 32 lanes write one contiguous row
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int v = p.is_i8 ? static_cast<int>(r[j]) : __float2int_rn(__uint_as_float(r[j]));
+              asm volatile("st.shared.b16 [%0], %1;" ::"r"(stage_box + static_cast<uint32_t>(j) * 64u +
+                                                           static_cast<uint32_t>(lane) * 2u),
+                           "h"(static_cast<short>(v))
+                           : "memory");
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmOut, stage_box, ch0, pix0);
+              tma_store_commit();
+            }
+            continue;
+          }
           const uint32_t lane_chunk = static_cast<uint32_t>(lane >> 2);
           const uint32_t lane_byte = static_cast<uint32_t>(lane & 3) * 4u;
 #pragma unroll
@@ -1164,7 +1183,12 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   // narrow f32-output layers (dgrad into 128 input channels): swap operand roles so that the
   // MMAs are 256 wide (see KGemmParams::swap)
   p.swap = (out_kind == 0 && elem_bytes == 2 && N % 128 == 0 && N < 256) ? 1 : 0;
-  if (const char* e = getenv("ZKB_KGEMM_SWAP")) p.swap = (atoi(e) && out_kind == 0 && elem_bytes == 2 && N % 128 == 0) ? 1 : 0;
+  // ... and the int8 forward of a 128-channel layer with int16 output (no fused statistics there)
+  if (out_kind == 1 && elem_bytes == 1 && N == 128 && ldo == N && !st) p.swap = 1;
+  if (const char* e = getenv("ZKB_KGEMM_SWAP")) {
+    if (!atoi(e)) p.swap = 0;
+    else if (out_kind == 0 && elem_bytes == 2 && N % 128 == 0) p.swap = 1;
+  }
   if (l0) {
     p.swap = 1;
     p.l0_fused = 1;
@@ -1266,6 +1290,9 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   else if (out_kind == 0)
     rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, N, M,
                            static_cast<uint64_t>(ldo) * 4, 32, 32);
+  else if (out_kind == 1 && p.swap)
+    rc = zkb_tmap_tiled_2d_plain(&tmOut, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, N, M,
+                                 static_cast<uint64_t>(ldo) * 2, 32, 32);
   else if (out_kind == 1)
     rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, N, M,
                            static_cast<uint64_t>(ldo) * 2, 64, 32);

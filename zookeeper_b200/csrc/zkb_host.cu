@@ -88,6 +88,29 @@ int zkb_tmap_tiled_2d(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, 
   return ZKB_OK;
 }
 
+int zkb_tmap_tiled_2d_plain(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, const void* base,
+                            uint64_t dim0, uint64_t dim1, uint64_t stride1_bytes, uint32_t box0,
+                            uint32_t box1) {
+  std::call_once(g_once, resolve_driver);
+  if (!g_encode_tiled)
+    return zkb_fail(ZKB_ERR_DRIVER, "cuTensorMapEncodeTiled is not available from the driver");
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || stride1_bytes % 16 != 0)
+    return zkb_fail(ZKB_ERR_ARG, "tensor-map base and row stride must be multiples of 16 bytes");
+  if ((box0 * static_cast<uint32_t>(elem_bytes)) % 16 != 0 || box0 == 0 || box0 > 256 || box1 == 0 || box1 > 256)
+    return zkb_fail(ZKB_ERR_ARG, "unswizzled tensor-map box rows must be a multiple of 16 bytes, 1..256 x 1..256");
+  cuuint64_t dims[2] = {dim0, dim1};
+  cuuint64_t strides[1] = {stride1_bytes};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode_tiled(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return zkb_fail(static_cast<int>(r), "cuTensorMapEncodeTiled failed with CUresult %d",
+                    static_cast<int>(r));
+  return ZKB_OK;
+}
+
 int zkb_tmap_im2col_nhwc(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes,
                          const void* base, int N, int H, int W, int C, int ksize, int pad,
                          uint32_t channels_per_pixel, uint32_t pixels_per_column) {

@@ -45,6 +45,11 @@ int zkb_fail(int code, const char* fmt, ...);
 int zkb_tmap_tiled_2d(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, const void* base,
                       uint64_t dim0, uint64_t dim1, uint64_t stride1_bytes, uint32_t box0,
                       uint32_t box1);
+// The same without shared-memory swizzle (box rows of any multiple of 16 bytes): store boxes that
+// threads fill row by row.
+int zkb_tmap_tiled_2d_plain(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, const void* base,
+                      uint64_t dim0, uint64_t dim1, uint64_t stride1_bytes, uint32_t box0,
+                      uint32_t box1);
 // NHWC activation [N,H,W,C]; 'same'-style window described by pad (lower) and ksize.
 int zkb_tmap_im2col_nhwc(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes,
                          const void* base, int N, int H, int W, int C, int ksize, int pad,
