@@ -123,6 +123,8 @@ int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i
  * int16 map is written.  Cout (N) must be a multiple of the tile width min(256, Cout).
  * zkb_maxpool2_sign_i8: 2x2/2 max-pool of such signs (= sign of the normalised pooled maximum,
  * because rstd > 0); C % 16 == 0. */
+/* rstd[c] = rsqrt(moving_var[c] + eps): the inference scale of BatchNormalization. */
+int zkb_bn_eval_rstd(const float* moving_var, float eps, int C, float* rstd, void* stream);
 int zkb_bn_sign_thresholds(const float* mean, const float* rstd, const float* beta, int C,
                            int* thr_i32, void* stream);
 int zkb_bconv2d_fwd_i8_sign(const void* act_i8, const void* wq_oc_k_i8, const int* thr, void* s_out_i8,

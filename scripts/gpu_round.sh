@@ -1,8 +1,11 @@
 #!/bin/bash
-# One GPU visit: parity tests, smoke, bench with per-kernel breakdown.
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -30 | tee gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee gpurun_out/smoke.log
 timeout 900 python bench.py --steps 20 --warmup 5 --breakdown > gpurun_out/bench.json 2> gpurun_out/bench_breakdown.txt
-echo "bench exit=$?"; cat gpurun_out/bench.json; grep TOTAL gpurun_out/bench_breakdown.txt | head -14
+echo "bench exit=$?"; grep TOTAL gpurun_out/bench_breakdown.txt | head -8
+pr() { python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'], d['e2e']['value'])"; }
+for i in 1 2; do
+timeout 900 python bench.py --steps 20 --warmup 5 2>/dev/null > gpurun_out/bench2.json; echo -n "step: "; pr < gpurun_out/bench2.json
+done

@@ -458,6 +458,14 @@ __global__ void bn_sign_threshold_kernel(const float* __restrict__ mean, const f
   thr[c] = hi;
 }
 
+// Inference scale from the moving variance: rstd = rsqrt(var + eps) (as bn_finalize_kernel does
+// for the batch variance).
+__global__ void bn_eval_rstd_kernel(const float* __restrict__ var, float eps, int C,
+                                    float* __restrict__ rstd) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < C) rstd[c] = rsqrtf(var[c] + eps);
+}
+
 // 2x2/2 max-pool of int8 signs: +1 if any of the four is +1 (= sign(BN(max y)) for rstd > 0).
 __global__ void __launch_bounds__(256)
 maxpool2_sign_i8_kernel(const int8_t* __restrict__ s, int B, int H, int W, int C,
@@ -1047,6 +1055,14 @@ ZKB_API int zkb_bn_sign_thresholds(const float* mean, const float* rstd, const f
   bn_sign_threshold_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(mean, rstd, beta, C,
                                                                                          thr_i32);
   ZKB_LAUNCH_CHECK("bn_sign_threshold_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_eval_rstd(const float* moving_var, float eps, int C, float* rstd, void* stream) {
+  ZKB_REQUIRE(moving_var && rstd, "bn_eval_rstd: null pointer");
+  ZKB_REQUIRE(C > 0, "bn_eval_rstd: C must be positive");
+  bn_eval_rstd_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(moving_var, eps, C, rstd);
+  ZKB_LAUNCH_CHECK("bn_eval_rstd_kernel");
   return ZKB_OK;
 }
 

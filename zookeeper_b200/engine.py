@@ -873,7 +873,9 @@ class BinaryNetEngine:
             # weights and moving statistics only change in training steps: sign(W) layouts, the
             # inference rstd and the folded thresholds are prepared once per run of eval steps
             for L in self.L:
-                L.eval_rstd = torch.rsqrt(L.mv + BN_EPS)
+                if getattr(L, "eval_rstd", None) is None:
+                    L.eval_rstd = torch.zeros_like(L.mv)
+                self._call("zkb_bn_eval_rstd", zn.ptr(L.mv), BN_EPS, L.cp, zn.ptr(L.eval_rstd))
             self.prepare_weights()
             if self.fold_eval:
                 for L in self.L[1:-1]:
