@@ -320,7 +320,9 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    // (the whole warp runs the loop: warp-uniform values stay in uniform registers and each
+    // tcgen05.mma is one instruction; an elected lane issues)
+    {
       const uint32_t idesc = p.is_i8 ? umma_idesc_s8(128, p.block_n) : umma_idesc_bf16(128, p.block_n, 0, 0);  // swap: block_n = 256 pixels
       int stage = 0;
       uint32_t phase = 0;
@@ -334,31 +336,38 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           mbar_wait(smem_u32(&ctl->full[stage]), phase);
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
-          const uint32_t sB = sA + static_cast<uint32_t>(p.a_terms) * kATileBytes;
-          for (int t = 0; t < p.a_terms; ++t) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              // swap: the weight tile (first 16 KB of the stage) is the M operand, the 256 pixel
-              // rows of term t are the N operand
-              const uint64_t ad = p.swap ? umma_smem_desc_sw128(sA + k * 32, 16, 1024)
-                                         : umma_smem_desc_sw128(sA + t * kATileBytes + k * 32, 16, 1024);
-              const uint64_t bd = p.swap ? umma_smem_desc_sw128(sA + kATileBytes + t * 2 * kATileBytes + k * 32, 16, 1024)
-                                         : umma_smem_desc_sw128(sB + k * 32, 16, 1024);
+          // Descriptors differ only in their start-address field (bytes >> 4): built once per
+          // stage, then one add per MMA -- the single issuing thread has to stay ahead of the
+          // tensor pipe.  swap: the weight tile (first 16 KB of the stage) is the M operand and
+          // the 256 pixel rows of term t the N operand; otherwise term t's tile is the M operand
+          // and the weight tile behind the terms the N operand.
+          const uint64_t m_desc = umma_smem_desc_sw128(sA, 16, 1024);
+          const uint64_t n_desc = umma_smem_desc_sw128(sA + (p.swap ? 1u : static_cast<uint32_t>(p.a_terms)) * kATileBytes, 16, 1024);
+          const uint64_t m_step = p.swap ? 0u : (kATileBytes >> 4), n_step = p.swap ? (2u * kATileBytes >> 4) : 0u;
+          if (elect_one()) {
+          if (!(p.dbg & 1)) {
+            for (int t = 0; t < p.a_terms; ++t) {
+              const uint64_t ad = m_desc + t * m_step, bd = n_desc + t * n_step;
               // a 128-byte row holds 64 bf16 or 128 int8: either way 4 MMAs of 32 bytes of K
-              if (p.dbg & 1) continue;
-              if (p.is_i8)
-                umma_i8(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
-              else
-                umma_f16(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              if (p.is_i8) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_i8(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              }
             }
           }
           umma_commit(smem_u32(&ctl->empty[stage]));
+          }
+          __syncwarp();
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(smem_u32(&ctl->tfull[as]));
+        if (elect_one()) umma_commit(smem_u32(&ctl->tfull[as]));
+        __syncwarp();
         as ^= 1;
         if (as == 0) aphase ^= 1u;
       }
@@ -757,7 +766,7 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (leader CTA only)
-    if (lane == 0 && leader) {
+    if (leader) {   // whole warp, an elected lane issues (see kgemm_body)
       const uint32_t idesc = p.is_i8 ? umma_idesc_s8(256, 256) : umma_idesc_bf16(256, 256, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
@@ -771,25 +780,29 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
           mbar_wait(smem_u32(&ctl->full[stage]), phase);
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
-          const uint32_t sB = sA + static_cast<uint32_t>(p.a_terms) * kATileBytes;
+          const uint64_t a_desc = umma_smem_desc_sw128(sA, 16, 1024);
+          const uint64_t bd = umma_smem_desc_sw128(sA + static_cast<uint32_t>(p.a_terms) * kATileBytes, 16, 1024);
+          if (elect_one()) {
           for (int t = 0; t < p.a_terms; ++t) {
+            const uint64_t ad = a_desc + static_cast<uint64_t>(t) * (kATileBytes >> 4);
+            if (p.is_i8) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint64_t ad = umma_smem_desc_sw128(sA + t * kATileBytes + k * 32, 16, 1024);
-              const uint64_t bd = umma_smem_desc_sw128(sB + k * 32, 16, 1024);
-              if (p.is_i8)
-                umma2_i8(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
-              else
-                umma2_f16(d_tmem, ad, bd, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < 4; ++k) umma2_i8(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
+            } else {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma2_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
             }
           }
           umma2_commit(smem_u32(&ctl->empty[stage]));   // frees the slot in both CTAs
+          }
+          __syncwarp();
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma2_commit(smem_u32(&ctl->tfull[as]));          // accumulator ready in both CTAs
+        if (elect_one()) umma2_commit(smem_u32(&ctl->tfull[as]));          // accumulator ready in both CTAs
+        __syncwarp();
         as ^= 1;
         if (as == 0) aphase ^= 1u;
       }
@@ -1037,7 +1050,10 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
+      // The whole warp runs this loop so that every value is warp-uniform (descriptors live in
+      // uniform registers and each tcgen05.mma is a single instruction instead of a per-thread
+      // operand loop); one elected lane issues the MMAs and the commits.
+      {
         const uint32_t idesc = umma_idesc_bf16(128, p.block_n, 1, 1);
         const int ksteps = p.kpix / 16;
         int stage = 0;
@@ -1047,27 +1063,35 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
           const uint32_t sB = sA + a_bytes;
+          // Descriptors differ only in their 14-bit start-address field: one add per MMA instead of
+          // rebuilding them (the single issuing thread must stay ahead of a 128-cycle MMA).
+          const uint64_t a_desc0 = umma_smem_desc_sw128(sA, box_bytes, 1024);
+          const uint64_t b_desc0 = umma_smem_desc_sw128(sB, box_bytes, 1024);
+          if (elect_one()) {
           for (int t = 0; t < tcount; ++t) {
             const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(t * p.block_n);
+            const uint64_t a_desc = a_desc0 + static_cast<uint64_t>((t * a_tile_bytes) >> 4);
             for (int bt = 0; bt < mma_terms; ++bt) {
-              for (int k = 0; k < ksteps; ++k) {
-                // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each); successive 64-wide
-                // channel blocks of an operand are box_bytes apart.
-                const uint64_t ad = umma_smem_desc_sw128(sA + t * a_tile_bytes + k * 2048,
-                                                         box_bytes, 1024);
-                const uint64_t bd = umma_smem_desc_sw128(sB + bt * b_term_bytes + k * 2048,
-                                                         box_bytes, 1024);
-                if (!(p.dbg & 1)) umma_f16(d_tmem, ad, bd, idesc, (ch | bt | k) != 0 ? 1u : 0u);
+              const uint64_t b_desc = b_desc0 + static_cast<uint64_t>((bt * b_term_bytes) >> 4);
+              // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each): 2048 B per k-step
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                if (k < ksteps && !(p.dbg & 1))
+                  umma_f16(d_tmem, a_desc + static_cast<uint64_t>(k * 128), b_desc + static_cast<uint64_t>(k * 128),
+                           idesc, (ch | bt | k) != 0 ? 1u : 0u);
               }
             }
           }
           umma_commit(smem_u32(&ctl->empty[stage]));
+          }
+          __syncwarp();
           if (++stage == p.num_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        umma_commit(smem_u32(&ctl->tfull));
+        if (elect_one()) umma_commit(smem_u32(&ctl->tfull));
+        __syncwarp();
       }
     } else {
       const int q = warp & 3;
