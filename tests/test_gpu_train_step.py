@@ -358,9 +358,17 @@ def test_training_learns_like_the_oracle_and_checkpoint_roundtrip(native_lib, tm
     # inference-mode accuracy is far from the batch-statistics one -- for BOTH implementations,
     # and by a similar amount (256 held-out samples: +-3 pt sampling noise each)
     assert acc_oracle > 0.2 and acc_engine > 0.2, (acc_oracle, acc_engine)
-    # (the two trajectories are not the same weights: any change of float summation order in a
-    # gradient kernel flips near-zero latent weights differently -- see the module docstring)
-    assert abs(acc_engine - acc_oracle) <= 0.12, (acc_oracle, acc_engine)
+    # The two trajectories do not hold the same weights (any change of float summation order in a
+    # gradient kernel flips near-zero latent weights differently -- see the module docstring), so
+    # their held-out accuracies are only loosely comparable.  What IS comparable: the oracle's
+    # inference on the ENGINE's trained weights and moving statistics must predict what the
+    # engine's validation pass predicts (same state, two implementations).
+    assert abs(acc_engine - acc_oracle) <= 0.25, (acc_oracle, acc_engine)
+    same_state = O.predict(eng.get_params(), eng.get_moving(), layers_o, xt)
+    got = ev.logits()
+    agree = (same_state.argmax(1) == got.argmax(1)).mean()
+    assert agree >= 0.98, agree                      # ties of near-equal logits aside
+    assert abs(float((same_state.argmax(1) == test_lab).mean()) - acc_engine) <= 0.02
     # the checkpoint holds exactly what the engine holds
     for k, a in eng.get_params().items():
         assert np.array_equal(a, ev.get_params()[k])

@@ -73,6 +73,8 @@ struct KGemmParams {
   const int16_t* bn_x;
   const float *bn_mean, *bn_rstd, *bn_beta;
   double *bn_sum_da, *bn_sum_dax;
+  int swap_boxes;  // swap mode: pixel boxes per tile and their height: 2 x 128 (default) or 3 x 64
+  int swap_box_px; // (192-pixel tiles: three 64 KB stages fit -- measured no faster than two of 80 KB)
   int swap;      // 1: operand roles swapped -- the MMA computes D^T[128 out channels, 256 pixels]
                  //    so that narrow (128-column) layers still issue 256-wide MMAs; f32 output only
   void* out;
@@ -210,20 +212,26 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
     // ------------------------------------------------------------ TMA producer
     // (whole warp, an elected lane issues: coordinates stay in uniform registers)
     if (p.swap) {
-      // stage layout: [W tile 128 x 128 B][X term 0: 256 pixel rows][X term 1: 256 pixel rows]
+      // stage layout: [W tile 128 x 128 B][X term 0: swap_boxes x 64 pixel rows][X term 1: ...]
+      const int nbox = p.swap_boxes, box_px = p.swap_box_px;
+      const uint32_t box_bytes = static_cast<uint32_t>(box_px) * 128u;
+      const uint32_t term_bytes = static_cast<uint32_t>(nbox) * box_bytes;
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int tm = tile / p.tiles_n;
         const int tn = tile - tm * p.tiles_n;
-        const int m0 = tm * 256;
+        const int m0 = tm * nbox * box_px;
         const int c0 = tn * 128;
-        int img[2] = {0, 0}, oh[2] = {0, 0}, ow[2] = {0, 0};
-        int live[2];
-        for (int h = 0; h < 2; ++h) {
-          const int mh = m0 + h * 128;
+        int img[4] = {0, 0, 0, 0}, oh[4] = {0, 0, 0, 0}, ow[4] = {0, 0, 0, 0};
+        int live[4] = {0, 0, 0, 0}, n_live = 0;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          if (h >= nbox) break;
+          const int mh = m0 + h * box_px;
           live[h] = mh < p.M;   // a box entirely beyond the last pixel is not loaded (its columns
                                 // of D^T are never stored)
+          n_live += live[h];
           if (p.a_im2col && live[h]) {
             const int hw = p.OH * p.OW;
             img[h] = mh / hw;
@@ -232,7 +240,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
             ow[h] = rem - oh[h] * p.OW;
           }
         }
-        const uint32_t tx = static_cast<uint32_t>(kATileBytes + p.a_terms * kATileBytes * (live[0] + live[1]));
+        const uint32_t tx = static_cast<uint32_t>(kATileBytes) + static_cast<uint32_t>(p.a_terms * n_live) * box_bytes;
         int cb = 0, kw = 0, kh = 0;   // k-block -> (filter tap, channel block), advanced without divisions
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
@@ -250,14 +258,15 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           tma_load_2d(sW, &tmB, full, kb * p.kelems, c0);
           for (int t = 0; t < p.a_terms; ++t) {
             const CUtensorMap* mp = t == 0 ? &tmA0 : &tmA1;
-            for (int h = 0; h < 2; ++h) {
-              if (!live[h]) continue;
-              const uint32_t dst = sX + static_cast<uint32_t>(t * 2 * kATileBytes + h * kATileBytes);
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              if (h >= nbox || !live[h]) continue;
+              const uint32_t dst = sX + static_cast<uint32_t>(t) * term_bytes + static_cast<uint32_t>(h) * box_bytes;
               if (p.a_im2col)
                 tma_load_im2col_4d(dst, mp, full, cb * p.kelems, ow[h] - p.pad, oh[h] - p.pad, img[h],
                                    static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
               else
-                tma_load_2d(dst, mp, full, kb * p.kelems, m0 + h * 128);
+                tma_load_2d(dst, mp, full, kb * p.kelems, m0 + h * box_px);
             }
           }
           }
@@ -351,7 +360,8 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           // and the weight tile behind the terms the N operand.
           const uint64_t m_desc = umma_smem_desc_sw128(sA, 16, 1024);
           const uint64_t n_desc = umma_smem_desc_sw128(sA + (p.swap ? 1u : static_cast<uint32_t>(p.a_terms)) * kATileBytes, 16, 1024);
-          const uint64_t m_step = p.swap ? 0u : (kATileBytes >> 4), n_step = p.swap ? (2u * kATileBytes >> 4) : 0u;
+          const uint64_t m_step = p.swap ? 0u : (kATileBytes >> 4);
+          const uint64_t n_step = p.swap ? (static_cast<uint32_t>(p.swap_boxes * p.swap_box_px) * 128u >> 4) : 0u;
           if (elect_one()) {
           if (!(p.dbg & 1)) {
             for (int t = 0; t < p.a_terms; ++t) {
@@ -429,8 +439,8 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
         // D^T: TMEM lane = output channel, column = pixel.  A unit is 32 pixels x this warp's 32
         // channels, transposed through the staging box (row = pixel, 4 bytes per lane).
         const int ch0 = tn * 128 + q * 32;
-        for (int u = half; u < 8; u += 2) {
-          const int pix0 = tm * 256 + u * 32;
+        for (int u = half; u < p.block_n / 32; u += 2) {
+          const int pix0 = tm * p.block_n + u * 32;
           if (pix0 >= p.M) break;
           uint32_t r[32];
           tmem_ld_32x32(tbase + static_cast<uint32_t>(u * 32), r);
@@ -1233,8 +1243,16 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     p.l0_acc = l0->acc; p.l0_H = l0->H; p.l0_W = l0->W;
   }
   if (p.swap) {
-    p.block_n = 256;
-    p.stage_bytes = kATileBytes + p.a_terms * 2 * kATileBytes;
+    // 256 pixels per tile as two 128-pixel boxes.  ZKB_SWAP_BOXES=3: 192 pixels as three 64-pixel
+    // boxes, which makes a two-term stage 64 KB so that three stages fit instead of two --
+    // measured r1 no faster (dgrad 1.37 against 1.34 ms, int8 forward 0.51 against 0.37).
+    p.swap_boxes = 2;
+    p.swap_box_px = 128;
+    if (const char* e = getenv("ZKB_SWAP_BOXES")) {
+      if (atoi(e) == 3) { p.swap_boxes = 3; p.swap_box_px = 64; }
+    }
+    p.block_n = p.swap_boxes * p.swap_box_px;
+    p.stage_bytes = kATileBytes + p.a_terms * p.block_n * 128;
   }
   // CTA pairs (cta_group::2) for layers at least 256 columns wide
   // (measured r1: +3..5 % for the two-term dgrad, -8 % for the int8 forward whose stages are
@@ -1275,7 +1293,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   p.tiles_m = static_cast<int>((M + 127) / 128);
   p.tiles_n = (N + p.block_n - 1) / p.block_n;
   if (p.swap) {
-    p.tiles_m = static_cast<int>((M + 255) / 256);
+    p.tiles_m = static_cast<int>((M + p.block_n - 1) / p.block_n);
     p.tiles_n = N / 128;
   }
   if (use_pairs) {
@@ -1298,21 +1316,23 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     p.pad = pad;
     p.kw_taps = ksize;
     p.cblocks = C / kelems;
-    rc = zkb_tmap_im2col_nhwc(&tmA0, dt, elem_bytes, A_hi, NB, H, W, C, ksize, pad, kelems, 128);
+    const int abox = p.swap ? p.swap_box_px : 128;   // pixel rows per A box
+    rc = zkb_tmap_im2col_nhwc(&tmA0, dt, elem_bytes, A_hi, NB, H, W, C, ksize, pad, kelems, abox);
     if (rc) return rc;
     tmA1 = tmA0;
     if (A_lo) {
-      rc = zkb_tmap_im2col_nhwc(&tmA1, dt, elem_bytes, A_lo, NB, H, W, C, ksize, pad, kelems, 128);
+      rc = zkb_tmap_im2col_nhwc(&tmA1, dt, elem_bytes, A_lo, NB, H, W, C, ksize, pad, kelems, abox);
       if (rc) return rc;
     }
   } else {
+    const int abox = p.swap ? p.swap_box_px : 128;
     rc = zkb_tmap_tiled_2d(&tmA0, dt, elem_bytes, A_hi, K, M, static_cast<uint64_t>(K) * elem_bytes,
-                           kelems, 128);
+                           kelems, abox);
     if (rc) return rc;
     tmA1 = tmA0;
     if (A_lo) {
       rc = zkb_tmap_tiled_2d(&tmA1, dt, elem_bytes, A_lo, K, M, static_cast<uint64_t>(K) * elem_bytes,
-                             kelems, 128);
+                             kelems, abox);
       if (rc) return rc;
     }
   }
@@ -1420,8 +1440,11 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   p.OW = W;
   p.ci_tiles = Ma / 128;
   p.n_tiles = N / p.cols_per_tile;
-  const int box_bytes = p.kpix * 128;
   const int boxes_b = p.b_terms * (p.concat ? 2 : p.block_n / 64);
+  // Three pipeline stages hide the TMA latency, two do not (measured r1: -5..12 % with three):
+  // when 64 reduction rows per stage leave room for only two stages, take 48.
+  if (!getenv("ZKB_WGRAD_KPIX") && kSmemBudget / ((p.tpi * 2 + boxes_b) * p.kpix * 128) < 3) p.kpix = 48;
+  const int box_bytes = p.kpix * 128;
   p.stage_bytes = (p.tpi * 2 + boxes_b) * box_bytes;
   p.num_stages = kSmemBudget / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
