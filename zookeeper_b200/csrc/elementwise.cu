@@ -1515,22 +1515,30 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
   for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
    typename FC::Row walk;
    walk.begin(x, row, H, W);
+   // output pointers of this thread's 4 channels, advanced by one pixel (Cout elements) per step
+   const size_t o0 = static_cast<size_t>(row) * OWr * Cout + cl * 4;
+   uint16_t* so = s_out ? s_out + o0 : nullptr;
+   int8_t* so8 = s8_out ? s8_out + o0 : nullptr;
    for (unsigned owi = 0; owi < OWr; ++owi) {
-    const long long pix = static_cast<long long>(row) * OWr + owi;
     float xv[FC::K], y[4];
     walk.step(owi, xv);
     FC::dot(xv, s_w, wr, Cout, cl * 4, y);
-    uint16_t s[4];
+    // bit j of neg: channel j's sign is -1 (a < 0; sign(0) = sign(-0.0) = +1 as everywhere)
+    uint32_t neg = 0;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) s[j] = pm1_bf16((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f);
-    if (s_out)
-      *reinterpret_cast<uint2*>(s_out + pix * Cout + cl * 4) =
-          make_uint2(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16));
-    if (s8_out) {
-      uint32_t w8 = 0;
-#pragma unroll
-      for (int e = 0; e < 4; ++e) w8 |= ((s[e] & 0x8000u) ? 0xFFu : 0x01u) << (8 * e);
-      *reinterpret_cast<uint32_t*>(s8_out + pix * Cout + cl * 4) = w8;
+    for (int j = 0; j < 4; ++j) neg |= (((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f) ? 0u : 1u) << j;
+    if (so) {    // bf16 +1 = 0x3F80, -1 = 0xBF80: the sign bits go to bits 15 and 31 of each pair
+      *reinterpret_cast<uint2*>(so) =
+          make_uint2(0x3F803F80u | ((neg & 1u) << 15) | ((neg & 2u) << 30),
+                     0x3F803F80u | ((neg & 4u) << 13) | ((neg & 8u) << 28));
+      so += Cout;
+    }
+    if (so8) {
+      // one byte per channel, 0x01 or 0xFF: spread bit j to bit 8j (the four partial products of
+      // the multiplication land on distinct bits), then 0x01 + 0xFE per negative byte
+      const uint32_t spread = (neg * 0x00204081u) & 0x01010101u;
+      *reinterpret_cast<uint32_t*>(so8) = spread * 0xFEu + 0x01010101u;
+      so8 += Cout;
     }
    }
   }
