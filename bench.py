@@ -179,7 +179,8 @@ def algorithmic_work(eng, name, tag):
         # epilogue (about 60 flop per output element: 9-tap conv, 2 + 18 accumulating FMAs)
         return ("flop", 2.0 * M * N * K + 60.0 * B * L.in_hw[0] * L.in_hw[1] * l.cin)
     if name in ("zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
-                "zkb_bconv2d_wgrad", "zkb_bdense_wgrad"):
+                "zkb_bconv2d_wgrad", "zkb_bdense_wgrad", "zkb_bconv2d_fwd_i8_stats", "zkb_bdense_fwd_i8_stats",
+                "zkb_bconv2d_dgrad_bn"):
         return ("flop", 2.0 * M * N * K)  # split terms are implementation overhead, not counted
     rows, C = L.bn_rows, L.cp
     xb = 4 if i == 0 else 2
@@ -190,6 +191,7 @@ def algorithmic_work(eng, name, tag):
         "zkb_bn_bwd_reduce": rows * C * (4 + xb),
         "zkb_bn_bwd_apply": rows * C * (4 + xb) + M * N * 4,
         "zkb_conv_first_bn_stats": B * 28 * 28 * 4,
+        "zkb_conv_first_gram": B * 28 * 28 * 4,
         "zkb_conv_first_bn_sign": M * N * 2 + B * 28 * 28 * 4,
         "zkb_conv_first_bwd_reduce": M * N * 4 + B * 28 * 28 * 4,
         "zkb_conv_first_bwd_wgrad": M * N * 4 + B * 28 * 28 * 4,
@@ -325,10 +327,11 @@ def main():
         if k["flop"]:
             # int8 pipe: no measured peak in MEASURED_PEAKS.json; 2x the measured bf16 figure
             # (the nominal int8:bf16 ratio) is used and said so
-            pk = peaks_tc * (2.0 if name.endswith("_i8") else 1.0)
+            is_i8 = "_i8" in name
+            pk = peaks_tc * (2.0 if is_i8 else 1.0)
             row.update({"achieved": round(k["flop"] / (k["ms"] * 1e-3) / 1e12, 1), "unit": "TFLOP/s", "bound": "tensor",
                         "peak": round(pk, 1), "frac": round(k["flop"] / (k["ms"] * 1e-3) / 1e12 / pk, 3)})
-            if name.endswith("_i8"):
+            if is_i8:
                 row["peak_note"] = "2 x measured bf16 sustained"
         elif k["byte"]:
             row.update({"achieved": round(k["byte"] / (k["ms"] * 1e-3) / 1e9, 0), "unit": "GB/s", "bound": "hbm",
