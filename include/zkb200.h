@@ -168,7 +168,19 @@ int zkb_bconv2d_dgrad_bn(const void* dy_hi, const void* dy_lo, const void* wq_ic
 int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, int NB,
                                 int H, int W, int Cin, int Cout, int ksize, const float* x0, int H0,
                                 int W0, const float* wq0_k_co, const float* mean0, const float* rstd0,
-                                const float* beta0, double* acc, void* stream);
+                                const float* beta0, const void* ste_mask, double* acc, void* stream);
+/* Mask mode (ste_mask != NULL): zkb_conv_first_bn_sign_mask is zkb_conv_first_bn_sign that also
+ * writes, per output pixel, 16 bytes of ste_sign mask (word j, bit l set: channel 4 l + j has
+ * |a| <= 1 and keeps its gradient; Cout == 128).  The fused dgrad then reads one mask word per
+ * element instead of recomputing the first conv, leaves acc[1][*] untouched, and
+ * zkb_conv_first_bwd_derive_dax fills it before the finalize:
+ *   acc[1][c] = sum da*xhat = rstd_c * (sum_k w_kc * acc[2+k][c] - mean_c * acc[0][c]). */
+int zkb_conv_first_bn_sign_mask(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
+                                int Cout, int ksize, const float* mean, const float* rstd,
+                                const float* beta, void* s_out_bf16, void* s_out_i8, void* ste_mask,
+                                void* stream);
+int zkb_conv_first_bwd_derive_dax(double* acc, const float* wq0_k_co, const float* mean0,
+                                  const float* rstd0, int Cout, void* stream);
 int zkb_conv_first_gram(const float* x0, int NB, int H0, int W0, double* gram, void* stream);
 int zkb_conv_first_stats_from_gram(const double* gram, const float* wq0_k_co, int Cout, double* sum,
                                    double* sumsq, void* stream);

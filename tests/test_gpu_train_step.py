@@ -103,11 +103,13 @@ def test_train_step_matches_oracle(native_lib, B):
             assert np.median(err) < 1e-4 and (err > 1e-2).mean() < 0.05, f"beta step {k}"
 
 
-@pytest.mark.parametrize("B", [5, 64])
-def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, monkeypatch):
+@pytest.mark.parametrize("B,mask", [(5, "1"), (64, "1"), (37, "0")])
+def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, mask, monkeypatch):
     """zkb_bconv2d_dgrad_first_bwd (+ finalize) against zkb_bconv2d_dgrad -> conv_first_bwd_reduce ->
     bn_bwd_finalize -> conv_first_bwd_wgrad on the same state: all gradients equal up to float
-    summation order."""
+    summation order.  mask = "1": the forward leaves the ste mask and the fused epilogue reads it
+    (zkb_conv_first_bn_sign_mask, zkb_conv_first_bwd_derive_dax); "0": the epilogue recomputes."""
+    monkeypatch.setenv("ZKB_FIRST_MASK", mask)
     from oracle import binarynet_oracle as O
     from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
 
@@ -128,7 +130,7 @@ def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, monke
     a, b = grads
     for k in a:
         if k in ("kernel0", "beta0"):
-            assert _rel(a[k], b[k]) < 2e-6, f"{k}: {_rel(a[k], b[k]):.3g}"
+            assert _rel(a[k], b[k]) < 5e-6, f"{k}: {_rel(a[k], b[k]):.3g}"
         else:       # same kernels on both sides (float atomics: summation order may differ)
             assert _rel(a[k], b[k]) < 1e-6, k
 

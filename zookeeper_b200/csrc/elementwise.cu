@@ -1492,12 +1492,12 @@ conv_first_bn_stats_kernel(const float* __restrict__ x, const float* __restrict_
   block_channel_reduce<4>(a0, a1, tpr, Cout, sum, sumsq);
 }
 
-template <int KS, int CIN>
-__global__ void __launch_bounds__(256)
-conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
+template <int KS, int CIN, bool kMask>
+__device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
                           int W, int Cout, const float* __restrict__ mean,
                           const float* __restrict__ rstd, const float* __restrict__ beta,
-                          uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out) {
+                          uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out,
+                          uint4* __restrict__ ste_mask) {
   using FC = FirstConv<KS, CIN>;
   float* s_w = first_conv_weights_smem();
   for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
@@ -1525,8 +1525,22 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
     FC::dot(xv, s_w, wr, Cout, cl * 4, y);
     // bit j of neg: channel j's sign is -1 (a < 0; sign(0) = sign(-0.0) = +1 as everywhere)
     uint32_t neg = 0;
+    float a[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) neg |= (((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f) ? 0u : 1u) << j;
+    for (int j = 0; j < 4; ++j) {
+      a[j] = (y[j] - mu[j]) * rs[j] + be[j];
+      neg |= ((a[j] >= 0.0f) ? 0u : 1u) << j;
+    }
+    if constexpr (kMask) {
+      // ste_sign keeps the gradient where |a| <= 1.  Cout == 128: the 32 threads of a warp hold the
+      // 128 channels of one pixel; word j of the pixel's 16 bytes gets bit l for channel 4 l + j.
+      uint4 m;
+      m.x = __ballot_sync(0xffffffffu, fabsf(a[0]) <= 1.0f);
+      m.y = __ballot_sync(0xffffffffu, fabsf(a[1]) <= 1.0f);
+      m.z = __ballot_sync(0xffffffffu, fabsf(a[2]) <= 1.0f);
+      m.w = __ballot_sync(0xffffffffu, fabsf(a[3]) <= 1.0f);
+      if (cl == 0) ste_mask[static_cast<size_t>(row) * OWr + owi] = m;
+    }
     if (so) {    // bf16 +1 = 0x3F80, -1 = 0xBF80: the sign bits go to bits 15 and 31 of each pair
       *reinterpret_cast<uint2*>(so) =
           make_uint2(0x3F803F80u | ((neg & 1u) << 15) | ((neg & 2u) << 30),
@@ -1542,6 +1556,25 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
     }
    }
   }
+}
+
+template <int KS, int CIN>
+__global__ void __launch_bounds__(256)
+conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H, int W,
+                          int Cout, const float* __restrict__ mean, const float* __restrict__ rstd,
+                          const float* __restrict__ beta, uint16_t* __restrict__ s_out,
+                          int8_t* __restrict__ s8_out) {
+  conv_first_bn_sign_body<KS, CIN, false>(x, wq, B, H, W, Cout, mean, rstd, beta, s_out, s8_out, nullptr);
+}
+
+template <int KS, int CIN>
+__global__ void __launch_bounds__(256, 3)
+conv_first_bn_sign_mask_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
+                               int W, int Cout, const float* __restrict__ mean,
+                               const float* __restrict__ rstd, const float* __restrict__ beta,
+                               uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out,
+                               uint4* __restrict__ ste_mask) {
+  conv_first_bn_sign_body<KS, CIN, true>(x, wq, B, H, W, Cout, mean, rstd, beta, s_out, s8_out, ste_mask);
 }
 
 template <int KS, int CIN>
@@ -1838,6 +1871,22 @@ ZKB_API int zkb_conv_first_bn_sign(const float* x, const float* wq_k_co, int B, 
   if (B == 0) return ZKB_OK;
   ZKB_FIRST_DISPATCH(conv_first_bn_sign_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
                      static_cast<uint16_t*>(s_out_bf16), static_cast<int8_t*>(s_out_i8));
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_conv_first_bn_sign_mask(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
+                                        int Cout, int ksize, const float* mean, const float* rstd,
+                                        const float* beta, void* s_out_bf16, void* s_out_i8,
+                                        void* ste_mask, void* stream) {
+  int rc = first_conv_check("conv_first_bn_sign_mask", x, wq_k_co, B, H, W, Cin, Cout, ksize);
+  if (rc) return rc;
+  ZKB_REQUIRE(mean && rstd && beta && ste_mask, "conv_first_bn_sign_mask: null pointer");
+  ZKB_REQUIRE(Cout == 128, "conv_first_bn_sign_mask: the mask layout is built for 128 channels");
+  ZKB_REQUIRE(ZKB_ALIGNED16(ste_mask), "conv_first_bn_sign_mask: mask must be 16-byte aligned");
+  if (B == 0) return ZKB_OK;
+  ZKB_FIRST_DISPATCH(conv_first_bn_sign_mask_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
+                     static_cast<uint16_t*>(s_out_bf16), static_cast<int8_t*>(s_out_i8),
+                     static_cast<uint4*>(ste_mask));
   return ZKB_OK;
 }
 

@@ -57,6 +57,10 @@ struct KGemmParams {
   const float* l0_rstd;
   const float* l0_beta;
   double* l0_acc;            // [11][128]: sum da, sum da*xhat, S1[k] = sum x_k*da (9 taps)
+  const uint32_t* l0_mask;   // optional ste mask written by the forward (16 B per pixel: word j, bit l
+                             // = channel 4l + j keeps its gradient).  With it the epilogue does not
+                             // recompute the first conv, and sum da*xhat is left to the finalize
+                             // kernel (it equals rstd * (sum_k w_k S1[k] - mean * sum da)).
   // BatchNorm-backward sums of the layer BELOW, fused into the f32 dgrad epilogue (swap mode and
   // CTA pairs): D[row][c] is the gradient w.r.t. that layer's sign output, bn_x its pre-BatchNorm
   // int16 map of the same shape; per channel sum da and sum da*xhat (da = D masked by |a| <= 1)
@@ -116,6 +120,32 @@ __device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uin
   float f[11];
 #pragma unroll
   for (int i = 0; i < 11; ++i) f[i] = 0.f;
+  if (p.l0_mask) {
+    const int c = static_cast<int>((threadIdx.x >> 5) & 3u) * 32 + lane;   // lane quarter * 32 + lane
+    const uint32_t* mrow = p.l0_mask + (c & 3);
+    const int bit = c >> 2;
+    const int last = p.M - 1 - pix0;
+    // all 32 mask words first (they come from L2 / HBM), then the taps (L1 hits)
+    uint32_t keep_bits = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      keep_bits |= ((__ldg(mrow + 4 * static_cast<size_t>(pix0 + (j < last ? j : last))) >> bit) & 1u) << j;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const uint32_t keep = (keep_bits >> j) & 1u;
+      const float* q0 = p.l0_x + __shfl_sync(0xffffffffu, my_off, j);
+      const float* q1 = q0 + p.l0_W;
+      const float* q2 = q1 + p.l0_W;
+      const float da = keep ? __uint_as_float(r[j]) : 0.f;
+      f[0] += da;
+      f[2] = fmaf(__ldg(q0), da, f[2]); f[3] = fmaf(__ldg(q0 + 1), da, f[3]); f[4] = fmaf(__ldg(q0 + 2), da, f[4]);
+      f[5] = fmaf(__ldg(q1), da, f[5]); f[6] = fmaf(__ldg(q1 + 1), da, f[6]); f[7] = fmaf(__ldg(q1 + 2), da, f[7]);
+      f[8] = fmaf(__ldg(q2), da, f[8]); f[9] = fmaf(__ldg(q2 + 1), da, f[9]); f[10] = fmaf(__ldg(q2 + 2), da, f[10]);
+    }
+#pragma unroll
+    for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
+    return;
+  }
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
     const float* q0 = p.l0_x + __shfl_sync(0xffffffffu, my_off, j);
@@ -653,6 +683,18 @@ kgemm_first_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
   kgemm_body<true>(tmA0, tmA1, tmB, tmOut, p);
 }
 
+// Mask mode of the fused epilogue leaves acc[1][c] = sum da*xhat to this kernel:
+//   sum_p da*xhat = rstd * (sum_p da*y - mean * sum_p da),  sum_p da*y = sum_k w_kc * S1[k][c]
+// (y is the first conv's output, linear in the taps).
+__global__ void conv_first_dax_from_s1_kernel(double* __restrict__ acc, const float* __restrict__ wq,
+                                              const float* __restrict__ mean,
+                                              const float* __restrict__ rstd) {
+  const int c = threadIdx.x;   // 128 threads
+  double day = 0.0;
+  for (int k = 0; k < 9; ++k) day += static_cast<double>(wq[k * 128 + c]) * acc[(2 + k) * 128 + c];
+  acc[128 + c] = static_cast<double>(rstd[c]) * (day - static_cast<double>(mean[c]) * acc[c]);
+}
+
 // Per channel c and tap k: dbeta = sum da; dW0[k][c] = rstd_c * (S1 - mean(da) * S2[k] -
 // mean(da*xhat) * S3[k][c]) from the sums the fused epilogue left.  S2[k] = sum x_k and
 // S3[k][c] = sum x_k * xhat_c = rstd_c * (sum_k' w_k'c G[k][k'] - mean_c S2[k]) do not depend on the
@@ -1175,6 +1217,7 @@ struct FirstLayerFuse {   // see KGemmParams::l0_fused
   const float *x, *wq, *mean, *rstd, *beta;
   double* acc;
   int H, W;
+  const uint32_t* mask;
 };
 
 struct BnBackwardFuse {   // see KGemmParams::bn_fused
@@ -1241,6 +1284,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     p.l0_fused = 1;
     p.l0_x = l0->x; p.l0_wq = l0->wq; p.l0_mean = l0->mean; p.l0_rstd = l0->rstd; p.l0_beta = l0->beta;
     p.l0_acc = l0->acc; p.l0_H = l0->H; p.l0_W = l0->W;
+    p.l0_mask = l0->mask;
   }
   if (p.swap) {
     // 256 pixels per tile as two 128-pixel boxes.  ZKB_SWAP_BOXES=3: 192 pixels as three 64-pixel
@@ -1592,16 +1636,26 @@ ZKB_API int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, co
                                         int NB, int H, int W, int Cin, int Cout, int ksize,
                                         const float* x0, int H0, int W0, const float* wq0_k_co,
                                         const float* mean0, const float* rstd0, const float* beta0,
-                                        double* acc, void* stream) {
+                                        const void* ste_mask, double* acc, void* stream) {
+  ZKB_REQUIRE((reinterpret_cast<uintptr_t>(ste_mask) & 15) == 0, "bconv2d_dgrad_first_bwd: mask must be 16-byte aligned");
   ZKB_REQUIRE(ksize == 3 && Cin == 128, "bconv2d_dgrad_first_bwd: built for 3x3 kernels into 128 channels");
   ZKB_REQUIRE(H0 == H + 2 && W0 == W + 2,
               "bconv2d_dgrad_first_bwd: first layer must be a 'valid' 3x3 conv (image %dx%d, map %dx%d)",
               H0, W0, H, W);
   ZKB_REQUIRE(x0 && wq0_k_co && mean0 && rstd0 && beta0 && acc, "bconv2d_dgrad_first_bwd: null pointer");
-  FirstLayerFuse l0{x0, wq0_k_co, mean0, rstd0, beta0, acc, H0, W0};
+  FirstLayerFuse l0{x0, wq0_k_co, mean0, rstd0, beta0, acc, H0, W0, static_cast<const uint32_t*>(ste_mask)};
   return launch_kgemm(dy_hi, dy_lo, wq_ic_k, nullptr, 0, Cin, static_cast<long long>(NB) * H * W, Cin,
                       ksize * ksize * Cout, 1, NB, H, W, Cout, ksize, ksize / 2,
                       static_cast<cudaStream_t>(stream), 2, &l0);
+}
+
+ZKB_API int zkb_conv_first_bwd_derive_dax(double* acc, const float* wq0_k_co, const float* mean0,
+                                          const float* rstd0, int Cout, void* stream) {
+  ZKB_REQUIRE(acc && wq0_k_co && mean0 && rstd0, "conv_first_bwd_derive_dax: null pointer");
+  ZKB_REQUIRE(Cout == 128, "conv_first_bwd_derive_dax: Cout must be 128");
+  conv_first_dax_from_s1_kernel<<<1, 128, 0, static_cast<cudaStream_t>(stream)>>>(acc, wq0_k_co, mean0, rstd0);
+  ZKB_LAUNCH_CHECK("conv_first_dax_from_s1_kernel");
+  return ZKB_OK;
 }
 
 ZKB_API int zkb_conv_first_bwd_finalize(const double* acc, const double* gram, const float* wq0_k_co,

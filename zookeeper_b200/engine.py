@@ -130,6 +130,9 @@ class BinaryNetEngine:
         self.fuse_first_backward = (os.environ.get("ZKB_FUSE_FIRST_BWD", "1") != "0"
                                     and self._can_fuse_first_backward())
         # BatchNorm-backward sums of layer i-1 inside layer i's dgrad epilogue (conv layers)
+        # the forward leaves the first layer's ste mask for the fused backward (opt-in: measured r1
+        # slower, +0.1 ms in the forward and no gain in the epilogue)
+        self.first_layer_mask = os.environ.get("ZKB_FIRST_MASK", "0") == "1"
         self.fuse_bn_backward_sums = os.environ.get("ZKB_FUSE_BN_BWD", "1") != "0"
         # BatchNorm batch statistics inside the forward GEMM epilogue (layers that do not pool)
         self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
@@ -192,6 +195,7 @@ class BinaryNetEngine:
         self.acc = torch.zeros(4 * self.n_beta + 2 + 11 * 128 + 90, dtype=torch.float64, device=dev)
         self.l0_acc = self.acc[4 * self.n_beta + 2: 4 * self.n_beta + 2 + 11 * 128]
         self.l0_gram = self.acc[4 * self.n_beta + 2 + 11 * 128:]
+        self.l0_mask = None      # ste mask of the first layer (16 B per output pixel), see _first_layer_forward
         self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
         self.stat = torch.zeros(4 * self.n_beta, dtype=f32, device=dev)  # mean, rstd, mean_da, mean_dax
         self.x0 = torch.zeros(B, H, W, C, dtype=f32, device=dev)
@@ -504,9 +508,17 @@ class BinaryNetEngine:
                    zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
         ev["fin"].record(main)
         side.wait_event(ev["fin"])
+        if self.first_layer_mask and self.l0_mask is None:
+            self.l0_mask = torch.zeros(L.bn_rows * 4, dtype=torch.int32, device=self.device)
+        per_img = (L.bn_rows // B) * 4            # mask words per image
         for h, st in ((0, None), (1, side)):
-            self._call("zkb_conv_first_bn_sign", part(self.x0, h), zn.ptr(L.wq), n[h], H, W, C, l.cout, l.ksize,
-                       zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.beta), part(L.s, h), part(L.s8, h), on=st)
+            if self.first_layer_mask:
+                self._call("zkb_conv_first_bn_sign_mask", part(self.x0, h), zn.ptr(L.wq), n[h], H, W, C, l.cout, l.ksize,
+                           zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.beta), part(L.s, h), part(L.s8, h),
+                           zn.ptr(self.l0_mask[off[h] * per_img:]), on=st)
+            else:
+                self._call("zkb_conv_first_bn_sign", part(self.x0, h), zn.ptr(L.wq), n[h], H, W, C, l.cout, l.ksize,
+                           zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.beta), part(L.s, h), part(L.s8, h), on=st)
         ev["s1"].record(side)                      # second half's signs are ready
         prev = L
         if self._prep_pending:
@@ -594,8 +606,16 @@ class BinaryNetEngine:
             mean, rstd = L.mean, L.rstd
         else:
             mean, rstd = L.mm, L.eval_rstd
-        self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
-                   zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
+        if training and self.fuse_first_backward and self.first_layer_mask:
+            # also leave the ste mask |a| <= 1 (one bit per element) for the fused backward, which
+            # then need not recompute the conv
+            if self.l0_mask is None:
+                self.l0_mask = torch.zeros(L.bn_rows * 4, dtype=torch.int32, device=self.device)
+            self._call("zkb_conv_first_bn_sign_mask", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
+                       zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8), zn.ptr(self.l0_mask))
+        else:
+            self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
+                       zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
 
     def _can_fuse_first_backward(self) -> bool:
         """zkb_bconv2d_dgrad_first_bwd is built for: 3x3 'valid' conv of one input channel into 128
@@ -623,7 +643,12 @@ class BinaryNetEngine:
         l = L1.spec
         self._call("zkb_bconv2d_dgrad_first_bwd", zn.ptr(L1.dy_hi), zn.ptr(L1.dy_lo), zn.ptr(L1.w_dgrad),
                    self.B, ih, iw, l.cin, l.cout, l.ksize, zn.ptr(self.x0), H, W, zn.ptr(L0.wq),
-                   zn.ptr(L0.mean), zn.ptr(L0.rstd), zn.ptr(L0.beta), self.l0_acc.data_ptr())
+                   zn.ptr(L0.mean), zn.ptr(L0.rstd), zn.ptr(L0.beta),
+                   zn.ptr(self.l0_mask) if self.first_layer_mask else 0, self.l0_acc.data_ptr())
+        self._tag = "bwd0"
+        if self.first_layer_mask:
+            self._call("zkb_conv_first_bwd_derive_dax", self.l0_acc.data_ptr(), zn.ptr(L0.wq), zn.ptr(L0.mean),
+                       zn.ptr(L0.rstd), L0.spec.cout)
         count = float(L0.bn_rows)
         if self.sync_bn:
             self._all_reduce(self.l0_acc[:256])      # sum da, sum da*xhat; the tap sums stay local

@@ -54,7 +54,9 @@ SIGNATURES = {
     "zkb_bconv2d_dgrad": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_dgrad": [P, P, P, P, I, I, I, P],
     "zkb_bconv2d_dgrad_bn": [P, P, P, P, I, I, I, I, I, I, P, P, P, P, P, P, P],
-    "zkb_bconv2d_dgrad_first_bwd": [P, P, P, I, I, I, I, I, I, P, I, I, P, P, P, P, P, P],
+    "zkb_bconv2d_dgrad_first_bwd": [P, P, P, I, I, I, I, I, I, P, I, I, P, P, P, P, P, P, P],
+    "zkb_conv_first_bn_sign_mask": [P, P, I, I, I, I, I, I, P, P, P, P, P, P, P],
+    "zkb_conv_first_bwd_derive_dax": [P, P, P, P, I, P],
     "zkb_conv_first_bwd_finalize": [P, P, P, P, P, D, D, P, P, I, P],
     "zkb_conv_first_gram": [P, I, I, I, P, P],
     "zkb_conv_first_stats_from_gram": [P, P, I, P, P, P],
