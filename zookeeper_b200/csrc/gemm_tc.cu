@@ -108,7 +108,7 @@ __device__ __forceinline__ uint8_t* align_1024(uint8_t* p) {
 // only their address is clamped.
 __device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uint32_t (&r)[32], int pix0,
                                                  int lane, const float (&l0_w)[9], float l0_mu,
-                                                 float l0_rs, float l0_be, double (&l0_d)[11]) {
+                                                 float l0_rs, float l0_be, float (&f)[11]) {
   unsigned pj = static_cast<unsigned>(pix0 + lane);
   if (pj >= static_cast<unsigned>(p.M)) pj = static_cast<unsigned>(p.M) - 1u;
   const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
@@ -117,9 +117,6 @@ __device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uin
   const unsigned oh = rem / static_cast<unsigned>(p.OW);
   const unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
   const unsigned my_off = (b * static_cast<unsigned>(p.l0_H) + oh) * static_cast<unsigned>(p.l0_W) + ow;
-  float f[11];
-#pragma unroll
-  for (int i = 0; i < 11; ++i) f[i] = 0.f;
   if (p.l0_mask) {
     const int c = static_cast<int>((threadIdx.x >> 5) & 3u) * 32 + lane;   // lane quarter * 32 + lane
     const uint32_t* mrow = p.l0_mask + (c & 3);
@@ -142,31 +139,36 @@ __device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uin
       f[5] = fmaf(__ldg(q1), da, f[5]); f[6] = fmaf(__ldg(q1 + 1), da, f[6]); f[7] = fmaf(__ldg(q1 + 2), da, f[7]);
       f[8] = fmaf(__ldg(q2), da, f[8]); f[9] = fmaf(__ldg(q2 + 1), da, f[9]); f[10] = fmaf(__ldg(q2 + 2), da, f[10]);
     }
-#pragma unroll
-    for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
     return;
   }
+  // Groups of four pixels: all 36 tap loads of a group are issued before the first FMA that
+  // needs one (the FMAs otherwise sit on the loads' scoreboard: 2 epilogue warps per scheduler
+  // cannot hide an L1 hit each).
 #pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    const float* q0 = p.l0_x + __shfl_sync(0xffffffffu, my_off, j);
-    const float* q1 = q0 + p.l0_W;
-    const float* q2 = q1 + p.l0_W;
-    float xv[9];
-    xv[0] = __ldg(q0); xv[1] = __ldg(q0 + 1); xv[2] = __ldg(q0 + 2);
-    xv[3] = __ldg(q1); xv[4] = __ldg(q1 + 1); xv[5] = __ldg(q1 + 2);
-    xv[6] = __ldg(q2); xv[7] = __ldg(q2 + 1); xv[8] = __ldg(q2 + 2);
-    float y = 0.f;
+  for (int j0 = 0; j0 < 32; j0 += 4) {
+    float xv[4][9];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) y = fmaf(xv[k], l0_w[k], y);   // same FMA order as the forward
-    const float xh = (y - l0_mu) * l0_rs;
-    const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j]);
-    f[0] += da;
-    f[1] = fmaf(da, xh, f[1]);
+    for (int u = 0; u < 4; ++u) {
+      const float* q0 = p.l0_x + __shfl_sync(0xffffffffu, my_off, j0 + u);
+      const float* q1 = q0 + p.l0_W;
+      const float* q2 = q1 + p.l0_W;
+      xv[u][0] = __ldg(q0); xv[u][1] = __ldg(q0 + 1); xv[u][2] = __ldg(q0 + 2);
+      xv[u][3] = __ldg(q1); xv[u][4] = __ldg(q1 + 1); xv[u][5] = __ldg(q1 + 2);
+      xv[u][6] = __ldg(q2); xv[u][7] = __ldg(q2 + 1); xv[u][8] = __ldg(q2 + 2);
+    }
 #pragma unroll
-    for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(xv[k], da, f[2 + k]);
+    for (int u = 0; u < 4; ++u) {
+      float y = 0.f;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) y = fmaf(xv[u][k], l0_w[k], y);   // same FMA order as the forward
+      const float xh = (y - l0_mu) * l0_rs;
+      const float da = (fabsf(xh + l0_be) > 1.0f) ? 0.f : __uint_as_float(r[j0 + u]);
+      f[0] += da;
+      f[1] = fmaf(da, xh, f[1]);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) f[2 + k] = fmaf(xv[u][k], da, f[2 + k]);
+    }
   }
-#pragma unroll
-  for (int i = 0; i < 11; ++i) l0_d[i] += f[i];
 }
 
 // Column `lane` of the 32 x 32 f32 box a warp has just staged (row j at stage_box + 128 j, 16-byte
@@ -439,6 +441,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
     const int l0_c = q * 32 + lane;
     float l0_w[kFirstLayer ? 9 : 1], l0_mu = 0.f, l0_rs = 0.f, l0_be = 0.f;
     double l0_d[kFirstLayer ? 11 : 1];
+    float l0_f[kFirstLayer ? 11 : 1];     // float partial sums of one tile (<= 128 pixels), then double
     if constexpr (kFirstLayer) {
 #pragma unroll
       for (int k = 0; k < 9; ++k) l0_w[k] = p.l0_wq[k * 128 + l0_c];
@@ -469,6 +472,10 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
         // D^T: TMEM lane = output channel, column = pixel.  A unit is 32 pixels x this warp's 32
         // channels, transposed through the staging box (row = pixel, 4 bytes per lane).
         const int ch0 = tn * 128 + q * 32;
+        if constexpr (kFirstLayer) {
+#pragma unroll
+          for (int i = 0; i < 11; ++i) l0_f[i] = 0.f;
+        }
         for (int u = half; u < p.block_n / 32; u += 2) {
           const int pix0 = tm * p.block_n + u * 32;
           if (pix0 >= p.M) break;
@@ -479,7 +486,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
             // r[j] = gradient w.r.t. sign(a0) at pixel pix0 + j, channel l0_c.  Recompute the
             // first conv at that pixel (9 taps, same FMA order as the forward kernels), apply the
             // ste mask and accumulate everything the first layer's backward needs.
-            first_layer_unit(p, r, pix0, lane, l0_w, l0_mu, l0_rs, l0_be, l0_d);
+            first_layer_unit(p, r, pix0, lane, l0_w, l0_mu, l0_rs, l0_be, l0_f);
             continue;
           }
           if (p.bn_fused) {   // thread = channel: r[j] is the gradient at pixel pix0 + j
@@ -538,6 +545,10 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
         }
         tc_fence_before();
         mbar_arrive(smem_u32(&ctl->tempty[as]));
+        if constexpr (kFirstLayer) {   // (after the accumulator stage is released)
+#pragma unroll
+          for (int i = 0; i < 11; ++i) l0_d[i] += l0_f[i];
+        }
         as ^= 1;
         if (as == 0) aphase ^= 1u;
         continue;
