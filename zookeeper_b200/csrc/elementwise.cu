@@ -1512,6 +1512,62 @@ __device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict_
   for (int j = 0; j < 4; ++j) { mu[j] = mean[cl * 4 + j]; rs[j] = rstd[cl * 4 + j]; be[j] = beta[cl * 4 + j]; }
   const unsigned OWr = W - KS + 1;
   const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
+  if constexpr (KS == 3 && CIN == 1 && !kMask) {
+    // One input channel: the 3x3 window slides by one column per pixel.  Three pixels per
+    // iteration, so that the three column registers rotate by renaming instead of moves, and row
+    // pointers that advance by three (tap loads with immediate offsets).
+    const unsigned OH = H - 2;
+    for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+      const unsigned b = row / OH, oh = row - b * OH;
+      const float* r0 = x + static_cast<size_t>(b * H + oh) * W;
+      const float* r1 = r0 + W;
+      const float* r2 = r1 + W;
+      const size_t o0 = static_cast<size_t>(row) * OWr * Cout + cl * 4;
+      uint16_t* so = s_out ? s_out + o0 : nullptr;
+      int8_t* so8 = s8_out ? s8_out + o0 : nullptr;
+      float c0[3] = {__ldg(r0), __ldg(r1), __ldg(r2)};             // input column ow
+      float c1[3] = {__ldg(r0 + 1), __ldg(r1 + 1), __ldg(r2 + 1)}; // input column ow + 1
+      float c2[3];
+      auto pixel = [&](const float (&a0)[3], const float (&a1)[3], const float (&a2)[3]) {
+        const float xv[9] = {a0[0], a1[0], a2[0], a0[1], a1[1], a2[1], a0[2], a1[2], a2[2]};
+        float y[4];
+        FC::dot(xv, s_w, wr, Cout, cl * 4, y);
+        uint32_t neg = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) neg |= (((y[j] - mu[j]) * rs[j] + be[j] >= 0.0f) ? 0u : 1u) << j;
+        if (so) {
+          *reinterpret_cast<uint2*>(so) =
+              make_uint2(0x3F803F80u | ((neg & 1u) << 15) | ((neg & 2u) << 30),
+                         0x3F803F80u | ((neg & 4u) << 13) | ((neg & 8u) << 28));
+          so += Cout;
+        }
+        if (so8) {
+          const uint32_t spread = (neg * 0x00204081u) & 0x01010101u;
+          *reinterpret_cast<uint32_t*>(so8) = spread * 0xFEu + 0x01010101u;
+          so8 += Cout;
+        }
+      };
+      unsigned ow = 0;
+      for (; ow + 3 <= OWr; ow += 3) {
+        c2[0] = __ldg(r0 + 2); c2[1] = __ldg(r1 + 2); c2[2] = __ldg(r2 + 2);
+        pixel(c0, c1, c2);
+        c0[0] = __ldg(r0 + 3); c0[1] = __ldg(r1 + 3); c0[2] = __ldg(r2 + 3);
+        pixel(c1, c2, c0);
+        c1[0] = __ldg(r0 + 4); c1[1] = __ldg(r1 + 4); c1[2] = __ldg(r2 + 4);
+        pixel(c2, c0, c1);
+        r0 += 3; r1 += 3; r2 += 3;
+      }
+      if (ow < OWr) {          // one or two pixels left
+        c2[0] = __ldg(r0 + 2); c2[1] = __ldg(r1 + 2); c2[2] = __ldg(r2 + 2);
+        pixel(c0, c1, c2);
+        if (ow + 1 < OWr) {
+          c0[0] = __ldg(r0 + 3); c0[1] = __ldg(r1 + 3); c0[2] = __ldg(r2 + 3);
+          pixel(c1, c2, c0);
+        }
+      }
+    }
+    return;
+  }
   for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
    typename FC::Row walk;
    walk.begin(x, row, H, W);
@@ -1559,7 +1615,7 @@ __device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict_
 }
 
 template <int KS, int CIN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H, int W,
                           int Cout, const float* __restrict__ mean, const float* __restrict__ rstd,
                           const float* __restrict__ beta, uint16_t* __restrict__ s_out,
