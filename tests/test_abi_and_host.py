@@ -192,3 +192,22 @@ def test_example_cli_configures_and_lowers_without_a_gpu():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "larq_experiment.py"), "BinaryNetMnist",
                         "epochs=0", "no_such_field=1"], capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode != 0 and "does not correspond to any field" in (r.stderr + r.stdout + str(r))
+
+
+def test_bench_reference_arm_prints_one_contract_line():
+    """`bench.py --impl reference` (the CPU restatement timed on host cores) prints exactly one JSON
+    line with the keys the driver reads; no GPU needed."""
+    import json
+
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "1"], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "BinaryNet train images/sec" and d["unit"] == "images/s"
+    assert d["higher_is_better"] is True and d["steps"] == 1 and d["warmup"] == 1 and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    assert d["e2e"]["value"] == d["value"] and "workload" in d["config"]
