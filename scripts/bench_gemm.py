@@ -12,8 +12,13 @@ LAYERS = [(26, 26, 128, 128), (13, 13, 128, 256), (13, 13, 256, 256), (6, 6, 256
 which = sys.argv[1:] or ["fwd", "fwd8", "dgrad", "wgrad"]
 
 
+ONCE = os.environ.get("GEMM_ONCE") == "1"      # one launch per kernel (profiling runs)
+
+
 def timeit(fn, n=8):
-    for _ in range(2):
+    if ONCE:
+        n = 1
+    for _ in range(0 if ONCE else 2):
         fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
