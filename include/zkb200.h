@@ -123,6 +123,22 @@ int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i
  * int16 map is written.  Cout (N) must be a multiple of the tile width min(256, Cout).
  * zkb_maxpool2_sign_i8: 2x2/2 max-pool of such signs (= sign of the normalised pooled maximum,
  * because rstd > 0); C % 16 == 0. */
+/* zkb_bn_finalize + zkb_bn_apply_sign in one launch: every thread derives mean / rstd of its
+ * channels from the batch sums with the arithmetic of zkb_bn_finalize (same floats), block 0 also
+ * stores them (mean_out, rstd_out: the backward reads them) and updates the moving statistics.
+ * zkb_bn_bwd_finalize_apply: the same for zkb_bn_bwd_finalize + zkb_bn_bwd_apply (dbeta, mean_da_out,
+ * mean_dax_out written by block 0).  At most 256 channel groups (C <= 1024 for f32, 2048 for int16). */
+int zkb_bn_finalize_apply_sign(const void* x, int x_is_i16, long long rows, int C, const double* sum,
+                               const double* sumsq, double count, float eps, float momentum, int bessel,
+                               const float* beta, float* mean_out, float* rstd_out, float* moving_mean,
+                               float* moving_var, void* s_out_bf16, float* a_out, void* s_out_i8,
+                               void* stream);
+int zkb_bn_bwd_finalize_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                              const float* mean, const float* rstd, const float* beta,
+                              const double* sum_da, const double* sum_dax, double count,
+                              double dbeta_scale, float* dbeta, float* mean_da_out, float* mean_dax_out,
+                              int ste, int out_mode, float* out_f32, void* out_hi, void* out_lo,
+                              const uint8_t* arg, int H, int W, void* stream);
 /* rstd[c] = rsqrt(moving_var[c] + eps): the inference scale of BatchNormalization. */
 int zkb_bn_eval_rstd(const float* moving_var, float eps, int C, float* rstd, void* stream);
 int zkb_bn_sign_thresholds(const float* mean, const float* rstd, const float* beta, int C,

@@ -195,6 +195,40 @@ def test_half_batch_forward_pipeline_equals_the_whole_batch_forward(native_lib, 
         assert _rel(ga[k], gb[k]) < 1e-5, k
 
 
+def test_finalize_folded_into_consumers_gives_the_same_numbers(native_lib, monkeypatch):
+    """zkb_bn_finalize_apply_sign / zkb_bn_bwd_finalize_apply against the separate finalize launches:
+    identical statistics, moving statistics, signs and loss; gradients up to float atomics order."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    B = 40
+    params = O.glorot_uniform_params(O.binarynet_layers((28, 28, 1), 128, 1024, 10), 0)
+    rng = np.random.default_rng(21)
+    img = torch.as_tensor(rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)).cuda()
+    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
+    out = []
+    for fold in ("1", "0"):
+        monkeypatch.setenv("ZKB_FOLD_FINALIZE", fold)
+        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+        assert eng.fold_finalize == (fold == "1")
+        eng.load_params(params)
+        eng.train_step(img, lab, None, pad_size=32, seed=3, apply_update=False)
+        torch.cuda.synchronize()
+        stats = torch.cat([torch.cat([L.mean, L.rstd, L.mean_da, L.mean_dax]) for L in eng.L[1:]]).cpu().numpy()
+        signs = [L.s8.cpu().numpy().copy() for L in eng.L[:-1]]
+        out.append((stats, signs, eng.last_loss(), eng.get_moving(), eng.get_grads(), eng.launches_per_step))
+    (sa, ga, la, ma, gra, na), (sb, gb, lb, mb, grb, nb) = out
+    assert na == nb - 16                 # 8 forward + 8 backward finalize launches fewer
+    assert la == lb
+    for a, b in zip(ga, gb):
+        assert np.array_equal(a, b)
+    for k in ma:
+        assert np.array_equal(ma[k], mb[k]), k
+    assert _rel(sa, sb) < 1e-6           # mean_da / mean_dax follow float-atomics-ordered gradients upstream
+    for k in gra:
+        assert _rel(gra[k], grb[k]) < 1e-5, k
+
+
 def test_second_step_from_engine_state(native_lib):
     """Step 2 (Adam t = 2, non-zero moments, re-prepared sign weights, in-kernel augmentation RNG).
 

@@ -364,13 +364,44 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sum, const double*
   }
 }
 
+// Optional fold of bn_finalize_kernel into its consumer: every thread derives mean / rstd of its
+// channels from the batch sums (same float64 arithmetic, hence the same floats), and the first
+// threads of block 0 also store them and update the moving statistics.  One launch less per layer.
+struct BnFoldFwd {
+  const double* sum;       // null: statistics are read from mean / rstd
+  const double* sumsq;
+  double count;
+  float eps, momentum;
+  int bessel;
+  float *mean_out, *rstd_out, *moving_mean, *moving_var;
+};
+
+__device__ __forceinline__ void bn_fold_channel(const BnFoldFwd& f, int c, bool writer, float& mean, float& rstd) {
+  const double m = f.sum[c] / f.count;
+  double var = f.sumsq[c] / f.count - m * m;
+  if (var < 0.0) var = 0.0;
+  const float meanf = static_cast<float>(m);
+  const float varf = static_cast<float>(var);
+  mean = meanf;
+  rstd = rsqrtf(varf + f.eps);
+  if (writer) {
+    f.mean_out[c] = meanf;
+    f.rstd_out[c] = rstd;
+    if (f.moving_mean) {
+      const float uv = (f.bessel && f.count > 1.0) ? static_cast<float>(var * (f.count / (f.count - 1.0))) : varf;
+      f.moving_mean[c] = f.moving_mean[c] * f.momentum + meanf * (1.0f - f.momentum);
+      f.moving_var[c] = f.moving_var[c] * f.momentum + uv * (1.0f - f.momentum);
+    }
+  }
+}
+
 // a = (x - mean) * rstd + beta ; s = sign(a) with sign(0) = +1, written as bf16 +-1.
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const float* __restrict__ beta,
                      uint16_t* __restrict__ s_out, float* __restrict__ a_out,
-                     int8_t* __restrict__ s8_out = nullptr) {
+                     int8_t* __restrict__ s8_out = nullptr, const BnFoldFwd fold = BnFoldFwd{}) {
   constexpr int VEC = Vec16<T>::N;
   const int tpr = C / VEC;
   const long long total = rows * tpr;
@@ -378,9 +409,15 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
   // its per-channel parameters live in registers for the whole loop.
   const int cl = threadIdx.x % tpr;
   float mu[VEC], rs[VEC], be[VEC];
+  const bool writer = blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tpr;
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
-    mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j]; be[j] = beta[cl * VEC + j];
+    if (fold.sum) {
+      bn_fold_channel(fold, cl * VEC + j, writer, mu[j], rs[j]);
+    } else {
+      mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j];
+    }
+    be[j] = beta[cl * VEC + j];
   }
   const long long gstride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long i0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i0 < total;
@@ -717,6 +754,14 @@ __global__ void bn_bwd_finalize_kernel(const double* __restrict__ sum_da,
 //   out_mode 1: bf16 hi/lo split [rows][C]
 //   out_mode 2: bf16 hi/lo split scattered through the 2x2 max-pool argmax into [B,H,W,C]
 //               (x, g and arg are pooled maps [B,H/2,W/2,C]; the three losers get zeros).
+// Optional fold of bn_bwd_finalize_kernel into bn_bwd_apply_kernel (see BnFoldFwd).
+struct BnFoldBwd {
+  const double* sum_da;    // null: the means are read from mean_da / mean_dax
+  const double* sum_dax;
+  double count, dbeta_scale;
+  float *dbeta, *mean_da_out, *mean_dax_out;
+};
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long long rows, int C,
@@ -724,7 +769,8 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
                     const float* __restrict__ beta, const float* __restrict__ mean_da,
                     const float* __restrict__ mean_dax, int ste, int out_mode,
                     float* __restrict__ out_f32, uint16_t* __restrict__ out_hi,
-                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W) {
+                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W,
+                    const BnFoldBwd fold = BnFoldBwd{}) {
   constexpr int VEC = 4;
   const int tpr = C / VEC;
   const long long total = rows * tpr;
@@ -732,9 +778,21 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
   const int cl = threadIdx.x % tpr;   // fixed per thread (blockDim and grid stride are multiples of tpr)
   float mu[VEC], rs[VEC], be[VEC], mda[VEC], mdx[VEC];
 #pragma unroll
+  const bool writer = blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tpr;
   for (int j = 0; j < VEC; ++j) {
     const int c = cl * VEC + j;
-    mu[j] = mean[c]; rs[j] = rstd[c]; be[j] = beta[c]; mda[j] = mean_da[c]; mdx[j] = mean_dax[c];
+    mu[j] = mean[c]; rs[j] = rstd[c]; be[j] = beta[c];
+    if (fold.sum_da) {
+      mda[j] = static_cast<float>(fold.sum_da[c] / fold.count);
+      mdx[j] = static_cast<float>(fold.sum_dax[c] / fold.count);
+      if (writer) {
+        if (fold.dbeta) fold.dbeta[c] = static_cast<float>(fold.sum_da[c] * fold.dbeta_scale);
+        fold.mean_da_out[c] = mda[j];
+        fold.mean_dax_out[c] = mdx[j];
+      }
+    } else {
+      mda[j] = mean_da[c]; mdx[j] = mean_dax[c];
+    }
   }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -1100,6 +1158,34 @@ ZKB_API int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C
   return ZKB_OK;
 }
 
+ZKB_API int zkb_bn_finalize_apply_sign(const void* x, int x_is_i16, long long rows, int C,
+                                       const double* sum, const double* sumsq, double count, float eps,
+                                       float momentum, int bessel, const float* beta, float* mean_out,
+                                       float* rstd_out, float* moving_mean, float* moving_var,
+                                       void* s_out_bf16, float* a_out, void* s_out_i8, void* stream) {
+  const int vec = x_is_i16 ? 8 : 4;
+  int rc = check_rows_c("bn_finalize_apply_sign", x, rows, C, vec);
+  if (rc) return rc;
+  ZKB_REQUIRE(sum && sumsq && beta && mean_out && rstd_out, "bn_finalize_apply_sign: null pointer");
+  ZKB_REQUIRE(count > 0.0 && rows > 0, "bn_finalize_apply_sign: count and rows must be positive");
+  ZKB_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr),
+              "bn_finalize_apply_sign: moving_mean and moving_var go together");
+  ZKB_REQUIRE(C / vec <= 256, "bn_finalize_apply_sign: at most %d channels", 256 * vec);
+  ZKB_REQUIRE(s_out_bf16 || a_out || s_out_i8, "bn_finalize_apply_sign: no output requested");
+  const BnFoldFwd fold{sum, sumsq, count, eps, momentum, bessel, mean_out, rstd_out, moving_mean, moving_var};
+  const int grid = grid_for(rows * (C / vec), 256, 16);
+  if (x_is_i16)
+    bn_apply_sign_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const int16_t*>(x), rows, C, nullptr, nullptr, beta,
+        static_cast<uint16_t*>(s_out_bf16), a_out, static_cast<int8_t*>(s_out_i8), fold);
+  else
+    bn_apply_sign_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const float*>(x), rows, C, nullptr, nullptr, beta, static_cast<uint16_t*>(s_out_bf16),
+        a_out, static_cast<int8_t*>(s_out_i8), fold);
+  ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
+  return ZKB_OK;
+}
+
 ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_out, uint8_t* arg_out,
                              double* sum, double* sumsq, void* stream) {
   int rc = check_rows_c("maxpool2_i16", y, static_cast<long long>(B) * H * W, C, 8);
@@ -1186,6 +1272,41 @@ ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long l
     bn_bwd_apply_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         g, static_cast<const float*>(x), rows, C, mean, rstd, beta, mean_da, mean_dax, ste,
         out_mode, out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W);
+  ZKB_LAUNCH_CHECK("bn_bwd_apply_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_bwd_finalize_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
+                                      const float* mean, const float* rstd, const float* beta,
+                                      const double* sum_da, const double* sum_dax, double count,
+                                      double dbeta_scale, float* dbeta, float* mean_da_out,
+                                      float* mean_dax_out, int ste, int out_mode, float* out_f32,
+                                      void* out_hi, void* out_lo, const uint8_t* arg, int H, int W,
+                                      void* stream) {
+  int rc = check_rows_c("bn_bwd_finalize_apply", g, rows, C, 4);
+  if (rc) return rc;
+  ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax && mean_da_out && mean_dax_out,
+              "bn_bwd_finalize_apply: null pointer");
+  ZKB_REQUIRE(count > 0.0 && rows > 0, "bn_bwd_finalize_apply: count and rows must be positive");
+  ZKB_REQUIRE(C / 4 <= 256, "bn_bwd_finalize_apply: at most 1024 channels");
+  ZKB_REQUIRE(out_mode >= 0 && out_mode <= 2, "bn_bwd_finalize_apply: out_mode must be 0, 1 or 2");
+  if (out_mode == 0) ZKB_REQUIRE(out_f32, "bn_bwd_finalize_apply: out_f32 is null");
+  if (out_mode >= 1) ZKB_REQUIRE(out_hi && out_lo, "bn_bwd_finalize_apply: hi/lo outputs are null");
+  if (out_mode == 2) {
+    ZKB_REQUIRE(arg && H >= 2 && W >= 2, "bn_bwd_finalize_apply: pool scatter needs argmax and H, W");
+    ZKB_REQUIRE(rows % (static_cast<long long>(H / 2) * (W / 2)) == 0,
+                "bn_bwd_finalize_apply: rows is not a multiple of the pooled map size");
+  }
+  const BnFoldBwd fold{sum_da, sum_dax, count, dbeta_scale, dbeta, mean_da_out, mean_dax_out};
+  const int grid = grid_for(rows * (C / 4), 256, 16);
+  if (x_is_i16)
+    bn_bwd_apply_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, nullptr, nullptr, ste, out_mode,
+        out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W, fold);
+  else
+    bn_bwd_apply_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        g, static_cast<const float*>(x), rows, C, mean, rstd, beta, nullptr, nullptr, ste, out_mode,
+        out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W, fold);
   ZKB_LAUNCH_CHECK("bn_bwd_apply_kernel");
   return ZKB_OK;
 }

@@ -47,6 +47,8 @@ SIGNATURES = {
     "zkb_bconv2d_fwd_i8_sign": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_fwd_i8_sign": [P, P, P, P, L, I, I, I, P],
     "zkb_bn_eval_rstd": [P, F, I, P, P],
+    "zkb_bn_finalize_apply_sign": [P, I, L, I, P, P, D, F, F, I, P, P, P, P, P, P, P, P, P],
+    "zkb_bn_bwd_finalize_apply": [P, P, I, L, I, P, P, P, P, P, D, D, P, P, P, I, I, P, P, P, P, I, I, P],
     "zkb_bn_sign_thresholds": [P, P, P, I, P, P],
     "zkb_maxpool2_sign_i8": [P, I, I, I, I, P, P],
     "zkb_bconv2d_fwd_i8_stats": [P, P, P, I, I, I, I, I, I, P, P, P],
