@@ -777,8 +777,8 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
   const int PH = H / 2, PW = W / 2;
   const int cl = threadIdx.x % tpr;   // fixed per thread (blockDim and grid stride are multiples of tpr)
   float mu[VEC], rs[VEC], be[VEC], mda[VEC], mdx[VEC];
-#pragma unroll
   const bool writer = blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tpr;
+#pragma unroll
   for (int j = 0; j < VEC; ++j) {
     const int c = cl * VEC + j;
     mu[j] = mean[c]; rs[j] = rstd[c]; be[j] = beta[c];
