@@ -1193,9 +1193,19 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const int col0 = tn * p.cols_per_tile + c * 32;
           if (row_in_tap < p.Ma) {
             float* o = p.out + orow * p.ldo + col0;
+            if (col0 + 32 <= p.n_valid && (p.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0) {
+              // whole 32-column chunk, 16-byte aligned rows: vector reductions (8 instead of 32)
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < p.n_valid) atomicAdd(o + j, __uint_as_float(r[j]));
+              for (int j = 0; j < 32; j += 4)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(o + j),
+                             "f"(__uint_as_float(r[j])), "f"(__uint_as_float(r[j + 1])),
+                             "f"(__uint_as_float(r[j + 2])), "f"(__uint_as_float(r[j + 3]))
+                             : "memory");
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col0 + j < p.n_valid) atomicAdd(o + j, __uint_as_float(r[j]));
+            }
           }
         }
       }
