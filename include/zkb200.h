@@ -123,22 +123,6 @@ int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i
  * int16 map is written.  Cout (N) must be a multiple of the tile width min(256, Cout).
  * zkb_maxpool2_sign_i8: 2x2/2 max-pool of such signs (= sign of the normalised pooled maximum,
  * because rstd > 0); C % 16 == 0. */
-/* zkb_bn_finalize + zkb_bn_apply_sign in one launch: every thread derives mean / rstd of its
- * channels from the batch sums with the arithmetic of zkb_bn_finalize (same floats), block 0 also
- * stores them (mean_out, rstd_out: the backward reads them) and updates the moving statistics.
- * zkb_bn_bwd_finalize_apply: the same for zkb_bn_bwd_finalize + zkb_bn_bwd_apply (dbeta, mean_da_out,
- * mean_dax_out written by block 0).  At most 256 channel groups (C <= 1024 for f32, 2048 for int16). */
-int zkb_bn_finalize_apply_sign(const void* x, int x_is_i16, long long rows, int C, const double* sum,
-                               const double* sumsq, double count, float eps, float momentum, int bessel,
-                               const float* beta, float* mean_out, float* rstd_out, float* moving_mean,
-                               float* moving_var, void* s_out_bf16, float* a_out, void* s_out_i8,
-                               void* stream);
-int zkb_bn_bwd_finalize_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
-                              const float* mean, const float* rstd, const float* beta,
-                              const double* sum_da, const double* sum_dax, double count,
-                              double dbeta_scale, float* dbeta, float* mean_da_out, float* mean_dax_out,
-                              int ste, int out_mode, float* out_f32, void* out_hi, void* out_lo,
-                              const uint8_t* arg, int H, int W, void* stream);
 /* rstd[c] = rsqrt(moving_var[c] + eps): the inference scale of BatchNormalization. */
 int zkb_bn_eval_rstd(const float* moving_var, float eps, int C, float* rstd, void* stream);
 int zkb_bn_sign_thresholds(const float* mean, const float* rstd, const float* beta, int C,
@@ -184,19 +168,7 @@ int zkb_bconv2d_dgrad_bn(const void* dy_hi, const void* dy_lo, const void* wq_ic
 int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, const void* wq_ic_k, int NB,
                                 int H, int W, int Cin, int Cout, int ksize, const float* x0, int H0,
                                 int W0, const float* wq0_k_co, const float* mean0, const float* rstd0,
-                                const float* beta0, const void* ste_mask, double* acc, void* stream);
-/* Mask mode (ste_mask != NULL): zkb_conv_first_bn_sign_mask is zkb_conv_first_bn_sign that also
- * writes, per output pixel, 16 bytes of ste_sign mask (word j, bit l set: channel 4 l + j has
- * |a| <= 1 and keeps its gradient; Cout == 128).  The fused dgrad then reads one mask word per
- * element instead of recomputing the first conv, leaves acc[1][*] untouched, and
- * zkb_conv_first_bwd_derive_dax fills it before the finalize:
- *   acc[1][c] = sum da*xhat = rstd_c * (sum_k w_kc * acc[2+k][c] - mean_c * acc[0][c]). */
-int zkb_conv_first_bn_sign_mask(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
-                                int Cout, int ksize, const float* mean, const float* rstd,
-                                const float* beta, void* s_out_bf16, void* s_out_i8, void* ste_mask,
-                                void* stream);
-int zkb_conv_first_bwd_derive_dax(double* acc, const float* wq0_k_co, const float* mean0,
-                                  const float* rstd0, int Cout, void* stream);
+                                const float* beta0, double* acc, void* stream);
 int zkb_conv_first_gram(const float* x0, int NB, int H0, int W0, double* gram, void* stream);
 int zkb_conv_first_stats_from_gram(const double* gram, const float* wq0_k_co, int Cout, double* sum,
                                    double* sumsq, void* stream);
@@ -286,14 +258,16 @@ int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, flo
  * cudaMalloc itself: an operator callback inside a runtime that owns the device allocator, or a
  * loop that cannot take the device-wide synchronisation cudaMalloc/cudaFree imply.  The call
  * allocates nothing.
- *   - Limit: C <= zkb_bn_train_sign_static_max_channels() (4096); larger C is refused with a
- *     negative status and a message naming the limit.
- *   - Every GPU that loads the library holds the array (about 96 KiB) until the process exits.
+ *   - Limit: C <= zkb_bn_train_sign_static_max_channels(x_is_i16): 2048 channels for int16 input,
+ *     1024 for f32 input, and C must be 8 (int16) or 4 (f32) times a power of two -- each thread of
+ *     the 256-thread blocks owns one 16-byte vector of channels.  Anything else is refused with a
+ *     negative status and a message naming the limit; nothing is launched.
+ *   - Every GPU that loads the library holds the array (48 KiB) until the process exits.
  *   - The first call on each device looks up the array's device address (that device must be
  *     current); make that first call before starting any stream capture.
  *   - All calls on a GPU share the array.  It is cleared on entry, so back-to-back calls on one
  *     stream are fine; calls that may overlap on the GPU (other streams, other threads) race. */
-int zkb_bn_train_sign_static_max_channels(void);
+int zkb_bn_train_sign_static_max_channels(int x_is_i16);
 int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows, int C, const float* beta,
                              float eps, float momentum, int bessel, float* moving_mean,
                              float* moving_var, void* s_out_bf16, float* a_out, void* stream);

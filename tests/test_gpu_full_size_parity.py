@@ -1,0 +1,295 @@
+"""Parity at BASELINE.json's headline size (configs[1]: batch 4096) against float64 / integer values
+computed on the CPU for SAMPLED entries of every contraction (oracle/sampled.py).
+
+At this size the GEMMs take paths the small oracle-compared tests never reach (persistent
+multi-tile loops, full-wave wgrad splits, 2-stage swap tiles, CTA pairs), and the whole-step CPU
+oracle does not fit.  So one train step is run and, layer by layer, the engine's OWN input maps of
+each GEMM are gathered on the GPU and the same entries are recomputed on the CPU -- each GEMM is
+checked in isolation:
+  * binary conv / dense forward: >= 2048 random output pixels x all channels, BIT-EXACT;
+  * dgrad: >= 2048 random input pixels x all channels of ds, 1e-5 (Frobenius over the sample);
+  * wgrad: 9 taps x 8 input x 32 output channels (a dot product over ALL pixels each), 1e-5;
+  * max-pool value and first-max slot, BatchNorm statistics, sign, BatchNorm backward (sums over all
+    rows of sampled channels, dy at all rows of those channels), loss, dbeta: 1e-4 or tighter.
+The ste mask |a| <= 1 is a discontinuity: an element whose |a| lies within float32 rounding of 1
+may legitimately be decided either way, and at 2.8 M pixels per channel a handful of those exist.
+Sums that depend on the mask are therefore compared with a slack equal to what those elements can
+contribute (oracle/sampled.py: bn_backward_columns), elementwise quantities skip them.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+B = 4096
+N_PIX = 2048
+GEMM_TOL = 1e-5
+STEP_TOL = 1e-4
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+def _f64(t):
+    return t.detach().double().cpu().numpy()
+
+
+def _patches(m, pix, flip):
+    """m [B,H,W,C] on the GPU, pix flat pixel ids -> [n,3,3,C]: patch[kh,kw] = m[p + (kh-1,kw-1)]
+    (flip: m[p - (kh-1,kw-1)]), zeros outside the image."""
+    Bn, H, W, C = m.shape
+    b, r = pix // (H * W), pix % (H * W)
+    y, x = r // W, r % W
+    out = torch.zeros(pix.numel(), 3, 3, C, dtype=m.dtype, device=m.device)
+    for kh in range(3):
+        for kw in range(3):
+            dy_, dx_ = (1 - kh, 1 - kw) if flip else (kh - 1, kw - 1)
+            yy, xx = y + dy_, x + dx_
+            ok = (yy >= 0) & (yy < H) & (xx >= 0) & (xx < W)
+            v = m[b, yy.clamp(0, H - 1), xx.clamp(0, W - 1)]
+            out[:, kh, kw] = torch.where(ok[:, None], v, torch.zeros_like(v))
+    return out
+
+
+def _shifted_columns(m, ch):
+    """m [B,H,W,C] -> int8 [9, B*H*W, len(ch)]: tap t = (kh,kw): m[p + (kh-1,kw-1), ch], zero padded."""
+    sub = m[..., ch].to(torch.int8)
+    Bn, H, W, n = sub.shape
+    pad = torch.nn.functional.pad(sub.permute(0, 3, 1, 2), (1, 1, 1, 1)).permute(0, 2, 3, 1)
+    return torch.stack([pad[:, kh:kh + H, kw:kw + W].reshape(-1, n) for kh in range(3) for kw in range(3)])
+
+
+def _hi_lo(L, rows=None, cols=None):
+    """dy of layer L as float64 = hi + lo (exactly what the backward GEMMs multiply)."""
+    hi, lo = L.dy_hi.reshape(-1, L.cp), L.dy_lo.reshape(-1, L.cp)
+    if rows is not None:
+        hi, lo = hi[rows], lo[rows]
+    if cols is not None:
+        hi, lo = hi[:, cols], lo[:, cols]
+    return _f64(hi) + _f64(lo)
+
+
+@pytest.fixture(scope="module")
+def step4096(native_lib):
+    """One batch-4096 step (no update, so kernels stay what the sign weights were prepared from) on
+    the default engine and on one with the separate first-layer backward kernels (it stores ds_0)."""
+    import os
+
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    g = torch.Generator(device="cpu").manual_seed(4096)
+    img = torch.randint(0, 256, (B, 28, 28, 1), generator=g, dtype=torch.uint8).cuda()
+    lab = torch.randint(0, 10, (B,), generator=g, dtype=torch.int64).cuda()
+    engines = []
+    saved = os.environ.get("ZKB_FUSE_FIRST_BWD")
+    try:
+        for fused in ("1", "0"):
+            os.environ["ZKB_FUSE_FIRST_BWD"] = fused
+            eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
+            eng.init_glorot(0)
+            # betas away from zero so that the ste mask and sign thresholds are not symmetric
+            rng = np.random.default_rng(5)
+            p = eng.get_params()
+            for k in p:
+                if k.startswith("beta"):
+                    p[k] = rng.normal(0, 0.3, p[k].shape).astype(np.float32)
+            eng.load_params(p)
+            eng.train_step(img, lab, None, pad_size=32, seed=77, apply_update=False)
+            torch.cuda.synchronize()
+            engines.append(eng)
+    finally:
+        if saved is None:
+            os.environ.pop("ZKB_FUSE_FIRST_BWD", None)
+        else:
+            os.environ["ZKB_FUSE_FIRST_BWD"] = saved
+    assert engines[0].fuse_first_backward and not engines[1].fuse_first_backward
+    return engines[0], engines[1], lab
+
+
+def _gen(seed):
+    return torch.Generator(device="cuda").manual_seed(seed)
+
+
+@pytest.mark.parametrize("i", [1, 2, 3, 4, 5])
+def test_binary_conv_layer_at_batch_4096(step4096, i):
+    from oracle import sampled as S
+
+    eng, eng_u, _ = step4096
+    L, P = eng.L[i], eng.L[i - 1]
+    l = L.spec
+    w = L.kernel.reshape(3, 3, l.cin, l.cout).cpu().numpy()
+    ih, iw = L.in_hw
+    oh, ow = L.out_hw
+    M = B * oh * ow
+    g = _gen(100 + i)
+    assert torch.equal(P.s.to(torch.int8), P.s8), "bf16 and int8 sign maps differ"
+
+    # ---- forward GEMM: exact integers
+    pix = torch.randint(0, M, (N_PIX,), device="cuda", generator=g)
+    y_ref = S.conv_forward_at(_patches(P.s8, pix, False).cpu().numpy(), w)
+    y_eng = L.y.reshape(-1, L.cp)[pix].cpu().numpy().astype(np.int64)
+    assert np.array_equal(y_eng, y_ref), f"layer {i}: forward integers differ"
+
+    # ---- max-pool: value and first-max slot (row-major window order, strict >)
+    x_map = L.y
+    if l.pool:
+        ph, pw = oh // 2, ow // 2
+        pp = torch.randint(0, B * ph * pw, (N_PIX,), device="cuda", generator=g)
+        b, r = pp // (ph * pw), pp % (ph * pw)
+        py, px = r // pw, r % pw
+        win = torch.stack([L.y[b, 2 * py + (k >> 1), 2 * px + (k & 1)] for k in range(4)]).cpu().numpy().astype(np.int64)
+        assert np.array_equal(L.p.reshape(-1, L.cp)[pp].cpu().numpy(), win.max(0))
+        assert np.array_equal(L.arg.reshape(-1, L.cp)[pp].cpu().numpy(), win.argmax(0))   # argmax = first maximum
+        x_map = L.p
+    rows = L.bn_rows
+
+    # ---- BatchNorm statistics, sign, backward on 16 sampled channels (all rows)
+    ch = torch.randperm(l.cout, device="cuda", generator=g)[:16].sort().values
+    chn = ch.cpu().numpy()
+    x = _f64(x_map.reshape(-1, L.cp)[:, ch])
+    mean_e, rstd_e, beta_e = (_f64(t[ch]) for t in (L.mean, L.rstd, L.beta))
+    assert np.allclose(mean_e, x.mean(0), rtol=1e-6, atol=1e-6)
+    assert np.allclose(rstd_e, 1.0 / np.sqrt(x.var(0) + 1e-3), rtol=1e-5)
+    a = (x - mean_e) * rstd_e + beta_e
+    s_eng = _f64(L.s8.reshape(-1, L.cp)[:, ch])
+    sure = np.abs(a) > 1e-5
+    assert np.array_equal(s_eng[sure], np.where(a >= 0, 1.0, -1.0)[sure]), f"layer {i}: sign map"
+
+    ds = _f64(L.ds.reshape(-1, L.cp)[:, ch])
+    r = S.bn_backward_columns(ds, x, mean_e, rstd_e, beta_e, ste=True)
+    for name, ref, slack in (("sum_da", r["sum_da"], r["slack_da"]), ("sum_dax", r["sum_dax"], r["slack_dax"])):
+        got = _f64(getattr(L, name)[ch])
+        assert S.excess(got - ref, slack) <= STEP_TOL * np.linalg.norm(ref), f"layer {i}: {name}"
+    assert S.excess(_f64(L.dbeta[ch]) - r["sum_da"], r["slack_da"]) <= STEP_TOL * np.linalg.norm(r["sum_da"])
+    # dy = BatchNorm backward with the ENGINE's means (their parity is the line above), scattered
+    # through the pool's first-max slot where the layer pools
+    mda, mdx = _f64(L.mean_da[ch]), _f64(L.mean_dax[ch])
+    da = np.where(np.abs(a) <= 1.0, ds, 0.0)
+    dy_ref = rstd_e * (da - mda - r["xhat"] * mdx)
+    keep = ~r["border"]
+    if l.pool:
+        ph, pw = oh // 2, ow // 2
+        arg = L.arg.reshape(-1, L.cp)[:, ch].cpu().numpy()
+        full = np.zeros((B, oh, ow, 16))
+        fkeep = np.ones((B, oh, ow, 16), dtype=bool)
+        d4, a4, k4 = dy_ref.reshape(B, ph, pw, 16), arg.reshape(B, ph, pw, 16), keep.reshape(B, ph, pw, 16)
+        for k in range(4):
+            sel = a4 == k
+            full[:, (k >> 1):2 * ph:2, (k & 1):2 * pw:2][sel] = d4[sel]
+            fkeep[:, (k >> 1):2 * ph:2, (k & 1):2 * pw:2] &= (k4 | ~sel)
+        dy_ref, keep = full.reshape(-1, 16), fkeep.reshape(-1, 16)
+    dy_eng = _hi_lo(L, cols=ch)
+    assert _rel(dy_eng * keep, dy_ref * keep) < GEMM_TOL, f"layer {i}: dy"
+
+    # ---- dgrad GEMM (output: gradient w.r.t. the previous sign map)
+    Pd = P if P.ds is not None else eng_u.L[i - 1]
+    src = L if P.ds is not None else eng_u.L[i]
+    qpix = torch.randint(0, B * ih * iw, (N_PIX,), device="cuda", generator=g)
+    dyp = _f64(_patches(src.dy_hi, qpix, True)) + _f64(_patches(src.dy_lo, qpix, True))
+    ds_ref = S.conv_dgrad_at(dyp[..., : l.cout], w)
+    assert _rel(_f64(Pd.ds.reshape(-1, l.cin)[qpix]), ds_ref) < GEMM_TOL, f"layer {i}: dgrad"
+
+    # ---- wgrad GEMM: every entry is a dot product over all B*oh*ow pixels
+    ci = torch.randperm(l.cin, device="cuda", generator=g)[:8].sort().values
+    co = torch.randperm(l.cout, device="cuda", generator=g)[:32].sort().values
+    dw_ref = S.conv_wgrad_entries(_shifted_columns(P.s, ci).cpu().numpy(), _hi_lo(L, cols=co))
+    dw_eng = _f64(L.dkernel.reshape(9, l.cin, l.cout)[:, ci][:, :, co])
+    assert _rel(dw_eng, dw_ref) < GEMM_TOL, f"layer {i}: wgrad"
+
+
+@pytest.mark.parametrize("i", [6, 7, 8])
+def test_binary_dense_layer_at_batch_4096(step4096, i):
+    from oracle import sampled as S
+
+    eng, _, lab = step4096
+    L, P = eng.L[i], eng.L[i - 1]
+    l = L.spec
+    last = i == len(eng.L) - 1
+    w = L.kernel.reshape(l.cin, l.cout).cpu().numpy()
+    g = _gen(200 + i)
+    s_prev8 = P.s8.reshape(B, -1)
+    assert torch.equal(P.s.reshape(B, -1).to(torch.int8), s_prev8)
+    # forward: every output (the layers are small enough), exact
+    y_ref = S.dense_forward(s_prev8.cpu().numpy(), w)
+    assert np.array_equal(L.y[:, : l.cout].cpu().numpy().astype(np.int64), y_ref)
+    # BatchNorm forward / backward, all channels
+    x = y_ref.astype(np.float64)
+    mean_e, rstd_e, beta_e = (_f64(t[: l.cout]) for t in (L.mean, L.rstd, L.beta))
+    assert np.allclose(mean_e, x.mean(0), rtol=1e-6, atol=1e-6)
+    assert np.allclose(rstd_e, 1.0 / np.sqrt(x.var(0) + 1e-3), rtol=1e-5)
+    a = (x - mean_e) * rstd_e + beta_e
+    if last:
+        assert _rel(eng.logits(), a) < 1e-6
+        z = a - a.max(1, keepdims=True)
+        lse = np.log(np.exp(z).sum(1))
+        lab_n = lab.cpu().numpy()
+        loss = float((lse - z[np.arange(B), lab_n]).mean())
+        assert abs(eng.last_loss() - loss) <= 1e-6 * abs(loss)
+        dlog = np.exp(z - lse[:, None])
+        dlog[np.arange(B), lab_n] -= 1.0
+        assert _rel(_f64(L.ds[:, : l.cout]), dlog / B) < 1e-5
+    else:
+        sure = np.abs(a) > 1e-5
+        assert np.array_equal(_f64(L.s8[:, : l.cout])[sure], np.where(a >= 0, 1.0, -1.0)[sure])
+    ds = _f64(L.ds[:, : l.cout])
+    r = S.bn_backward_columns(ds, x, mean_e, rstd_e, beta_e, ste=not last)
+    for name, ref, slack in (("sum_da", r["sum_da"], r["slack_da"]), ("sum_dax", r["sum_dax"], r["slack_dax"])):
+        got = _f64(getattr(L, name)[: l.cout])
+        assert S.excess(got - ref, slack) <= STEP_TOL * np.linalg.norm(ref), f"layer {i}: {name}"
+    assert S.excess(_f64(L.dbeta[: l.cout]) - r["sum_da"], r["slack_da"]) <= STEP_TOL * np.linalg.norm(r["sum_da"])
+    mda, mdx = _f64(L.mean_da[: l.cout]), _f64(L.mean_dax[: l.cout])
+    da = ds if last else np.where(np.abs(a) <= 1.0, ds, 0.0)
+    dy_ref = rstd_e * (da - mda - r["xhat"] * mdx)
+    keep = ~r["border"]
+    dy_eng = _hi_lo(L)[:, : l.cout]
+    assert _rel(dy_eng * keep, dy_ref * keep) < GEMM_TOL, f"layer {i}: dy"
+    if L.cp > l.cout:
+        assert float(_hi_lo(L)[:, l.cout:].__abs__().max()) == 0.0     # padded columns stay zero
+    # dgrad: 64 random rows x all K columns; wgrad: 64 x min(64, N) entries over all 4096 rows
+    rows = torch.randint(0, B, (64,), device="cuda", generator=g)
+    ds_ref = S.dense_dgrad(_hi_lo(L, rows=rows)[:, : l.cout], w)
+    assert _rel(_f64(P.ds.reshape(B, -1)[rows]), ds_ref) < GEMM_TOL, f"layer {i}: dgrad"
+    ks = torch.randperm(l.cin, device="cuda", generator=g)[:64].sort().values
+    ns = torch.randperm(l.cout, device="cuda", generator=g)[: min(64, l.cout)].sort().values
+    dw_ref = S.dense_wgrad_entries(s_prev8[:, ks].cpu().numpy(), _hi_lo(L, cols=ns))
+    assert _rel(_f64(L.dkernel.reshape(l.cin, l.cout)[ks][:, ns]), dw_ref) < GEMM_TOL, f"layer {i}: wgrad"
+
+
+def test_first_layer_at_batch_4096(step4096):
+    """The un-quantised first conv: sign map (forward), and the whole backward -- dbeta0 and dW0 of
+    16 sampled channels from the stored ds_0 of the separate-kernel engine, against BOTH engines
+    (fused dgrad epilogue and separate kernels)."""
+    from oracle import sampled as S
+
+    eng, eng_u, _ = step4096
+    L0 = eng.L[0]
+    assert np.array_equal(eng.x0.cpu().numpy(), eng_u.x0.cpu().numpy())
+    x0 = eng.x0[..., 0]
+    taps = torch.stack([x0[:, kh:kh + 26, kw:kw + 26].reshape(-1) for kh in range(3) for kw in range(3)], dim=1)
+    g = _gen(300)
+    ch = torch.randperm(128, device="cuda", generator=g)[:16].sort().values
+    wq = np.where(L0.kernel.reshape(9, 128).cpu().numpy() >= 0, 1.0, -1.0)[:, ch.cpu().numpy()]
+    assert np.array_equal(L0.wq.cpu().numpy()[:, ch.cpu().numpy()], wq.astype(np.float32))
+    ds0 = _f64(eng_u.L[0].ds.reshape(-1, 128)[:, ch])
+    beta = _f64(L0.beta[ch])
+    r = S.first_layer_backward_columns(_f64(taps), wq, ds0, beta)
+    # forward statistics (Gram-matrix path on eng, direct path on eng_u) and the sign map
+    for e in (eng, eng_u):
+        assert np.allclose(_f64(e.L[0].mean[ch]), r["mean"], rtol=1e-5, atol=1e-6)
+        assert np.allclose(_f64(e.L[0].rstd[ch]), r["rstd"], rtol=1e-5)
+    y = _f64(taps) @ wq
+    a = (y - r["mean"]) * r["rstd"] + beta
+    sure = np.abs(a) > 1e-4
+    assert np.array_equal(_f64(L0.s8.reshape(-1, 128)[:, ch])[sure], np.where(a >= 0, 1.0, -1.0)[sure])
+    # backward: both engines within 1e-4 of float64 up to the border elements
+    for e, what in ((eng, "fused"), (eng_u, "separate")):
+        E0 = e.L[0]
+        db = _f64(E0.dbeta[ch])
+        dw = _f64(E0.dkernel.reshape(9, 128)[:, ch])
+        assert S.excess(db - r["dbeta"], r["slack_dbeta"]) <= STEP_TOL * np.linalg.norm(r["dbeta"]), what
+        assert S.excess(dw - r["dw"], r["slack_dw"]) <= STEP_TOL * np.linalg.norm(r["dw"]), what
+    # ds_0 itself (layer 1's dgrad in swap mode, stored by the separate-kernel engine) is checked by
+    # test_binary_conv_layer_at_batch_4096[1]

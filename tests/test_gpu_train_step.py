@@ -103,13 +103,11 @@ def test_train_step_matches_oracle(native_lib, B):
             assert np.median(err) < 1e-4 and (err > 1e-2).mean() < 0.05, f"beta step {k}"
 
 
-@pytest.mark.parametrize("B,mask", [(5, "1"), (64, "1"), (37, "0")])
-def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, mask, monkeypatch):
+@pytest.mark.parametrize("B", [5, 37, 64])
+def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, monkeypatch):
     """zkb_bconv2d_dgrad_first_bwd (+ finalize) against zkb_bconv2d_dgrad -> conv_first_bwd_reduce ->
     bn_bwd_finalize -> conv_first_bwd_wgrad on the same state: all gradients equal up to float
-    summation order.  mask = "1": the forward leaves the ste mask and the fused epilogue reads it
-    (zkb_conv_first_bn_sign_mask, zkb_conv_first_bwd_derive_dax); "0": the epilogue recomputes."""
-    monkeypatch.setenv("ZKB_FIRST_MASK", mask)
+    summation order."""
     from oracle import binarynet_oracle as O
     from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
 
@@ -160,73 +158,6 @@ def test_bn_backward_sums_from_dgrad_epilogue_equal_the_reduction_kernel(native_
     assert _rel(sa, sb) < 1e-5          # float partial sums in a different order
     for k in ga:
         assert _rel(ga[k], gb[k]) < 1e-5, k
-
-
-@pytest.mark.parametrize("B", [37, 64])
-def test_half_batch_forward_pipeline_equals_the_whole_batch_forward(native_lib, monkeypatch, B):
-    """_forward_pipelined (two half-batches on two streams) against forward(): identical integer
-    maps, signs, statistics and loss; gradients equal up to float summation order."""
-    from oracle import binarynet_oracle as O
-    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
-
-    params = O.glorot_uniform_params(O.binarynet_layers((28, 28, 1), 128, 1024, 10), 0)
-    rng = np.random.default_rng(B)
-    img = torch.as_tensor(rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)).cuda()
-    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
-    out = []
-    for pipe in ("1", "0"):
-        monkeypatch.setenv("ZKB_PIPELINE_FWD", pipe)
-        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
-        assert eng._can_pipeline_forward() == (pipe == "1")
-        eng.load_params(params)
-        for step in range(2):      # the second step also exercises buffer reuse across steps
-            eng.train_step(img, lab, None, pad_size=32, seed=3, apply_update=False)
-        torch.cuda.synchronize()
-        maps = [L.y.cpu().numpy().copy() for L in eng.L[1:]] + [L.s8.cpu().numpy().copy() for L in eng.L[:-1]]
-        stats = torch.cat([torch.cat([L.mean, L.rstd]) for L in eng.L]).cpu().numpy()
-        out.append((maps, stats, eng.last_loss(), eng.get_grads(), eng.get_moving()))
-    (ma, sa, la, ga, va), (mb, sb, lb, gb, vb) = out
-    for k, (a, b) in enumerate(zip(ma, mb)):
-        assert np.array_equal(a, b), f"map {k} differs"
-    assert np.array_equal(sa, sb) and la == lb
-    for k in va:
-        assert np.array_equal(va[k], vb[k]), k
-    for k in ga:
-        assert _rel(ga[k], gb[k]) < 1e-5, k
-
-
-def test_finalize_folded_into_consumers_gives_the_same_numbers(native_lib, monkeypatch):
-    """zkb_bn_finalize_apply_sign / zkb_bn_bwd_finalize_apply against the separate finalize launches:
-    identical statistics, moving statistics, signs and loss; gradients up to float atomics order."""
-    from oracle import binarynet_oracle as O
-    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
-
-    B = 40
-    params = O.glorot_uniform_params(O.binarynet_layers((28, 28, 1), 128, 1024, 10), 0)
-    rng = np.random.default_rng(21)
-    img = torch.as_tensor(rng.integers(0, 256, (B, 28, 28, 1), dtype=np.uint8)).cuda()
-    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
-    out = []
-    for fold in ("1", "0"):
-        monkeypatch.setenv("ZKB_FOLD_FINALIZE", fold)
-        eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
-        assert eng.fold_finalize == (fold == "1")
-        eng.load_params(params)
-        eng.train_step(img, lab, None, pad_size=32, seed=3, apply_update=False)
-        torch.cuda.synchronize()
-        stats = torch.cat([torch.cat([L.mean, L.rstd, L.mean_da, L.mean_dax]) for L in eng.L[1:]]).cpu().numpy()
-        signs = [L.s8.cpu().numpy().copy() for L in eng.L[:-1]]
-        out.append((stats, signs, eng.last_loss(), eng.get_moving(), eng.get_grads(), eng.launches_per_step))
-    (sa, ga, la, ma, gra, na), (sb, gb, lb, mb, grb, nb) = out
-    assert na == nb - 16                 # 8 forward + 8 backward finalize launches fewer
-    assert la == lb
-    for a, b in zip(ga, gb):
-        assert np.array_equal(a, b)
-    for k in ma:
-        assert np.array_equal(ma[k], mb[k]), k
-    assert _rel(sa, sb) < 1e-6           # mean_da / mean_dax follow float-atomics-ordered gradients upstream
-    for k in gra:
-        assert _rel(gra[k], grb[k]) < 1e-5, k
 
 
 def test_second_step_from_engine_state(native_lib):
@@ -343,11 +274,16 @@ def test_cifar_shaped_config_matches_oracle(native_lib):
         assert _rel(g[k], v) < REL_TOL, f"grad {k}: rel {_rel(g[k], v):.3g}"
 
 
-def test_training_learns_like_the_oracle_and_checkpoint_roundtrip(native_lib, tmp_path):
+def test_training_converges_like_the_oracle_and_checkpoint_roundtrip(native_lib, tmp_path):
     """north_star: "final MNIST-shaped accuracy must agree within 0.5 pt".  MNIST itself is not
-    available offline, so both sides train on the same learnable MNIST-shaped task (10 fixed
-    prototypes + noise) with the same batches and augmentation, and are evaluated with moving
-    statistics on the same held-out set.  Also checks checkpoint save -> load -> identical eval."""
+    available offline, so both sides train TO CONVERGENCE on the same learnable MNIST-shaped task
+    (10 fixed prototypes + noise): 320 steps of batch 64 with the same batches and the same
+    augmentation stream, then inference with moving statistics on the same 2048 held-out samples.
+    Both must reach >= 97 % and agree within 0.5 pt.  (The two trajectories do not hold the same
+    weights -- float summation order flips near-zero latent weights differently, see the module
+    docstring -- which is why the criterion is the converged accuracy, as north_star states it.)
+    Also checks checkpoint save -> load -> identical eval, and that the oracle's inference on the
+    ENGINE's trained state predicts what the engine's validation pass predicts."""
     from oracle import binarynet_oracle as O
     from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
 
@@ -359,9 +295,8 @@ def test_training_learns_like_the_oracle_and_checkpoint_roundtrip(native_lib, tm
         img = np.clip(protos[lab] * 0.6 + rng.normal(60, 40, (n, 28, 28, 1)), 0, 255).astype(np.uint8)
         return img, lab
 
-    B, steps = 64, 24
-    train = [make(B) for _ in range(steps)]
-    test_img, test_lab = make(256)
+    B, steps, n_test = 64, 320, 2048
+    test_img, test_lab = make(n_test)
     layers_o = O.binarynet_layers()
     p = O.glorot_uniform_params(layers_o, 0)
     m = {k: np.zeros_like(v) for k, v in p.items()}
@@ -369,20 +304,20 @@ def test_training_learns_like_the_oracle_and_checkpoint_roundtrip(native_lib, tm
     mov = O.init_moving_stats(layers_o)
     eng = BinaryNetEngine(binarynet_layers(), (28, 28, 1), B, 10)
     eng.load_params(p)
-    for s, (img, lab) in enumerate(train):
+    for s in range(steps):
+        img, lab = make(B)
         aug = O.augmentation_params(11, s, B, 32, 28, 28)
         r = O.forward_backward(p, layers_o, O.preprocess(img, (28, 28), True, 32, aug), lab, torch.float32)
         p, m, v = O.adam_clip_step(p, r.grads, m, v, s + 1, dtype=np.float32)
         mov = O.update_moving_stats(mov, layers_o, r.batch_stats)
         eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda(), None, pad_size=32, seed=11)
-        if s >= steps - 4:   # both have learnt the task by now (batch-statistics accuracy)
-            assert r.accuracy > 0.5 and eng.last_accuracy() > 0.5, (s, r.accuracy, eng.last_accuracy())
-            assert abs(r.accuracy - eng.last_accuracy()) <= 0.15   # 64-sample batches: noisy
+        if s >= steps - 4:   # batch-statistics accuracy of the last steps: both have learnt the task
+            assert r.accuracy > 0.9 and eng.last_accuracy() > 0.9, (s, r.accuracy, eng.last_accuracy())
     torch.cuda.synchronize()
     xt = O.preprocess(test_img, (28, 28), False)
-    acc_oracle = float((O.predict(p, mov, layers_o, xt).argmax(1) == test_lab).mean())
+    acc_oracle = float((O.predict(p, mov, layers_o, xt, dtype=torch.float32).argmax(1) == test_lab).mean())
 
-    ev = BinaryNetEngine(binarynet_layers(), (28, 28, 1), 256, 10)
+    ev = BinaryNetEngine(binarynet_layers(), (28, 28, 1), n_test, 10)
     ck = str(tmp_path / "ck.npz")
     eng.save_checkpoint(ck)
     ev.load_checkpoint(ck)
@@ -390,21 +325,14 @@ def test_training_learns_like_the_oracle_and_checkpoint_roundtrip(native_lib, tm
     ev.eval_step(torch.as_tensor(test_img).cuda(), torch.as_tensor(test_lab).cuda())
     torch.cuda.synchronize()
     acc_engine = ev.last_accuracy()
-    # after 24 steps the moving statistics (momentum 0.99) are still 79 % initial values, so
-    # inference-mode accuracy is far from the batch-statistics one -- for BOTH implementations,
-    # and by a similar amount (256 held-out samples: +-3 pt sampling noise each)
-    assert acc_oracle > 0.2 and acc_engine > 0.2, (acc_oracle, acc_engine)
-    # The two trajectories do not hold the same weights (any change of float summation order in a
-    # gradient kernel flips near-zero latent weights differently -- see the module docstring), so
-    # their held-out accuracies are only loosely comparable.  What IS comparable: the oracle's
-    # inference on the ENGINE's trained weights and moving statistics must predict what the
-    # engine's validation pass predicts (same state, two implementations).
-    assert abs(acc_engine - acc_oracle) <= 0.25, (acc_oracle, acc_engine)
-    same_state = O.predict(eng.get_params(), eng.get_moving(), layers_o, xt)
+    assert acc_oracle >= 0.97 and acc_engine >= 0.97, (acc_oracle, acc_engine)
+    assert abs(acc_engine - acc_oracle) <= 0.005, (acc_oracle, acc_engine)      # 0.5 pt
+    # same state, two implementations of inference
+    same_state = O.predict(eng.get_params(), eng.get_moving(), layers_o, xt, dtype=torch.float32)
     got = ev.logits()
     agree = (same_state.argmax(1) == got.argmax(1)).mean()
-    assert agree >= 0.98, agree                      # ties of near-equal logits aside
-    assert abs(float((same_state.argmax(1) == test_lab).mean()) - acc_engine) <= 0.02
+    assert agree >= 0.995, agree                     # ties of near-equal logits aside
+    assert abs(float((same_state.argmax(1) == test_lab).mean()) - acc_engine) <= 0.005
     # the checkpoint holds exactly what the engine holds
     for k, a in eng.get_params().items():
         assert np.array_equal(a, ev.get_params()[k])

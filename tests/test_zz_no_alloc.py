@@ -70,15 +70,48 @@ def test_static_scratch_matches_three_call_sequence_twice(native_lib):
             assert err.item() < 1e-4, f"{what}: rel err {err.item():.3g}"
 
 
-def test_static_scratch_rejects_oversized_channel_count(native_lib):
-    from zookeeper_b200 import native as zn
-
+def _cmax(zn, is_i16):
     lib = zn.load()
     lib.zkb_bn_train_sign_static_max_channels.restype = ctypes.c_int
-    cmax = lib.zkb_bn_train_sign_static_max_channels()
-    C = cmax * 2
-    x = torch.zeros(4, C, dtype=torch.float32, device="cuda")
-    beta = torch.zeros(C, dtype=torch.float32, device="cuda")
-    s = torch.empty(4, C, dtype=torch.bfloat16, device="cuda")
-    with pytest.raises(zn.ZkbError, match="exceeds the built-in scratch"):
-        zn.call("zkb_bn_train_sign_static", zn.ptr(x), 0, 4, C, zn.ptr(beta), EPS, MOM, 0, 0, 0, zn.ptr(s), 0, 0)
+    lib.zkb_bn_train_sign_static_max_channels.argtypes = [ctypes.c_int]
+    return lib.zkb_bn_train_sign_static_max_channels(is_i16)
+
+
+@pytest.mark.parametrize("is_i16", [1, 0])
+def test_static_scratch_at_exactly_the_documented_limit(native_lib, is_i16):
+    """The widest layer the entry point accepts (2048 channels of int16 input, 1024 of f32): same
+    results as the three-call sequence, so the whole array is usable as documented."""
+    from zookeeper_b200 import native as zn
+
+    C = _cmax(zn, is_i16)
+    assert C == (2048 if is_i16 else 1024)
+    g = torch.Generator(device="cpu").manual_seed(17 + is_i16)
+    if is_i16:
+        x = torch.randint(-4608, 4609, (777, C), generator=g, dtype=torch.int16).cuda()
+    else:
+        x = (torch.randn(777, C, generator=g) * 5 - 1).cuda()
+    beta = torch.randn(C, generator=g).cuda()
+    ref = _reference(zn, x, is_i16, C, beta, 1)
+    got = _static(zn, x, is_i16, C, beta, 1)
+    assert torch.equal(got[0].view(torch.int16), ref[0].view(torch.int16))
+    for gt, rf in zip(got[1:], ref[1:]):
+        err = (gt.double() - rf.double()).norm() / rf.double().norm().clamp_min(1e-30)
+        assert err.item() < 1e-4
+
+
+@pytest.mark.parametrize("is_i16", [1, 0])
+def test_static_scratch_rejects_what_it_cannot_hold(native_lib, is_i16):
+    """One channel vector beyond the limit, twice the limit, and a width that is not a power-of-two
+    number of vectors: refused before any launch, with a message that names the rule."""
+    from zookeeper_b200 import native as zn
+
+    cmax = _cmax(zn, is_i16)
+    vec = 8 if is_i16 else 4
+    dt = torch.int16 if is_i16 else torch.float32
+    for C, msg in ((cmax + vec, "exceeds the built-in scratch"), (2 * cmax, "exceeds the built-in scratch"),
+                   (3 * vec, "times a power of two")):
+        x = torch.zeros(4, C, dtype=dt, device="cuda")
+        beta = torch.zeros(C, dtype=torch.float32, device="cuda")
+        s = torch.empty(4, C, dtype=torch.bfloat16, device="cuda")
+        with pytest.raises(zn.ZkbError, match=msg):
+            zn.call("zkb_bn_train_sign_static", zn.ptr(x), is_i16, 4, C, zn.ptr(beta), EPS, MOM, 0, 0, 0, zn.ptr(s), 0, 0)

@@ -23,6 +23,11 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
     "-DZKB_BUILD=1",
 ]
+# ZKB_MEASURE=1: a measurement build whose GEMM launchers read tile-shape overrides and the
+# "drop the MMA issue / drop the TMA loads" switches from the environment (scripts/bench_gemm.py).
+# The product build (build(), the tests, bench.py) has none of them compiled in.
+if os.environ.get("ZKB_MEASURE") == "1":
+    NVCC_FLAGS.append("-DZKB_MEASURE=1")
 
 
 def _nvcc() -> str:

@@ -20,7 +20,8 @@ __device__ __forceinline__ float bf16_to_f32(uint16_t h) {
   return __uint_as_float(static_cast<uint32_t>(h) << 16);
 }
 
-// Counter-based per-sample randomness shared with oracle/augment.py (splitmix64 finaliser).
+// Counter-based per-sample randomness (splitmix64 finaliser); oracle/binarynet_oracle.py
+// augmentation_params() derives the same offsets from (seed, step, sample).
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
   z += 0x9E3779B97F4A7C15ull;
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -364,44 +365,13 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sum, const double*
   }
 }
 
-// Optional fold of bn_finalize_kernel into its consumer: every thread derives mean / rstd of its
-// channels from the batch sums (same float64 arithmetic, hence the same floats), and the first
-// threads of block 0 also store them and update the moving statistics.  One launch less per layer.
-struct BnFoldFwd {
-  const double* sum;       // null: statistics are read from mean / rstd
-  const double* sumsq;
-  double count;
-  float eps, momentum;
-  int bessel;
-  float *mean_out, *rstd_out, *moving_mean, *moving_var;
-};
-
-__device__ __forceinline__ void bn_fold_channel(const BnFoldFwd& f, int c, bool writer, float& mean, float& rstd) {
-  const double m = f.sum[c] / f.count;
-  double var = f.sumsq[c] / f.count - m * m;
-  if (var < 0.0) var = 0.0;
-  const float meanf = static_cast<float>(m);
-  const float varf = static_cast<float>(var);
-  mean = meanf;
-  rstd = rsqrtf(varf + f.eps);
-  if (writer) {
-    f.mean_out[c] = meanf;
-    f.rstd_out[c] = rstd;
-    if (f.moving_mean) {
-      const float uv = (f.bessel && f.count > 1.0) ? static_cast<float>(var * (f.count / (f.count - 1.0))) : varf;
-      f.moving_mean[c] = f.moving_mean[c] * f.momentum + meanf * (1.0f - f.momentum);
-      f.moving_var[c] = f.moving_var[c] * f.momentum + uv * (1.0f - f.momentum);
-    }
-  }
-}
-
 // a = (x - mean) * rstd + beta ; s = sign(a) with sign(0) = +1, written as bf16 +-1.
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const float* __restrict__ beta,
                      uint16_t* __restrict__ s_out, float* __restrict__ a_out,
-                     int8_t* __restrict__ s8_out = nullptr, const BnFoldFwd fold = BnFoldFwd{}) {
+                     int8_t* __restrict__ s8_out = nullptr) {
   constexpr int VEC = Vec16<T>::N;
   const int tpr = C / VEC;
   const long long total = rows * tpr;
@@ -409,14 +379,9 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
   // its per-channel parameters live in registers for the whole loop.
   const int cl = threadIdx.x % tpr;
   float mu[VEC], rs[VEC], be[VEC];
-  const bool writer = blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tpr;
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
-    if (fold.sum) {
-      bn_fold_channel(fold, cl * VEC + j, writer, mu[j], rs[j]);
-    } else {
-      mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j];
-    }
+    mu[j] = mean[cl * VEC + j]; rs[j] = rstd[cl * VEC + j];
     be[j] = beta[cl * VEC + j];
   }
   const long long gstride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -754,14 +719,6 @@ __global__ void bn_bwd_finalize_kernel(const double* __restrict__ sum_da,
 //   out_mode 1: bf16 hi/lo split [rows][C]
 //   out_mode 2: bf16 hi/lo split scattered through the 2x2 max-pool argmax into [B,H,W,C]
 //               (x, g and arg are pooled maps [B,H/2,W/2,C]; the three losers get zeros).
-// Optional fold of bn_bwd_finalize_kernel into bn_bwd_apply_kernel (see BnFoldFwd).
-struct BnFoldBwd {
-  const double* sum_da;    // null: the means are read from mean_da / mean_dax
-  const double* sum_dax;
-  double count, dbeta_scale;
-  float *dbeta, *mean_da_out, *mean_dax_out;
-};
-
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long long rows, int C,
@@ -769,30 +726,18 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
                     const float* __restrict__ beta, const float* __restrict__ mean_da,
                     const float* __restrict__ mean_dax, int ste, int out_mode,
                     float* __restrict__ out_f32, uint16_t* __restrict__ out_hi,
-                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W,
-                    const BnFoldBwd fold = BnFoldBwd{}) {
+                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W) {
   constexpr int VEC = 4;
   const int tpr = C / VEC;
   const long long total = rows * tpr;
   const int PH = H / 2, PW = W / 2;
   const int cl = threadIdx.x % tpr;   // fixed per thread (blockDim and grid stride are multiples of tpr)
   float mu[VEC], rs[VEC], be[VEC], mda[VEC], mdx[VEC];
-  const bool writer = blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tpr;
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
     const int c = cl * VEC + j;
     mu[j] = mean[c]; rs[j] = rstd[c]; be[j] = beta[c];
-    if (fold.sum_da) {
-      mda[j] = static_cast<float>(fold.sum_da[c] / fold.count);
-      mdx[j] = static_cast<float>(fold.sum_dax[c] / fold.count);
-      if (writer) {
-        if (fold.dbeta) fold.dbeta[c] = static_cast<float>(fold.sum_da[c] * fold.dbeta_scale);
-        fold.mean_da_out[c] = mda[j];
-        fold.mean_dax_out[c] = mdx[j];
-      }
-    } else {
-      mda[j] = mean_da[c]; mdx[j] = mean_dax[c];
-    }
+    mda[j] = mean_da[c]; mdx[j] = mean_dax[c];
   }
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -1158,34 +1103,6 @@ ZKB_API int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C
   return ZKB_OK;
 }
 
-ZKB_API int zkb_bn_finalize_apply_sign(const void* x, int x_is_i16, long long rows, int C,
-                                       const double* sum, const double* sumsq, double count, float eps,
-                                       float momentum, int bessel, const float* beta, float* mean_out,
-                                       float* rstd_out, float* moving_mean, float* moving_var,
-                                       void* s_out_bf16, float* a_out, void* s_out_i8, void* stream) {
-  const int vec = x_is_i16 ? 8 : 4;
-  int rc = check_rows_c("bn_finalize_apply_sign", x, rows, C, vec);
-  if (rc) return rc;
-  ZKB_REQUIRE(sum && sumsq && beta && mean_out && rstd_out, "bn_finalize_apply_sign: null pointer");
-  ZKB_REQUIRE(count > 0.0 && rows > 0, "bn_finalize_apply_sign: count and rows must be positive");
-  ZKB_REQUIRE((moving_mean == nullptr) == (moving_var == nullptr),
-              "bn_finalize_apply_sign: moving_mean and moving_var go together");
-  ZKB_REQUIRE(C / vec <= 256, "bn_finalize_apply_sign: at most %d channels", 256 * vec);
-  ZKB_REQUIRE(s_out_bf16 || a_out || s_out_i8, "bn_finalize_apply_sign: no output requested");
-  const BnFoldFwd fold{sum, sumsq, count, eps, momentum, bessel, mean_out, rstd_out, moving_mean, moving_var};
-  const int grid = grid_for(rows * (C / vec), 256, 16);
-  if (x_is_i16)
-    bn_apply_sign_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const int16_t*>(x), rows, C, nullptr, nullptr, beta,
-        static_cast<uint16_t*>(s_out_bf16), a_out, static_cast<int8_t*>(s_out_i8), fold);
-  else
-    bn_apply_sign_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const float*>(x), rows, C, nullptr, nullptr, beta, static_cast<uint16_t*>(s_out_bf16),
-        a_out, static_cast<int8_t*>(s_out_i8), fold);
-  ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
-  return ZKB_OK;
-}
-
 ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_out, uint8_t* arg_out,
                              double* sum, double* sumsq, void* stream) {
   int rc = check_rows_c("maxpool2_i16", y, static_cast<long long>(B) * H * W, C, 8);
@@ -1276,41 +1193,6 @@ ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long l
   return ZKB_OK;
 }
 
-ZKB_API int zkb_bn_bwd_finalize_apply(const float* g, const void* x, int x_is_i16, long long rows, int C,
-                                      const float* mean, const float* rstd, const float* beta,
-                                      const double* sum_da, const double* sum_dax, double count,
-                                      double dbeta_scale, float* dbeta, float* mean_da_out,
-                                      float* mean_dax_out, int ste, int out_mode, float* out_f32,
-                                      void* out_hi, void* out_lo, const uint8_t* arg, int H, int W,
-                                      void* stream) {
-  int rc = check_rows_c("bn_bwd_finalize_apply", g, rows, C, 4);
-  if (rc) return rc;
-  ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax && mean_da_out && mean_dax_out,
-              "bn_bwd_finalize_apply: null pointer");
-  ZKB_REQUIRE(count > 0.0 && rows > 0, "bn_bwd_finalize_apply: count and rows must be positive");
-  ZKB_REQUIRE(C / 4 <= 256, "bn_bwd_finalize_apply: at most 1024 channels");
-  ZKB_REQUIRE(out_mode >= 0 && out_mode <= 2, "bn_bwd_finalize_apply: out_mode must be 0, 1 or 2");
-  if (out_mode == 0) ZKB_REQUIRE(out_f32, "bn_bwd_finalize_apply: out_f32 is null");
-  if (out_mode >= 1) ZKB_REQUIRE(out_hi && out_lo, "bn_bwd_finalize_apply: hi/lo outputs are null");
-  if (out_mode == 2) {
-    ZKB_REQUIRE(arg && H >= 2 && W >= 2, "bn_bwd_finalize_apply: pool scatter needs argmax and H, W");
-    ZKB_REQUIRE(rows % (static_cast<long long>(H / 2) * (W / 2)) == 0,
-                "bn_bwd_finalize_apply: rows is not a multiple of the pooled map size");
-  }
-  const BnFoldBwd fold{sum_da, sum_dax, count, dbeta_scale, dbeta, mean_da_out, mean_dax_out};
-  const int grid = grid_for(rows * (C / 4), 256, 16);
-  if (x_is_i16)
-    bn_bwd_apply_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, nullptr, nullptr, ste, out_mode,
-        out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W, fold);
-  else
-    bn_bwd_apply_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        g, static_cast<const float*>(x), rows, C, mean, rstd, beta, nullptr, nullptr, ste, out_mode,
-        out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W, fold);
-  ZKB_LAUNCH_CHECK("bn_bwd_apply_kernel");
-  return ZKB_OK;
-}
-
 ZKB_API int zkb_prep_conv_weights(const float* w_hwio, int ksize, int Cin, int Cout, void* w_fwd,
                                   void* w_dgrad, void* w_fwd_i8, void* stream) {
   ZKB_REQUIRE(w_hwio && w_fwd && w_dgrad, "prep_conv_weights: null pointer");
@@ -1366,12 +1248,17 @@ ZKB_API int zkb_adam_clip(float* w, const float* g, float* m, float* v, long lon
 // zkb_bn_apply_sign needs per-channel accumulators and statistics that such a caller has nowhere
 // to put.  zkb_bn_train_sign_static keeps them in the fixed array below instead.
 //
-// The array lives in every CUDA context that loads the library (about 96 KiB per GPU, until the
+// The array lives in every CUDA context that loads the library (48 KiB per GPU, until the
 // process exits) and is shared by ALL calls on that GPU: it still holds the previous call's values
 // on entry (the entry point clears what must start at zero), and two calls whose kernels overlap
 // on the GPU -- different streams, different host threads -- corrupt each other.
+//
+// Channel limit: the statistics and normalising kernels give each thread of a 256-thread block one
+// 16-byte vector of channels (8 int16 or 4 f32), so a row is at most 256 vectors wide and the vector
+// count must divide 256: C <= 2048 for int16 input, C <= 1024 for f32 input, C / vector a power of
+// two.  The array is sized for the larger of the two.
 namespace zkb {
-constexpr int kStaticBnMaxChannels = 4096;
+constexpr int kStaticBnMaxChannels = 2048;        // int16 input; f32 input: half of it
 struct StaticBnScratch {
   double sum[kStaticBnMaxChannels];
   double sumsq[kStaticBnMaxChannels];
@@ -1401,17 +1288,22 @@ static int static_bn_scratch(StaticBnScratch** out) {
   return ZKB_OK;
 }
 
-ZKB_API int zkb_bn_train_sign_static_max_channels() { return kStaticBnMaxChannels; }
+ZKB_API int zkb_bn_train_sign_static_max_channels(int x_is_i16) {
+  return x_is_i16 ? kStaticBnMaxChannels : kStaticBnMaxChannels / 2;
+}
 
 ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows, int C,
                                      const float* beta, float eps, float momentum, int bessel,
                                      float* moving_mean, float* moving_var, void* s_out_bf16,
                                      float* a_out, void* stream) {
   const int vec = x_is_i16 ? 8 : 4;
-  ZKB_REQUIRE(C <= kStaticBnMaxChannels,
-              "bn_train_sign_static: C=%d exceeds the built-in scratch (at most %d channels); use "
-              "zkb_bn_stats/zkb_bn_finalize/zkb_bn_apply_sign with caller-provided buffers",
-              C, kStaticBnMaxChannels);
+  const int cmax = zkb_bn_train_sign_static_max_channels(x_is_i16);
+  ZKB_REQUIRE(C > 0 && C <= cmax,
+              "bn_train_sign_static: C=%d exceeds the built-in scratch (at most %d channels for %s "
+              "input); larger layers need the stats/finalize/apply entry points with caller-provided buffers",
+              C, cmax, x_is_i16 ? "int16" : "f32");
+  ZKB_REQUIRE(C % vec == 0 && 256 % (C / vec) == 0,
+              "bn_train_sign_static: C=%d must be %d times a power of two (at most %d)", C, vec, cmax);
   int rc = check_rows_c("bn_train_sign_static", x, rows, C, vec);
   if (rc) return rc;
   ZKB_REQUIRE(rows > 0, "bn_train_sign_static: rows must be positive");
@@ -1613,12 +1505,11 @@ conv_first_bn_stats_kernel(const float* __restrict__ x, const float* __restrict_
   block_channel_reduce<4>(a0, a1, tpr, Cout, sum, sumsq);
 }
 
-template <int KS, int CIN, bool kMask>
+template <int KS, int CIN>
 __device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
                           int W, int Cout, const float* __restrict__ mean,
                           const float* __restrict__ rstd, const float* __restrict__ beta,
-                          uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out,
-                          uint4* __restrict__ ste_mask) {
+                          uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out) {
   using FC = FirstConv<KS, CIN>;
   float* s_w = first_conv_weights_smem();
   for (int i = threadIdx.x; i < FC::K * Cout; i += blockDim.x) s_w[i] = wq[i];
@@ -1633,7 +1524,7 @@ __device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict_
   for (int j = 0; j < 4; ++j) { mu[j] = mean[cl * 4 + j]; rs[j] = rstd[cl * 4 + j]; be[j] = beta[cl * 4 + j]; }
   const unsigned OWr = W - KS + 1;
   const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
-  if constexpr (KS == 3 && CIN == 1 && !kMask) {
+  if constexpr (KS == 3 && CIN == 1) {
     // One input channel: the 3x3 window slides by one column per pixel.  Three pixels per
     // iteration, so that the three column registers rotate by renaming instead of moves, and row
     // pointers that advance by three (tap loads with immediate offsets).
@@ -1708,16 +1599,6 @@ __device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict_
       a[j] = (y[j] - mu[j]) * rs[j] + be[j];
       neg |= ((a[j] >= 0.0f) ? 0u : 1u) << j;
     }
-    if constexpr (kMask) {
-      // ste_sign keeps the gradient where |a| <= 1.  Cout == 128: the 32 threads of a warp hold the
-      // 128 channels of one pixel; word j of the pixel's 16 bytes gets bit l for channel 4 l + j.
-      uint4 m;
-      m.x = __ballot_sync(0xffffffffu, fabsf(a[0]) <= 1.0f);
-      m.y = __ballot_sync(0xffffffffu, fabsf(a[1]) <= 1.0f);
-      m.z = __ballot_sync(0xffffffffu, fabsf(a[2]) <= 1.0f);
-      m.w = __ballot_sync(0xffffffffu, fabsf(a[3]) <= 1.0f);
-      if (cl == 0) ste_mask[static_cast<size_t>(row) * OWr + owi] = m;
-    }
     if (so) {    // bf16 +1 = 0x3F80, -1 = 0xBF80: the sign bits go to bits 15 and 31 of each pair
       *reinterpret_cast<uint2*>(so) =
           make_uint2(0x3F803F80u | ((neg & 1u) << 15) | ((neg & 2u) << 30),
@@ -1741,17 +1622,7 @@ conv_first_bn_sign_kernel(const float* __restrict__ x, const float* __restrict__
                           int Cout, const float* __restrict__ mean, const float* __restrict__ rstd,
                           const float* __restrict__ beta, uint16_t* __restrict__ s_out,
                           int8_t* __restrict__ s8_out) {
-  conv_first_bn_sign_body<KS, CIN, false>(x, wq, B, H, W, Cout, mean, rstd, beta, s_out, s8_out, nullptr);
-}
-
-template <int KS, int CIN>
-__global__ void __launch_bounds__(256, 3)
-conv_first_bn_sign_mask_kernel(const float* __restrict__ x, const float* __restrict__ wq, int B, int H,
-                               int W, int Cout, const float* __restrict__ mean,
-                               const float* __restrict__ rstd, const float* __restrict__ beta,
-                               uint16_t* __restrict__ s_out, int8_t* __restrict__ s8_out,
-                               uint4* __restrict__ ste_mask) {
-  conv_first_bn_sign_body<KS, CIN, true>(x, wq, B, H, W, Cout, mean, rstd, beta, s_out, s8_out, ste_mask);
+  conv_first_bn_sign_body<KS, CIN>(x, wq, B, H, W, Cout, mean, rstd, beta, s_out, s8_out);
 }
 
 template <int KS, int CIN>
@@ -2048,22 +1919,6 @@ ZKB_API int zkb_conv_first_bn_sign(const float* x, const float* wq_k_co, int B, 
   if (B == 0) return ZKB_OK;
   ZKB_FIRST_DISPATCH(conv_first_bn_sign_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
                      static_cast<uint16_t*>(s_out_bf16), static_cast<int8_t*>(s_out_i8));
-  return ZKB_OK;
-}
-
-ZKB_API int zkb_conv_first_bn_sign_mask(const float* x, const float* wq_k_co, int B, int H, int W, int Cin,
-                                        int Cout, int ksize, const float* mean, const float* rstd,
-                                        const float* beta, void* s_out_bf16, void* s_out_i8,
-                                        void* ste_mask, void* stream) {
-  int rc = first_conv_check("conv_first_bn_sign_mask", x, wq_k_co, B, H, W, Cin, Cout, ksize);
-  if (rc) return rc;
-  ZKB_REQUIRE(mean && rstd && beta && ste_mask, "conv_first_bn_sign_mask: null pointer");
-  ZKB_REQUIRE(Cout == 128, "conv_first_bn_sign_mask: the mask layout is built for 128 channels");
-  ZKB_REQUIRE(ZKB_ALIGNED16(ste_mask), "conv_first_bn_sign_mask: mask must be 16-byte aligned");
-  if (B == 0) return ZKB_OK;
-  ZKB_FIRST_DISPATCH(conv_first_bn_sign_mask_kernel, x, wq_k_co, B, H, W, Cout, mean, rstd, beta,
-                     static_cast<uint16_t*>(s_out_bf16), static_cast<int8_t*>(s_out_i8),
-                     static_cast<uint4*>(ste_mask));
   return ZKB_OK;
 }
 

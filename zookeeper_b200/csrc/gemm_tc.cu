@@ -11,8 +11,10 @@
 //           is the slow one: pixels / batch rows).  Split over P across CTAs; partial tiles are
 //           reduced into the f32 gradient with red.global.add.
 //
-// Operands are bf16 (+-1 is exact), accumulation f32 in tensor memory: for +-1 x +-1 with
-// K <= 2^24 the result is the exact integer.  Replaces the Eigen/oneDNN float conv + matmul that
+// Forward operands are int8 +-1 on kind::i8 with exact int32 accumulation (a bf16 kind::f16 form
+// is kept as the cross-check: +-1 x +-1 with K <= 2^24 in f32 is the same integer); backward
+// operands are bf16 (dy as a hi + lo pair, +-1 exact) with f32 accumulation in tensor memory.
+// Replaces the Eigen/oneDNN float conv + matmul that
 // TF runs for larq QuantConv2D / QuantDense (reference call sites:
 // examples/larq_experiment.py:71-73,76-82,85-91,95-99).
 #include <cuda_bf16.h>
@@ -23,6 +25,15 @@
 
 #ifndef ZKB_KGEMM_PLAIN_REGS
 #define ZKB_KGEMM_PLAIN_REGS 112   // register cap of the plain kgemm kernel (see kgemm_bf16_kernel)
+#endif
+
+// Timing experiments (scripts/bench_gemm.py: drop the MMA issue or the TMA loads to see which side
+// bounds a GEMM) exist only in a library built with -DZKB_MEASURE (ZKB_MEASURE=1 python -m
+// zookeeper_b200.build); the product build has no such switch.
+#ifdef ZKB_MEASURE
+#define ZKB_DBG(p, bit) (((p).dbg & (bit)) != 0)
+#else
+#define ZKB_DBG(p, bit) false
 #endif
 
 namespace zkb {
@@ -45,7 +56,7 @@ struct KGemmParams {
   int OH, OW, pad, kw_taps, cblocks;
   int out_kind;  // 0: f32, 1: int16 (exact integers expected)
   int is_i8;     // operands are signed int8 (+-1 / 0), accumulators int32 (kind::i8)
-  int dbg;       // measurement switches (scripts/bench_gemm.py): 1 = no MMA issue, 2 = no TMA loads
+  int dbg;       // ZKB_MEASURE builds only: 1 = no MMA issue, 2 = no TMA loads
   // Fused first-layer backward (swap mode, 128 output channels, one input channel, 3x3): the
   // epilogue consumes D^T = ds0 straight from tensor memory -- BatchNorm-backward sums and the
   // weight-gradient sums of the first layer -- and stores nothing.
@@ -57,10 +68,6 @@ struct KGemmParams {
   const float* l0_rstd;
   const float* l0_beta;
   double* l0_acc;            // [11][128]: sum da, sum da*xhat, S1[k] = sum x_k*da (9 taps)
-  const uint32_t* l0_mask;   // optional ste mask written by the forward (16 B per pixel: word j, bit l
-                             // = channel 4l + j keeps its gradient).  With it the epilogue does not
-                             // recompute the first conv, and sum da*xhat is left to the finalize
-                             // kernel (it equals rstd * (sum_k w_k S1[k] - mean * sum da)).
   // BatchNorm-backward sums of the layer BELOW, fused into the f32 dgrad epilogue (swap mode and
   // CTA pairs): D[row][c] is the gradient w.r.t. that layer's sign output, bn_x its pre-BatchNorm
   // int16 map of the same shape; per channel sum da and sum da*xhat (da = D masked by |a| <= 1)
@@ -77,8 +84,8 @@ struct KGemmParams {
   const int16_t* bn_x;
   const float *bn_mean, *bn_rstd, *bn_beta;
   double *bn_sum_da, *bn_sum_dax;
-  int swap_boxes;  // swap mode: pixel boxes per tile and their height: 2 x 128 (default) or 3 x 64
-  int swap_box_px; // (192-pixel tiles: three 64 KB stages fit -- measured no faster than two of 80 KB)
+  int swap_boxes;  // swap mode: pixel boxes per tile and their height (2 x 128)
+  int swap_box_px;
   int swap;      // 1: operand roles swapped -- the MMA computes D^T[128 out channels, 256 pixels]
                  //    so that narrow (128-column) layers still issue 256-wide MMAs; f32 output only
   void* out;
@@ -117,30 +124,6 @@ __device__ __forceinline__ void first_layer_unit(const KGemmParams& p, const uin
   const unsigned oh = rem / static_cast<unsigned>(p.OW);
   const unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
   const unsigned my_off = (b * static_cast<unsigned>(p.l0_H) + oh) * static_cast<unsigned>(p.l0_W) + ow;
-  if (p.l0_mask) {
-    const int c = static_cast<int>((threadIdx.x >> 5) & 3u) * 32 + lane;   // lane quarter * 32 + lane
-    const uint32_t* mrow = p.l0_mask + (c & 3);
-    const int bit = c >> 2;
-    const int last = p.M - 1 - pix0;
-    // all 32 mask words first (they come from L2 / HBM), then the taps (L1 hits)
-    uint32_t keep_bits = 0;
-#pragma unroll
-    for (int j = 0; j < 32; ++j)
-      keep_bits |= ((__ldg(mrow + 4 * static_cast<size_t>(pix0 + (j < last ? j : last))) >> bit) & 1u) << j;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      const uint32_t keep = (keep_bits >> j) & 1u;
-      const float* q0 = p.l0_x + __shfl_sync(0xffffffffu, my_off, j);
-      const float* q1 = q0 + p.l0_W;
-      const float* q2 = q1 + p.l0_W;
-      const float da = keep ? __uint_as_float(r[j]) : 0.f;
-      f[0] += da;
-      f[2] = fmaf(__ldg(q0), da, f[2]); f[3] = fmaf(__ldg(q0 + 1), da, f[3]); f[4] = fmaf(__ldg(q0 + 2), da, f[4]);
-      f[5] = fmaf(__ldg(q1), da, f[5]); f[6] = fmaf(__ldg(q1 + 1), da, f[6]); f[7] = fmaf(__ldg(q1 + 2), da, f[7]);
-      f[8] = fmaf(__ldg(q2), da, f[8]); f[9] = fmaf(__ldg(q2 + 1), da, f[9]); f[10] = fmaf(__ldg(q2 + 2), da, f[10]);
-    }
-    return;
-  }
   // Groups of four pixels: all 36 tap loads of a group are issued before the first FMA that
   // needs one (the FMAs otherwise sit on the loads' scoreboard: 2 epilogue warps per scheduler
   // cannot hide an L1 hit each).
@@ -277,7 +260,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
           const uint32_t full = smem_u32(&ctl->full[stage]);
-          if (p.dbg & 2) {
+          if (ZKB_DBG(p, 2)) {
             if (elect_one()) mbar_arrive(full);
             __syncwarp();
             if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
@@ -333,7 +316,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
           const uint32_t full = smem_u32(&ctl->full[stage]);
-          if (p.dbg & 2) {
+          if (ZKB_DBG(p, 2)) {
             if (elect_one()) mbar_arrive(full);
             __syncwarp();
             if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
@@ -395,7 +378,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           const uint64_t m_step = p.swap ? 0u : (kATileBytes >> 4);
           const uint64_t n_step = p.swap ? (static_cast<uint32_t>(p.swap_boxes * p.swap_box_px) * 128u >> 4) : 0u;
           if (elect_one()) {
-          if (!(p.dbg & 1)) {
+          if (!ZKB_DBG(p, 1)) {
             for (int t = 0; t < p.a_terms; ++t) {
               const uint64_t ad = m_desc + t * m_step, bd = n_desc + t * n_step;
               // a 128-byte row holds 64 bf16 or 128 int8: either way 4 MMAs of 32 bytes of K
@@ -692,18 +675,6 @@ kgemm_first_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_c
                         const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
                         const KGemmParams p) {
   kgemm_body<true>(tmA0, tmA1, tmB, tmOut, p);
-}
-
-// Mask mode of the fused epilogue leaves acc[1][c] = sum da*xhat to this kernel:
-//   sum_p da*xhat = rstd * (sum_p da*y - mean * sum_p da),  sum_p da*y = sum_k w_kc * S1[k][c]
-// (y is the first conv's output, linear in the taps).
-__global__ void conv_first_dax_from_s1_kernel(double* __restrict__ acc, const float* __restrict__ wq,
-                                              const float* __restrict__ mean,
-                                              const float* __restrict__ rstd) {
-  const int c = threadIdx.x;   // 128 threads
-  double day = 0.0;
-  for (int k = 0; k < 9; ++k) day += static_cast<double>(wq[k * 128 + c]) * acc[(2 + k) * 128 + c];
-  acc[128 + c] = static_cast<double>(rstd[c]) * (day - static_cast<double>(mean[c]) * acc[c]);
 }
 
 // Per channel c and tap k: dbeta = sum da; dW0[k][c] = rstd_c * (S1 - mean(da) * S2[k] -
@@ -1003,7 +974,7 @@ struct WGemmParams {
   int OH, OW, pad, kw_taps, taps;
   int tpi;      // taps per work item: they share the B (dy) tile, one TMEM accumulator each
   int kpix;     // reduction rows per pipeline stage (32, 48 or 64)
-  int dbg;      // measurement switches (scripts/bench_gemm.py): 1 = no MMA issue, 2 = no TMA loads
+  int dbg;      // ZKB_MEASURE builds only: 1 = no MMA issue, 2 = no TMA loads
   int ci_tiles, n_tiles, splits;
   int chunks_per_split;  // kpix-row chunks of P
   int num_stages, stage_bytes;
@@ -1102,11 +1073,11 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const uint32_t full = smem_u32(&ctl->full[stage]);
         if (lane == 0) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
-          if (p.dbg & 2) mbar_arrive(full);
+          if (ZKB_DBG(p, 2)) mbar_arrive(full);
           else mbar_expect_tx(full, tx_bytes);
         }
         __syncwarp();
-        if (lane < n_loads && !(p.dbg & 2)) {
+        if (lane < n_loads && !ZKB_DBG(p, 2)) {
           const uint32_t dst = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes) + my_off;
           if (is_b || !p.a_im2col) {
             tma_load_2d(dst, my_map, full, my_c, static_cast<int>(pix0));
@@ -1152,7 +1123,7 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each): 2048 B per k-step
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                if (k < ksteps && !(p.dbg & 1))
+                if (k < ksteps && !ZKB_DBG(p, 1))
                   umma_f16(d_tmem, a_desc + static_cast<uint64_t>(k * 128), b_desc + static_cast<uint64_t>(k * 128),
                            idesc, (ch | bt | k) != 0 ? 1u : 0u);
               }
@@ -1224,6 +1195,33 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 // ============================================================================================
 using namespace zkb;
 
+// Tile-shape overrides for A/B measurements (scripts/bench_gemm.py).  Read from the environment
+// once, and only in a -DZKB_MEASURE build: the product library has no environment switches.
+struct GemmTuning {
+  int dbg = 0;          // ZKB_GEMM_DBG
+  int pairs = -1;       // ZKB_KGEMM_PAIRS   (-1: default rule)
+  int swap = -1;        // ZKB_KGEMM_SWAP
+  int wgrad_tpi = 0;    // ZKB_WGRAD_TPI     (0: default rule)
+  int wgrad_kpix = 0;   // ZKB_WGRAD_KPIX
+  int wgrad_waves = 0;  // ZKB_WGRAD_WAVES
+};
+
+static const GemmTuning& gemm_tuning() {
+  static const GemmTuning t = [] {
+    GemmTuning g;
+#ifdef ZKB_MEASURE
+    if (const char* e = getenv("ZKB_GEMM_DBG")) g.dbg = atoi(e);
+    if (const char* e = getenv("ZKB_KGEMM_PAIRS")) g.pairs = atoi(e) != 0;
+    if (const char* e = getenv("ZKB_KGEMM_SWAP")) g.swap = atoi(e) != 0;
+    if (const char* e = getenv("ZKB_WGRAD_TPI")) g.wgrad_tpi = atoi(e);
+    if (const char* e = getenv("ZKB_WGRAD_KPIX")) g.wgrad_kpix = atoi(e) == 32 ? 32 : (atoi(e) == 48 ? 48 : 64);
+    if (const char* e = getenv("ZKB_WGRAD_WAVES")) g.wgrad_waves = atoi(e) > 0 ? atoi(e) : 0;
+#endif
+    return g;
+  }();
+  return t;
+}
+
 static int pick_block_n(int N) {
   if (N >= 256) return 256;
   if (N > 128) return 256;
@@ -1238,7 +1236,6 @@ struct FirstLayerFuse {   // see KGemmParams::l0_fused
   const float *x, *wq, *mean, *rstd, *beta;
   double* acc;
   int H, W;
-  const uint32_t* mask;
 };
 
 struct BnBackwardFuse {   // see KGemmParams::bn_fused
@@ -1286,7 +1283,8 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   p.N = N;
   p.num_kb = K / kelems;
   p.kelems = kelems;
-  if (const char* e = getenv("ZKB_GEMM_DBG")) p.dbg = atoi(e);
+  const GemmTuning& tune = gemm_tuning();
+  p.dbg = tune.dbg;
   p.is_i8 = elem_bytes == 1;
   p.a_terms = A_lo ? 2 : 1;
   p.block_n = pick_block_n(N);
@@ -1296,26 +1294,19 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   p.swap = (out_kind == 0 && elem_bytes == 2 && N % 128 == 0 && N < 256) ? 1 : 0;
   // ... and the int8 forward of a 128-channel layer with int16 output (no fused statistics there)
   if (out_kind == 1 && elem_bytes == 1 && N == 128 && ldo == N && !st) p.swap = 1;
-  if (const char* e = getenv("ZKB_KGEMM_SWAP")) {
-    if (!atoi(e)) p.swap = 0;
-    else if (out_kind == 0 && elem_bytes == 2 && N % 128 == 0) p.swap = 1;
-  }
+  if (tune.swap == 0) p.swap = 0;
+  else if (tune.swap == 1 && out_kind == 0 && elem_bytes == 2 && N % 128 == 0) p.swap = 1;
   if (l0) {
     p.swap = 1;
     p.l0_fused = 1;
     p.l0_x = l0->x; p.l0_wq = l0->wq; p.l0_mean = l0->mean; p.l0_rstd = l0->rstd; p.l0_beta = l0->beta;
     p.l0_acc = l0->acc; p.l0_H = l0->H; p.l0_W = l0->W;
-    p.l0_mask = l0->mask;
   }
   if (p.swap) {
-    // 256 pixels per tile as two 128-pixel boxes.  ZKB_SWAP_BOXES=3: 192 pixels as three 64-pixel
-    // boxes, which makes a two-term stage 64 KB so that three stages fit instead of two --
-    // measured r1 no faster (dgrad 1.37 against 1.34 ms, int8 forward 0.51 against 0.37).
+    // 256 pixels per tile as two 128-pixel boxes (192 pixels as three 64-pixel boxes, which fits
+    // three two-term stages instead of two, measured no faster in r1 and was removed)
     p.swap_boxes = 2;
     p.swap_box_px = 128;
-    if (const char* e = getenv("ZKB_SWAP_BOXES")) {
-      if (atoi(e) == 3) { p.swap_boxes = 3; p.swap_box_px = 64; }
-    }
     p.block_n = p.swap_boxes * p.swap_box_px;
     p.stage_bytes = kATileBytes + p.a_terms * p.block_n * 128;
   }
@@ -1323,7 +1314,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   // (measured r1: +3..5 % for the two-term dgrad, -8 % for the int8 forward whose stages are
   // smaller -- so pairs are the default for two-term problems only)
   bool use_pairs = !p.swap && N % 256 == 0 && p.a_terms == 2;
-  if (const char* e = getenv("ZKB_KGEMM_PAIRS")) use_pairs = atoi(e) != 0 && !p.swap && N % 256 == 0;
+  if (tune.pairs >= 0) use_pairs = tune.pairs != 0 && !p.swap && N % 256 == 0;
   if (use_pairs) {
     p.block_n = 256;
     p.stage_bytes = p.a_terms * kATileBytes + kATileBytes;   // A tile(s) + this CTA's half of B
@@ -1493,13 +1484,10 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
     if (p.tpi > ksize) p.tpi = ksize;
   }
   p.kpix = 64;
-  // tuning overrides for A/B measurements (scripts/bench_gemm.py); not part of the ABI contract
-  if (const char* e = getenv("ZKB_GEMM_DBG")) p.dbg = atoi(e);
-  if (const char* e = getenv("ZKB_WGRAD_TPI")) {
-    const int v = atoi(e);
-    if (im2col && v >= 1 && v * p.block_n <= 512) p.tpi = v;
-  }
-  if (const char* e = getenv("ZKB_WGRAD_KPIX")) p.kpix = atoi(e) == 32 ? 32 : (atoi(e) == 48 ? 48 : 64);
+  const GemmTuning& tune = gemm_tuning();
+  p.dbg = tune.dbg;
+  if (im2col && tune.wgrad_tpi >= 1 && tune.wgrad_tpi * p.block_n <= 512) p.tpi = tune.wgrad_tpi;
+  if (tune.wgrad_kpix) p.kpix = tune.wgrad_kpix;
   p.pad = pad;
   p.OH = H;
   p.OW = W;
@@ -1508,7 +1496,7 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   const int boxes_b = p.b_terms * (p.concat ? 2 : p.block_n / 64);
   // Three pipeline stages hide the TMA latency, two do not (measured r1: -5..12 % with three):
   // when 64 reduction rows per stage leave room for only two stages, take 48.
-  if (!getenv("ZKB_WGRAD_KPIX") && kSmemBudget / ((p.tpi * 2 + boxes_b) * p.kpix * 128) < 3) p.kpix = 48;
+  if (!tune.wgrad_kpix && kSmemBudget / ((p.tpi * 2 + boxes_b) * p.kpix * 128) < 3) p.kpix = 48;
   const int box_bytes = p.kpix * 128;
   p.stage_bytes = (p.tpi * 2 + boxes_b) * box_bytes;
   p.num_stages = kSmemBudget / p.stage_bytes;
@@ -1523,8 +1511,7 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   // one long wave beats two short ones (fewer pipeline fills and atomic epilogues; measured in the
   // step, r1) unless the output tiles divide the SMs badly.
   const int out_tiles = ((p.taps + p.tpi - 1) / p.tpi) * p.ci_tiles * p.n_tiles;
-  int waves = 0;
-  if (const char* e = getenv("ZKB_WGRAD_WAVES")) waves = atoi(e) > 0 ? atoi(e) : 0;
+  int waves = tune.wgrad_waves;
   if (waves == 0) {
     double best = 0.0;
     for (int w = 1; w <= 3; ++w) {
@@ -1657,26 +1644,16 @@ ZKB_API int zkb_bconv2d_dgrad_first_bwd(const void* dy_hi, const void* dy_lo, co
                                         int NB, int H, int W, int Cin, int Cout, int ksize,
                                         const float* x0, int H0, int W0, const float* wq0_k_co,
                                         const float* mean0, const float* rstd0, const float* beta0,
-                                        const void* ste_mask, double* acc, void* stream) {
-  ZKB_REQUIRE((reinterpret_cast<uintptr_t>(ste_mask) & 15) == 0, "bconv2d_dgrad_first_bwd: mask must be 16-byte aligned");
+                                        double* acc, void* stream) {
   ZKB_REQUIRE(ksize == 3 && Cin == 128, "bconv2d_dgrad_first_bwd: built for 3x3 kernels into 128 channels");
   ZKB_REQUIRE(H0 == H + 2 && W0 == W + 2,
               "bconv2d_dgrad_first_bwd: first layer must be a 'valid' 3x3 conv (image %dx%d, map %dx%d)",
               H0, W0, H, W);
   ZKB_REQUIRE(x0 && wq0_k_co && mean0 && rstd0 && beta0 && acc, "bconv2d_dgrad_first_bwd: null pointer");
-  FirstLayerFuse l0{x0, wq0_k_co, mean0, rstd0, beta0, acc, H0, W0, static_cast<const uint32_t*>(ste_mask)};
+  FirstLayerFuse l0{x0, wq0_k_co, mean0, rstd0, beta0, acc, H0, W0};
   return launch_kgemm(dy_hi, dy_lo, wq_ic_k, nullptr, 0, Cin, static_cast<long long>(NB) * H * W, Cin,
                       ksize * ksize * Cout, 1, NB, H, W, Cout, ksize, ksize / 2,
                       static_cast<cudaStream_t>(stream), 2, &l0);
-}
-
-ZKB_API int zkb_conv_first_bwd_derive_dax(double* acc, const float* wq0_k_co, const float* mean0,
-                                          const float* rstd0, int Cout, void* stream) {
-  ZKB_REQUIRE(acc && wq0_k_co && mean0 && rstd0, "conv_first_bwd_derive_dax: null pointer");
-  ZKB_REQUIRE(Cout == 128, "conv_first_bwd_derive_dax: Cout must be 128");
-  conv_first_dax_from_s1_kernel<<<1, 128, 0, static_cast<cudaStream_t>(stream)>>>(acc, wq0_k_co, mean0, rstd0);
-  ZKB_LAUNCH_CHECK("conv_first_dax_from_s1_kernel");
-  return ZKB_OK;
 }
 
 ZKB_API int zkb_conv_first_bwd_finalize(const double* acc, const double* gram, const float* wq0_k_co,

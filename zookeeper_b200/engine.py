@@ -125,28 +125,15 @@ class BinaryNetEngine:
         self._wgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._dgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._prep_fork, self._prep_join, self._prep_pending = torch.cuda.Event(), torch.cuda.Event(), False
-        self.serialize_gemms = os.environ.get("ZKB_SERIALIZE_GEMMS", "0") == "1"
         # first layer's backward inside layer 1's dgrad epilogue (ZKB_FUSE_FIRST_BWD=0: separate kernels)
         self.fuse_first_backward = (os.environ.get("ZKB_FUSE_FIRST_BWD", "1") != "0"
                                     and self._can_fuse_first_backward())
         # BatchNorm-backward sums of layer i-1 inside layer i's dgrad epilogue (conv layers)
-        # the forward leaves the first layer's ste mask for the fused backward (opt-in: measured r1
-        # slower, +0.1 ms in the forward and no gain in the epilogue)
-        self.first_layer_mask = os.environ.get("ZKB_FIRST_MASK", "0") == "1"
         self.fuse_bn_backward_sums = os.environ.get("ZKB_FUSE_BN_BWD", "1") != "0"
-        # bn_finalize / bn_bwd_finalize inside the kernels that consume their results (16 launches
-        # fewer); off by default: measured r1 neutral at batch 4096 and 4-5 % slower at batch 128-512
-        # (every thread repeats the float64 divisions of its channels)
-        self.fold_finalize = os.environ.get("ZKB_FOLD_FINALIZE", "0") == "1"
         # BatchNorm batch statistics inside the forward GEMM epilogue (layers that do not pool)
         self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
         # inference: BatchNorm + sign as integer thresholds inside the GEMM epilogue
         self.fold_eval = self.forward_int8 and os.environ.get("ZKB_FOLD_EVAL", "1") != "0"
-        # training forward as two half-batches on two streams (see _forward_pipelined); off by
-        # default: measured r1, the HBM-bound kernels slow down 3x next to a resident GEMM CTA and
-        # the step does not get shorter (14.3 against 14.1 ms)
-        self.pipeline_forward = os.environ.get("ZKB_PIPELINE_FWD", "0") == "1"
-        self._pipe_events = {k: torch.cuda.Event() for k in ("fin", "s1", "g0", "p0")}
         self._eval_ready = False
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
@@ -199,7 +186,6 @@ class BinaryNetEngine:
         self.acc = torch.zeros(4 * self.n_beta + 2 + 11 * 128 + 90, dtype=torch.float64, device=dev)
         self.l0_acc = self.acc[4 * self.n_beta + 2: 4 * self.n_beta + 2 + 11 * 128]
         self.l0_gram = self.acc[4 * self.n_beta + 2 + 11 * 128:]
-        self.l0_mask = None      # ste mask of the first layer (16 B per output pixel), see _first_layer_forward
         self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
         self.stat = torch.zeros(4 * self.n_beta, dtype=f32, device=dev)  # mean, rstd, mean_da, mean_dax
         self.x0 = torch.zeros(B, H, W, C, dtype=f32, device=dev)
@@ -422,14 +408,6 @@ class BinaryNetEngine:
                 self._pending_bn_sync(L)
                 count *= self.world
             bessel = 1 if L.spec.kind == "conv" else 0
-            last = L.idx == len(self.L) - 1
-            if self.fold_finalize:
-                # mean / rstd / moving statistics are derived inside the normalising kernel
-                self._call("zkb_bn_finalize_apply_sign", zn.ptr(x), int(is_i16), rows, cp, zn.ptr(L.sum), zn.ptr(L.sumsq),
-                           count, BN_EPS, BN_MOMENTUM, bessel, zn.ptr(L.beta), zn.ptr(L.mean), zn.ptr(L.rstd),
-                           zn.ptr(L.mm), zn.ptr(L.mv), 0 if last else zn.ptr(L.s), zn.ptr(L.logits) if last else 0,
-                           0 if last else zn.ptr(getattr(L, "s8", None)))
-                return
             self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, bessel, cp,
                        zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
             mean, rstd = L.mean, L.rstd
@@ -487,115 +465,6 @@ class BinaryNetEngine:
                 self._bn_forward(L, L.y, True, B, fused_stats, training)
             prev = L
 
-    def _forward_pipelined(self, side):
-        """Training forward with the batch cut in two halves that follow each other through the
-        layers on two streams: while the tensor cores work on one half's GEMM, the HBM-bound
-        kernels of the other half (max-pool, BatchNorm + sign) run next to it.  Batch statistics
-        are sums, so both halves add into the same accumulators and a layer is normalised only
-        after both halves have passed its GEMM (and pooling).  Results are identical to
-        :meth:`forward` (same kernels on the same data).  Convolution layers only; the three
-        small dense layers run whole on the main stream."""
-        main = torch.cuda.current_stream(self.device)
-        B = self.B
-        n = (B // 2, B - B // 2)
-        off = (0, B // 2)
-        ev = self._pipe_events
-
-        def part(t, h):
-            return zn.ptr(t[off[h]: off[h] + n[h]]) if t is not None else 0
-
-        # ---- layer 0: statistics over the whole batch, sign per half
-        L = self.L[0]
-        l = L.spec
-        H, W, C = self.input_shape
-        self._tag = "fwd0"
-        self._call("zkb_conv_first_gram", zn.ptr(self.x0), B, H, W, self.l0_gram.data_ptr())
-        self._call("zkb_conv_first_stats_from_gram", self.l0_gram.data_ptr(), zn.ptr(L.wq), l.cout,
-                   zn.ptr(L.sum), zn.ptr(L.sumsq))
-        count = float(L.bn_rows)
-        if self.sync_bn:
-            self._pending_bn_sync(L)
-            count *= self.world
-        self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, 1, L.cp,
-                   zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
-        ev["fin"].record(main)
-        side.wait_event(ev["fin"])
-        if self.first_layer_mask and self.l0_mask is None:
-            self.l0_mask = torch.zeros(L.bn_rows * 4, dtype=torch.int32, device=self.device)
-        per_img = (L.bn_rows // B) * 4            # mask words per image
-        for h, st in ((0, None), (1, side)):
-            if self.first_layer_mask:
-                self._call("zkb_conv_first_bn_sign_mask", part(self.x0, h), zn.ptr(L.wq), n[h], H, W, C, l.cout, l.ksize,
-                           zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.beta), part(L.s, h), part(L.s8, h),
-                           zn.ptr(self.l0_mask[off[h] * per_img:]), on=st)
-            else:
-                self._call("zkb_conv_first_bn_sign", part(self.x0, h), zn.ptr(L.wq), n[h], H, W, C, l.cout, l.ksize,
-                           zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.beta), part(L.s, h), part(L.s8, h), on=st)
-        ev["s1"].record(side)                      # second half's signs are ready
-        prev = L
-        if self._prep_pending:
-            main.wait_event(self._prep_join)
-            self._prep_pending = False
-        # ---- binary conv layers
-        i = 1
-        while i < len(self.L) and self.L[i].spec.kind == "conv":
-            L = self.L[i]
-            l = L.spec
-            self._tag = f"fwd{i}"
-            ih, iw = L.in_hw
-            oh, ow = L.out_hw
-            for h in (0, 1):
-                if h == 1:
-                    main.wait_event(ev["s1"])      # the other half's input signs (side stream)
-                if l.pool:
-                    self._call("zkb_bconv2d_fwd_i8", part(prev.s8, h), zn.ptr(L.w_fwd8), part(L.y, h), n[h], ih, iw,
-                               l.cin, l.cout, l.ksize)
-                else:
-                    self._call("zkb_bconv2d_fwd_i8_stats", part(prev.s8, h), zn.ptr(L.w_fwd8), part(L.y, h), n[h], ih, iw,
-                               l.cin, l.cout, l.ksize, zn.ptr(L.sum), zn.ptr(L.sumsq))
-                if l.pool and h == 0:
-                    ev["g0"].record(main)          # first half pools next to the second half's GEMM
-                    side.wait_event(ev["g0"])
-                    self._call("zkb_maxpool2_i16", part(L.y, 0), n[0], oh, ow, L.cp, part(L.p, 0), part(L.arg, 0),
-                               zn.ptr(L.sum), zn.ptr(L.sumsq), on=side)
-                    ev["p0"].record(side)
-            if l.pool:
-                self._call("zkb_maxpool2_i16", part(L.y, 1), n[1], oh, ow, L.cp, part(L.p, 1), part(L.arg, 1),
-                           zn.ptr(L.sum), zn.ptr(L.sumsq))
-                main.wait_event(ev["p0"])
-            count = float(L.bn_rows)
-            if self.sync_bn:
-                self._pending_bn_sync(L)
-                count *= self.world
-            self._call("zkb_bn_finalize", zn.ptr(L.sum), zn.ptr(L.sumsq), count, BN_EPS, BN_MOMENTUM, 1, L.cp,
-                       zn.ptr(L.mean), zn.ptr(L.rstd), zn.ptr(L.mm), zn.ptr(L.mv))
-            ev["fin"].record(main)
-            side.wait_event(ev["fin"])
-            x = L.p if l.pool else L.y
-            rows = L.bn_rows // B
-            for h, st in ((0, None), (1, side)):
-                self._call("zkb_bn_apply_sign", part(x, h), 1, rows * n[h], L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
-                           zn.ptr(L.beta), part(L.s, h), 0, part(L.s8, h), on=st)
-            ev["s1"].record(side)
-            prev = L
-            i += 1
-        main.wait_event(ev["s1"])
-        # ---- dense layers: whole batch on the main stream
-        for L in self.L[i:]:
-            l = L.spec
-            self._tag = f"fwd{L.idx}"
-            if self.fuse_forward_stats:
-                self._call("zkb_bdense_fwd_i8_stats", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp,
-                           zn.ptr(L.sum), zn.ptr(L.sumsq))
-            else:
-                self._call("zkb_bdense_fwd_i8", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), L.cp, B, l.cin, L.cp)
-            self._bn_forward(L, L.y, True, B, self.fuse_forward_stats, True)
-            prev = L
-
-    def _can_pipeline_forward(self) -> bool:
-        return (self.pipeline_forward and self.forward_int8 and self.fuse_first_backward and self.fuse_forward_stats
-                and self.B >= 2 and self.layers[-1].kind == "dense")
-
     def _first_layer_forward(self, L, training: bool):
         l = L.spec
         H, W, C = self.input_shape
@@ -618,16 +487,8 @@ class BinaryNetEngine:
             mean, rstd = L.mean, L.rstd
         else:
             mean, rstd = L.mm, L.eval_rstd
-        if training and self.fuse_first_backward and self.first_layer_mask:
-            # also leave the ste mask |a| <= 1 (one bit per element) for the fused backward, which
-            # then need not recompute the conv
-            if self.l0_mask is None:
-                self.l0_mask = torch.zeros(L.bn_rows * 4, dtype=torch.int32, device=self.device)
-            self._call("zkb_conv_first_bn_sign_mask", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
-                       zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8), zn.ptr(self.l0_mask))
-        else:
-            self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
-                       zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
+        self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
+                   zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
 
     def _can_fuse_first_backward(self) -> bool:
         """zkb_bconv2d_dgrad_first_bwd is built for: 3x3 'valid' conv of one input channel into 128
@@ -655,12 +516,7 @@ class BinaryNetEngine:
         l = L1.spec
         self._call("zkb_bconv2d_dgrad_first_bwd", zn.ptr(L1.dy_hi), zn.ptr(L1.dy_lo), zn.ptr(L1.w_dgrad),
                    self.B, ih, iw, l.cin, l.cout, l.ksize, zn.ptr(self.x0), H, W, zn.ptr(L0.wq),
-                   zn.ptr(L0.mean), zn.ptr(L0.rstd), zn.ptr(L0.beta),
-                   zn.ptr(self.l0_mask) if self.first_layer_mask else 0, self.l0_acc.data_ptr())
-        self._tag = "bwd0"
-        if self.first_layer_mask:
-            self._call("zkb_conv_first_bwd_derive_dax", self.l0_acc.data_ptr(), zn.ptr(L0.wq), zn.ptr(L0.mean),
-                       zn.ptr(L0.rstd), L0.spec.cout)
+                   zn.ptr(L0.mean), zn.ptr(L0.rstd), zn.ptr(L0.beta), self.l0_acc.data_ptr())
         count = float(L0.bn_rows)
         if self.sync_bn:
             self._all_reduce(self.l0_acc[:256])      # sum da, sum da*xhat; the tap sums stay local
@@ -743,24 +599,15 @@ class BinaryNetEngine:
             else:
                 mode, of32, ohi, olo, arg, H, W = 1, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), 0, 0, 0
             dbeta_scale = (1.0 / self.world) if self.sync_bn else 1.0
-            if self.fold_finalize:
-                self._call("zkb_bn_bwd_finalize_apply", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean),
-                           zn.ptr(L.rstd), zn.ptr(L.beta), zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, dbeta_scale,
-                           zn.ptr(L.dbeta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), ste, mode, of32, ohi, olo, arg, H, W)
-            else:
-                self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, dbeta_scale, L.cp,
-                           zn.ptr(L.dbeta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
-                self._call("zkb_bn_bwd_apply", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
-                           zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), ste, mode, of32, ohi, olo, arg, H, W)
+            self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count, dbeta_scale, L.cp,
+                       zn.ptr(L.dbeta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax))
+            self._call("zkb_bn_bwd_apply", zn.ptr(L.ds), zn.ptr(x), is_i16, rows, L.cp, zn.ptr(L.mean), zn.ptr(L.rstd),
+                       zn.ptr(L.beta), zn.ptr(L.mean_da), zn.ptr(L.mean_dax), ste, mode, of32, ohi, olo, arg, H, W)
             prev = self.L[i - 1]
             if side is not None:
                 ev = self._side_events[i]
                 ev.record(main)          # dy_i is complete (and the gradient arena was zeroed) here
                 side.wait_event(ev)
-                if self.serialize_gemms and pending_wgrad is not None:
-                    # two GEMMs only time-slice the tensor pipe: let the previous layer's wgrad
-                    # finish before this dgrad starts, so that wgrad overlaps HBM-bound kernels only
-                    main.wait_event(pending_wgrad)
             if l.kind == "conv":
                 ih, iw = L.in_hw
                 # dgrad first: it is on the critical path (the next BatchNorm backward needs it)
@@ -775,10 +622,6 @@ class BinaryNetEngine:
                 else:
                     self._call("zkb_bconv2d_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                                B, ih, iw, l.cin, l.cout, l.ksize)
-                if side is not None and self.serialize_gemms:
-                    ev2 = self._dgrad_events[i]
-                    ev2.record(main)     # ... and start this layer's wgrad only after its dgrad
-                    side.wait_event(ev2)
                 self._call("zkb_bconv2d_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
                            B, ih, iw, l.cin, l.cout, l.ksize, on=side)
                 if side is not None:
@@ -837,10 +680,7 @@ class BinaryNetEngine:
             if not preprocessed:
                 self.preprocess(images_u8, labels_i64, index, True, pad_size, aug, seed, self.step_count)
             self.prepare_weights(self._side if use_side else None)
-            if use_side and self._can_pipeline_forward():
-                self._forward_pipelined(self._side)
-            else:
-                self.forward(training=True)
+            self.forward(training=True)
             self.loss_and_grad()
             self.backward(self._side if use_side else None)
             if self.world > 1:
@@ -879,10 +719,7 @@ class BinaryNetEngine:
                 self.preprocess(images_u8, labels_i64, self.index_buf, True, pad_size, None, seed, 0,
                                 step_dev=self._dyn_step)
                 self.prepare_weights(self._side if self.overlap else None)
-                if self.overlap and self._can_pipeline_forward():
-                    self._forward_pipelined(self._side)
-                else:
-                    self.forward(training=True)
+                self.forward(training=True)
                 self.loss_and_grad()
                 self.backward(self._side if self.overlap else None)
                 if self.world > 1:

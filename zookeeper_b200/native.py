@@ -47,8 +47,6 @@ SIGNATURES = {
     "zkb_bconv2d_fwd_i8_sign": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_fwd_i8_sign": [P, P, P, P, L, I, I, I, P],
     "zkb_bn_eval_rstd": [P, F, I, P, P],
-    "zkb_bn_finalize_apply_sign": [P, I, L, I, P, P, D, F, F, I, P, P, P, P, P, P, P, P, P],
-    "zkb_bn_bwd_finalize_apply": [P, P, I, L, I, P, P, P, P, P, D, D, P, P, P, I, I, P, P, P, P, I, I, P],
     "zkb_bn_sign_thresholds": [P, P, P, I, P, P],
     "zkb_maxpool2_sign_i8": [P, I, I, I, I, P, P],
     "zkb_bconv2d_fwd_i8_stats": [P, P, P, I, I, I, I, I, I, P, P, P],
@@ -56,9 +54,7 @@ SIGNATURES = {
     "zkb_bconv2d_dgrad": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_bdense_dgrad": [P, P, P, P, I, I, I, P],
     "zkb_bconv2d_dgrad_bn": [P, P, P, P, I, I, I, I, I, I, P, P, P, P, P, P, P],
-    "zkb_bconv2d_dgrad_first_bwd": [P, P, P, I, I, I, I, I, I, P, I, I, P, P, P, P, P, P, P],
-    "zkb_conv_first_bn_sign_mask": [P, P, I, I, I, I, I, I, P, P, P, P, P, P, P],
-    "zkb_conv_first_bwd_derive_dax": [P, P, P, P, I, P],
+    "zkb_bconv2d_dgrad_first_bwd": [P, P, P, I, I, I, I, I, I, P, I, I, P, P, P, P, P, P],
     "zkb_conv_first_bwd_finalize": [P, P, P, P, P, D, D, P, P, I, P],
     "zkb_conv_first_gram": [P, I, I, I, P, P],
     "zkb_conv_first_stats_from_gram": [P, P, I, P, P, P],
