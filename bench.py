@@ -24,11 +24,15 @@ sys.path.insert(0, ROOT)
 
 METRIC = "BinaryNet train images/sec"
 UNIT = "images/s"
-INPUT_SHAPE = (28, 28, 1)
 NUM_CLASSES = 10
-PAD_SIZE = 32
-BATCH_PER_GPU = 4096      # BASELINE.json configs[1]
+# BASELINE.json configs: [1] MNIST-shaped, batch 4096 per GPU (the headline); [2] CIFAR-10-shaped,
+# batch 256 per GPU.  pad = canvas the training crop is taken from (examples/larq_experiment.py:24-37).
+CONFIGS = {
+    "mnist": {"shape": (28, 28, 1), "pad": 32, "batch": 4096, "name": "MNIST-shaped 28x28x1"},
+    "cifar": {"shape": (32, 32, 3), "pad": 40, "batch": 256, "name": "CIFAR-10-shaped 32x32x3"},
+}
 CPU_SAMPLE_BATCH = 128    # BASELINE.json configs[0] (the reference's own CPU-runnable case)
+DTYPE = "int8 fwd (int32 acc) / bf16x2 bwd (f32 acc) / f32 elementwise"
 
 
 def parse():
@@ -37,23 +41,34 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=BATCH_PER_GPU, help="images per GPU per step")
+    ap.add_argument("--config", default="mnist", choices=sorted(CONFIGS), help="BASELINE.json configs[1] / [2]")
+    ap.add_argument("--batch", type=int, default=None, help="images per GPU per step (default: the config's)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="strong: the config's batch is the GLOBAL batch, split over the GPUs")
     ap.add_argument("--breakdown", action="store_true", help="also print a per-kernel time table (stderr)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-binary-gemm", action="store_true", help="skip the int8-peak / popcount measurements")
     ap.add_argument("--sync-bn", action="store_true")
     ap.add_argument("--graph", action="store_true", help="replay a captured CUDA graph per step (small batches)")
-    return ap.parse_args()
+    args = ap.parse_args()
+    cfg = CONFIGS[args.config]
+    if args.batch is None:
+        args.batch = cfg["batch"] // args.gpus if args.scaling == "strong" else cfg["batch"]
+    args.shape, args.pad = cfg["shape"], cfg["pad"]
+    return args
 
 
-def workload_name(batch):
-    return f"BinaryNet (examples/larq_experiment.py) MNIST-shaped 28x28x1 synthetic, batch {batch}/GPU"
+def workload_name(args, batch=None):
+    return (f"BinaryNet (examples/larq_experiment.py) {CONFIGS[args.config]['name']} synthetic, "
+            f"batch {args.batch if batch is None else batch}/GPU")
 
 
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle restatement of the reference's TF/Larq path, timed on the host cores
 # ------------------------------------------------------------------------------------------------
-def cpu_train_steps(n_steps, warmup, batch, budget_s=None):
-    """Time full train steps (preprocess + fwd + bwd + Adam + clip, fp32) of the CPU restatement."""
+def cpu_train_steps(n_steps, warmup, batch, budget_s=None, shape=(28, 28, 1), pad=32):
+    """Time full train steps (preprocess + fwd + bwd + Adam + clip, fp32) of the CPU restatement.
+    With budget_s the loop stops early once that much wall time has gone by (at least one timed step)."""
     import numpy as np
     import torch
 
@@ -61,48 +76,66 @@ def cpu_train_steps(n_steps, warmup, batch, budget_s=None):
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    layers = O.binarynet_layers(INPUT_SHAPE, 128, 1024, NUM_CLASSES)
+    layers = O.binarynet_layers(shape, 128, 1024, NUM_CLASSES)
     p = O.glorot_uniform_params(layers, 0)
     m = {k: np.zeros_like(v) for k, v in p.items()}
     v = {k: np.zeros_like(v_) for k, v_ in p.items()}
     rng = np.random.default_rng(1234)
-    img = rng.integers(0, 256, (batch,) + INPUT_SHAPE, dtype=np.uint8)
+    img = rng.integers(0, 256, (batch,) + tuple(shape), dtype=np.uint8)
     lab = rng.integers(0, NUM_CLASSES, (batch,)).astype(np.int64)
     times = []
     t_begin = time.perf_counter()
     for s in range(warmup + n_steps):
         t0 = time.perf_counter()
-        aug = O.augmentation_params(1234, s, batch, PAD_SIZE, INPUT_SHAPE[0], INPUT_SHAPE[1])
-        x = O.preprocess(img, INPUT_SHAPE[:2], True, PAD_SIZE, aug)
+        aug = O.augmentation_params(1234, s, batch, pad, shape[0], shape[1])
+        x = O.preprocess(img, shape[:2], True, pad, aug)
         r = O.forward_backward(p, layers, x, lab, torch.float32)
         p, m, v = O.adam_clip_step(p, r.grads, m, v, s + 1, dtype=np.float32)
         dt = time.perf_counter() - t0
         if s >= warmup:
             times.append(dt)
-        if budget_s is not None and s >= warmup and time.perf_counter() - t_begin > budget_s:
-            break
+        if budget_s is not None and time.perf_counter() - t_begin > budget_s:
+            if s < warmup:            # over budget before the first timed step: time exactly one
+                warmup = s + 1
+                n_steps = 1
+            elif times:
+                break
     return times, cores
 
 
 def run_reference(args):
+    """The reference's own implementation of the path timed on the host cores.  TensorFlow / Larq
+    cannot be installed here (no network, not vendored under the reference), so this is the oracle
+    port, run on the SAME config as the GPU arm (same input shape, same per-GPU batch).  A batch-4096
+    CPU step takes ~10 s, so the run is bounded: one warm-up step and as many of the requested timed
+    steps as fit in REF_BUDGET_S seconds (at least one)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    times, cores = cpu_train_steps(args.steps, args.warmup, CPU_SAMPLE_BATCH)
+    budget = float(os.environ.get("ZKB_REF_BUDGET_S", "150"))
+    warm = min(args.warmup, 1)
+    times, cores = cpu_train_steps(args.steps, warm, args.batch, budget_s=budget, shape=args.shape, pad=args.pad)
     total = sum(times)
-    value = CPU_SAMPLE_BATCH * len(times) / total
-    sample = (f"{len(times)} steps of batch {CPU_SAMPLE_BATCH} (bounded sample of the batch-{args.batch} workload), "
-              f"torch-CPU fp32 restatement of the TF/Larq path, {cores} threads")
+    value = args.batch * len(times) / total
+    sample = (f"{len(times)} timed train steps of batch {args.batch} (the GPU arm's per-GPU batch; {warm} warm-up, "
+              f"bounded to ~{budget:.0f} s of the {args.steps} requested), torch-CPU fp32 restatement of the TF/Larq path, "
+              f"{cores} threads")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": len(times), "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "steps": len(times), "warmup": warm, "ms_per_step": 1e3 * total / len(times),
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": workload_name(args.batch), "sample_batch": CPU_SAMPLE_BATCH},
+        "config": {"workload": workload_name(args), "global_batch": args.batch, "parallelism": "cpu",
+                   "steps_requested": args.steps, "warmup_requested": args.warmup},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    if args.config == "mnist" and args.batch != CPU_SAMPLE_BATCH and os.environ.get("ZKB_REF_SKIP_B128") != "1":
+        # second key: the reference's own CPU-runnable case (BASELINE.json configs[0], batch 128)
+        t2, _ = cpu_train_steps(20, 2, CPU_SAMPLE_BATCH, budget_s=15.0, shape=args.shape, pad=args.pad)
+        line["cpu_baseline_b128"] = {"value": CPU_SAMPLE_BATCH * len(t2) / sum(t2), "unit": UNIT, "cores": cores,
+                                     "kind": "port", "sample": f"{len(t2)} train steps of batch {CPU_SAMPLE_BATCH} (configs[0])"}
     emit(line)
 
 
@@ -174,27 +207,26 @@ def algorithmic_work(eng, name, tag):
         M, N, K = B * oh * ow, l.cout, l.ksize * l.ksize * l.cin
     else:
         M, N, K = B, l.cout, l.cin
-    if name == "zkb_bconv2d_dgrad_first_bwd":
-        # the dgrad GEMM plus the first layer's recomputed conv / BatchNorm-backward sums in its
-        # epilogue (about 60 flop per output element: 9-tap conv, 2 + 18 accumulating FMAs)
-        return ("flop", 2.0 * M * N * K + 60.0 * B * L.in_hw[0] * L.in_hw[1] * l.cin)
-    if name in ("zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
+    # (zkb_bconv2d_dgrad_first_bwd: the tensor-pipe figure counts the GEMM only; the CUDA-core work
+    # of its fused first-layer epilogue is not added)
+    if name in ("zkb_bconv2d_dgrad_first_bwd", "zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
                 "zkb_bconv2d_wgrad", "zkb_bdense_wgrad", "zkb_bconv2d_fwd_i8_stats", "zkb_bdense_fwd_i8_stats",
                 "zkb_bconv2d_dgrad_bn"):
         return ("flop", 2.0 * M * N * K)  # split terms are implementation overhead, not counted
     rows, C = L.bn_rows, L.cp
     xb = 4 if i == 0 else 2
+    img_bytes = B * eng.input_shape[0] * eng.input_shape[1] * eng.input_shape[2] * 4
     table = {
         "zkb_bn_stats": rows * C * xb,
         "zkb_bn_apply_sign": rows * C * (xb + 2),
         "zkb_maxpool2_i16": (M * N * 2) + rows * C * 3,
         "zkb_bn_bwd_reduce": rows * C * (4 + xb),
         "zkb_bn_bwd_apply": rows * C * (4 + xb) + M * N * 4,
-        "zkb_conv_first_bn_stats": B * 28 * 28 * 4,
-        "zkb_conv_first_gram": B * 28 * 28 * 4,
-        "zkb_conv_first_bn_sign": M * N * 2 + B * 28 * 28 * 4,
-        "zkb_conv_first_bwd_reduce": M * N * 4 + B * 28 * 28 * 4,
-        "zkb_conv_first_bwd_wgrad": M * N * 4 + B * 28 * 28 * 4,
+        "zkb_conv_first_bn_stats": img_bytes,
+        "zkb_conv_first_gram": img_bytes,
+        "zkb_conv_first_bn_sign": M * N * 3 + img_bytes,      # bf16 + int8 sign per output element
+        "zkb_conv_first_bwd_reduce": M * N * 4 + img_bytes,
+        "zkb_conv_first_bwd_wgrad": M * N * 4 + img_bytes,
     }
     if name in table:
         return ("byte", float(table[name]))
@@ -210,6 +242,70 @@ def global_work(eng, name):
     if name == "zkb_adam_clip":
         return ("byte", 28.0 * (eng.n_kernel + eng.n_beta) / 2)  # two launches: kernels, betas
     return None
+
+
+# ------------------------------------------------------------------------------------------------
+# binary-GEMM roofline: measured int8 tensor-pipe peak and the CUDA-core popcount candidate
+# ------------------------------------------------------------------------------------------------
+def _time_loop(fn, n, torch):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def measure_int8_peak(torch, dev):
+    """cuBLASLt int8 GEMM (torch._int_mm) at 8192^3, the way MEASURED_PEAKS.json measured bf16: best
+    of 10 single calls (burst) and back-to-back calls for ~1.5 s (sustained).  2*N^3 ops per call."""
+    n = 8192
+    try:
+        a = torch.randint(-1, 2, (n, n), dtype=torch.int8, device=dev)
+        b = torch.randint(-1, 2, (n, n), dtype=torch.int8, device=dev).t().contiguous().t()
+        for _ in range(3):
+            torch._int_mm(a, b)
+        torch.cuda.synchronize()
+    except Exception as exc:  # library GEMM not available for this shape / build: report, do not guess
+        return {"unavailable": f"{type(exc).__name__}: {str(exc)[:160]}"}
+    ops = 2.0 * n ** 3
+    burst = min(_time_loop(lambda: torch._int_mm(a, b), 1, torch) for _ in range(10))
+    t_begin, ms, calls = time.perf_counter(), 0.0, 0
+    while time.perf_counter() - t_begin < 1.5:
+        ms += _time_loop(lambda: torch._int_mm(a, b), 100, torch) * 100
+        calls += 100
+    return {"burst_pops": ops / (burst * 1e-3) / 1e15, "sustained_pops": ops / (ms / calls * 1e-3) / 1e15,
+            "how": f"torch._int_mm int8 {n}^3 (cuBLASLt): best of 10 (burst), {calls} back-to-back calls (sustained)"}
+
+
+def measure_popc_path(torch, zn, dev, M=4096, K=4608, N=1024):
+    """north_star item 3's other candidate at dense1's shape: warp-ballot sign + bit-pack
+    (zkb_sign_pack, HBM-bound: 4 B read + 1/8 B write per element) and the CUDA-core XNOR-popcount
+    GEMM over the packed words (zkb_bgemm_popc), next to the tcgen05 kind::i8 GEMM on the same shape."""
+    a = torch.randn(M, K, device=dev)
+    w = torch.randn(N, K, device=dev)
+    pa = torch.empty(M, K // 32, dtype=torch.int32, device=dev)
+    pw = torch.empty(N, K // 32, dtype=torch.int32, device=dev)
+    y = torch.empty(M, N, dtype=torch.int32, device=dev)
+    a8 = torch.where(a >= 0, 1, -1).to(torch.int8)
+    w8 = torch.where(w >= 0, 1, -1).to(torch.int8)
+    y16 = torch.empty(M, N, dtype=torch.int16, device=dev)
+    pack = lambda: zn.call("zkb_sign_pack", zn.ptr(a), zn.ptr(pa), a.numel(), 0, 0)
+    zn.call("zkb_sign_pack", zn.ptr(w), zn.ptr(pw), w.numel(), 0, 0)
+    popc = lambda: zn.call("zkb_bgemm_popc", zn.ptr(pa), zn.ptr(pw), zn.ptr(y), N, M, N, K // 32, 0)
+    i8 = lambda: zn.call("zkb_bdense_fwd_i8", zn.ptr(a8), zn.ptr(w8), zn.ptr(y16), N, M, K, N, 0)
+    for f in (pack, popc, i8):
+        f(); f()
+    torch.cuda.synchronize()
+    t_pack, t_popc, t_i8 = (_time_loop(f, 10, torch) for f in (pack, popc, i8))
+    ok = bool(torch.equal(y.to(torch.int16), y16))
+    ops = 2.0 * M * N * K
+    return {"shape": f"{M}x{K}x{N} (dense1 at batch {M})", "identical_integers": ok,
+            "sign_pack": {"ms": t_pack, "gbs": a.numel() * (4 + 1 / 8) / (t_pack * 1e-3) / 1e9,
+                          "bytes_model": "4 B read + 1/8 B write per element"},
+            "popc_gemm": {"ms": t_popc, "pops": ops / (t_popc * 1e-3) / 1e15},
+            "tcgen05_i8_gemm": {"ms": t_i8, "pops": ops / (t_i8 * 1e-3) / 1e15}}
 
 
 _REAL_STDOUT = None
@@ -255,6 +351,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     B = args.batch
+    INPUT_SHAPE, PAD_SIZE = tuple(args.shape), args.pad
     n_pool = 8 * B
     g = torch.Generator(device="cpu").manual_seed(1234 + rank)
     images = torch.randint(0, 256, (n_pool,) + INPUT_SHAPE, generator=g, dtype=torch.uint8)
@@ -421,7 +518,56 @@ def main():
         ar_ms = max_over_ranks(a0.elapsed_time(a1)) / 20
         nbytes = buf.numel() * 4
         allreduce = {"bytes": nbytes, "ms": ar_ms, "bus_gbs": 2.0 * (world - 1) / world * nbytes / (ar_ms * 1e-3) / 1e9,
-                     "backend": "nccl " + ".".join(str(v) for v in torch.cuda.nccl.version())}
+                     "backend": "nccl " + ".".join(str(v) for v in torch.cuda.nccl.version()),
+                     "buckets": [[int(lo), int(hi)] for _, lo, hi in eng.grad_buckets],
+                     "schedule": "buckets in reverse layer order, each started behind its last wgrad GEMM on the side stream"}
+        # what the collective costs the step: the same steps with the gradients left local
+        eng.reduce_gradients = False
+        for _ in range(3):
+            resident_step()
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(args.steps):
+            resident_step()
+        c1.record()
+        barrier()
+        eng.reduce_gradients = True
+        local_ms = max_over_ranks(c0.elapsed_time(c1)) / args.steps
+        allreduce["step_ms_without_allreduce"] = local_ms
+        allreduce["exposed_ms_per_step"] = ms_total / args.steps - local_ms
+
+    # ---- binary GEMM (BASELINE.json metric "binary-GEMM % of roofline"): every forward GEMM of the
+    # serial per-launch pass against an int8 peak measured in this run, and the popcount candidate
+    binary_gemm = None
+    if rank == 0 and not args.no_binary_gemm:
+        from zookeeper_b200 import native as zn
+        i8 = measure_int8_peak(torch, dev)
+        layers_bg, tot_ops, tot_ms = {}, 0.0, 0.0
+        for (name, tag), v in per.items():
+            if "_fwd_i8" not in name:
+                continue
+            w = algorithmic_work(eng, name, tag)
+            ms = sum(v) / len(v)
+            tot_ops += w[1]
+            tot_ms += ms
+            row = {"kernel": name, "ms": round(ms, 4), "pops": round(w[1] / (ms * 1e-3) / 1e15, 3),
+                   "frac_nominal": round(w[1] / (ms * 1e-3) / 4.5e15, 3)}
+            if "sustained_pops" in i8:
+                row["frac_measured"] = round(w[1] / (ms * 1e-3) / 1e15 / i8["sustained_pops"], 3)
+            layers_bg[tag] = row
+        binary_gemm = {"pipe": "tcgen05 kind::i8 (+-1 as int8, int32 accumulate)", "int8_peak_measured": i8,
+                       "int8_peak_nominal_pops": 4.5, "layers": layers_bg,
+                       "achieved_pops": tot_ops / (tot_ms * 1e-3) / 1e15 if tot_ms else None,
+                       "ops_per_step": tot_ops, "ms_per_step": tot_ms,
+                       "frac_nominal": tot_ops / (tot_ms * 1e-3) / 4.5e15 if tot_ms else None}
+        if "sustained_pops" in i8 and tot_ms:
+            binary_gemm["frac"] = binary_gemm["achieved_pops"] / i8["sustained_pops"]
+            binary_gemm["frac_vs_burst"] = binary_gemm["achieved_pops"] / i8["burst_pops"]
+        try:
+            binary_gemm["popcount_candidate"] = measure_popc_path(torch, zn, dev)
+        except Exception as exc:
+            binary_gemm["popcount_candidate"] = {"error": str(exc)[:200]}
 
     # ---- roofline of the dominant kernel
     peaks = {}
@@ -444,10 +590,16 @@ def main():
             ach = work[1] / avg_s / 1e9
             roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                         "traffic": None}
+        # dram bytes of this kernel per launch: NOT measured by this run -- a stored figure from one
+        # `ncu --set full` capture of the same kernel at the same shape (file, date and commit named)
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-                roofline["traffic"] = json.load(f).get(f"{dominant[0]}[{dominant[1]}]")
-        except OSError:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                tr = json.load(f)
+            ent = tr.get("kernels", {}).get(f"{dominant[0]}[{dominant[1]}]") if args.config == "mnist" and B == 4096 else None
+            if ent:
+                roofline["traffic"] = ent["dram_bytes"]
+                roofline["traffic_source"] = f"stored ncu capture {ent['capture']} ({ent['date']}, commit {ent['commit']}); not re-measured in this run"
+        except (OSError, KeyError, ValueError):
             pass
         # the same launch timed alone (serial per-launch pass before the timed region): in the timed
         # region the step runs on two streams and this kernel shares the SMs with a wgrad GEMM
@@ -466,8 +618,8 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(B), "global_batch": B * world, "parallelism": f"dp{world}",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
+            "config": {"workload": workload_name(args), "global_batch": B * world, "parallelism": f"dp{world}",
                        "batchnorm": "sync" if eng.sync_bn else "per-replica",
                        "launch": "cuda-graph replay" if args.graph else "per-kernel launches, 2 streams",
                        "l2": "working set (GBs of activations per step) far larger than the 126 MB L2; no flush"},
@@ -478,13 +630,20 @@ def main():
         }
         if allreduce:
             line["allreduce"] = allreduce
+        if binary_gemm:
+            line["binary_gemm"] = binary_gemm
         if world == 1 and not args.no_cpu_baseline:
-            times, cores = cpu_train_steps(40, 2, CPU_SAMPLE_BATCH, budget_s=20.0)
-            v = CPU_SAMPLE_BATCH * len(times) / sum(times)
+            # same config as the GPU arm (bounded: ~25 s of CPU work), and configs[0]'s batch 128
+            times, cores = cpu_train_steps(2, 1, B, budget_s=25.0, shape=INPUT_SHAPE, pad=PAD_SIZE)
+            v = B * len(times) / sum(times)
             line["cpu_baseline"] = {
                 "value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                "sample": f"{len(times)} train steps of batch {CPU_SAMPLE_BATCH} (BASELINE.json configs[0]) of the "
-                          f"torch-CPU fp32 restatement, {cores} threads"}
+                "sample": f"{len(times)} train step(s) of batch {B} (this run's config) of the torch-CPU fp32 "
+                          f"restatement of the TF/Larq path, {cores} threads"}
+            if B != CPU_SAMPLE_BATCH and args.config == "mnist":
+                t2, _ = cpu_train_steps(20, 2, CPU_SAMPLE_BATCH, budget_s=10.0, shape=INPUT_SHAPE, pad=PAD_SIZE)
+                line["cpu_baseline_b128"] = {"value": CPU_SAMPLE_BATCH * len(t2) / sum(t2), "unit": UNIT, "cores": cores,
+                                             "kind": "port", "sample": f"{len(t2)} train steps of batch {CPU_SAMPLE_BATCH} (configs[0])"}
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -23,13 +23,19 @@ def sign_pm1(w: np.ndarray) -> np.ndarray:
 
 def conv_forward_at(s_patches: np.ndarray, w_hwio: np.ndarray) -> np.ndarray:
     """s_patches int [n, kh, kw, cin] (zeros outside the image) -> exact integers [n, cout]."""
-    return np.einsum("nhwc,hwco->no", s_patches.astype(np.int64), sign_pm1(w_hwio))
+    # float64 BLAS is exact here (|sum| <= 9 * 512 << 2^53) and much faster than an int64 einsum
+    n = s_patches.shape[0]
+    y = s_patches.reshape(n, -1).astype(np.float64) @ sign_pm1(w_hwio).reshape(-1, w_hwio.shape[-1]).astype(np.float64)
+    return np.rint(y).astype(np.int64)
 
 
 def conv_dgrad_at(dy_patches: np.ndarray, w_hwio: np.ndarray) -> np.ndarray:
     """dy_patches f64 [n, kh, kw, cout] with patch[kh,kw] = dy[q - (kh-pad, kw-pad)] (zeros outside)
     -> ds f64 [n, cin]."""
-    return np.einsum("nhwo,hwco->nc", dy_patches.astype(np.float64), sign_pm1(w_hwio).astype(np.float64))
+    n = dy_patches.shape[0]
+    q = sign_pm1(w_hwio).astype(np.float64)                       # [kh, kw, ci, co]
+    qt = q.transpose(0, 1, 3, 2).reshape(-1, q.shape[2])          # [(kh, kw, co), ci]
+    return dy_patches.astype(np.float64).reshape(n, -1) @ qt
 
 
 def conv_wgrad_entries(s_shifted: np.ndarray, dy: np.ndarray) -> np.ndarray:
@@ -40,7 +46,7 @@ def conv_wgrad_entries(s_shifted: np.ndarray, dy: np.ndarray) -> np.ndarray:
 
 
 def dense_forward(s_rows: np.ndarray, w_kn: np.ndarray) -> np.ndarray:
-    return s_rows.astype(np.int64) @ sign_pm1(w_kn)
+    return np.rint(s_rows.astype(np.float64) @ sign_pm1(w_kn).astype(np.float64)).astype(np.int64)
 
 
 def dense_dgrad(dy_rows: np.ndarray, w_kn: np.ndarray) -> np.ndarray:

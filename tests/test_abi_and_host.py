@@ -177,6 +177,11 @@ def test_dataset_contract_and_plan_chain():
     pos = {int(v): k for k, v in enumerate(first_epoch)}
     assert all(k >= v - 39 for v, k in pos.items())
     assert not np.array_equal(first_epoch, np.arange(96))
+    # repeat() before batch(): the 4-sample tail of pass 1 opens the next batch (tf.data semantics)
+    seventh = next(it)
+    assert set(seventh[:4].tolist()) == set(range(100)) - set(first_epoch.tolist())
+    two_passes = np.concatenate([first_epoch, seventh] + [next(it) for _ in range(5)] + [next(it)[:8]])
+    assert len(two_passes) == 200 and sorted(two_passes.tolist()) == sorted(list(range(100)) * 2)
     seq = plan.batch(32)
     batches = list(seq.index_stream())
     assert len(batches) == 3 and np.array_equal(batches[0], np.arange(32))   # remainder dropped
@@ -199,9 +204,9 @@ def test_bench_reference_arm_prints_one_contract_line():
     line with the keys the driver reads; no GPU needed."""
     import json
 
-    env = dict(os.environ, PYTHONPATH=ROOT)
+    env = dict(os.environ, PYTHONPATH=ROOT, ZKB_REF_SKIP_B128="1")
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
-                        "--warmup", "1"], capture_output=True, text=True, env=env, timeout=600)
+                        "--warmup", "1", "--batch", "32"], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
     assert len(lines) == 1, r.stdout
@@ -211,3 +216,6 @@ def test_bench_reference_arm_prints_one_contract_line():
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
     assert d["e2e"]["value"] == d["value"] and "workload" in d["config"]
+    # the arm runs the batch it was asked for (the GPU arm's), and says so
+    assert d["config"]["global_batch"] == 32 and "batch 32/GPU" in d["config"]["workload"]
+    assert "batch 32" in d["cpu_baseline"]["sample"]

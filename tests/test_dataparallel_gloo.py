@@ -58,6 +58,19 @@ def _worker(rank, world, port, out_dir):
                      loss=total_loss.numpy())
         with pytest.raises(ValueError, match="not divisible"):
             dp.shard(np.arange(B + 1))
+
+        # bucketed gradient all-reduce as the engine issues it: the buckets of the flat arena are
+        # started one by one (async handles) and joined at the end -- same sums as one collective
+        from zookeeper_b200.engine import gradient_buckets
+
+        k_off = np.array([0, 40, 1000, 3000, 3016])
+        arena = torch.arange(3016 + 24, dtype=torch.float64) * (rank + 1)
+        whole = arena.clone()
+        dp.all_reduce_sum_(whole)
+        works = [dp.all_reduce_sum_async_(arena[lo:hi]) for _, lo, hi in gradient_buckets(k_off, 24, min_bytes=4000)]
+        for wk in works:
+            wk.wait()
+        assert torch.equal(arena, whole)
     finally:
         dist.destroy_process_group()
 
@@ -82,6 +95,26 @@ def test_two_rank_shards_reproduce_single_process(tmp_path):
     np.testing.assert_allclose(got["grad"], w.grad.reshape(-1).numpy(), rtol=1e-10, atol=1e-14)
 
 
+def test_gradient_buckets_tile_the_arena_in_backward_order():
+    """Reverse-layer-order buckets: disjoint slices that cover [betas | kernels] exactly, dense
+    layers first, the beta prefix and the first layers' kernels last."""
+    sys.path.insert(0, ROOT)
+    from zookeeper_b200.engine import binarynet_layers, gradient_buckets
+
+    ls = binarynet_layers()
+    ks = [l.ksize * l.ksize * l.cin * l.cout if l.kind == "conv" else l.cin * l.cout for l in ls]
+    k_off = np.concatenate([[0], np.cumsum([(s + 3) // 4 * 4 for s in ks])])
+    kbase = 3904
+    b = gradient_buckets(k_off, kbase)
+    assert [x[0] for x in b] == [6, 5, 0]                       # dense1..3 | conv6 | the rest + betas
+    assert b[0][2] == kbase + k_off[-1] and b[-1][1] == 0
+    assert all(b[i][1] == b[i + 1][2] for i in range(len(b) - 1))
+    assert all((hi - lo) * 4 >= 8 << 20 for _, lo, hi in b[:-1])
+    assert b[0][1] == kbase + k_off[6] and b[1][1] == kbase + k_off[5]
+    # a small model is one bucket
+    assert gradient_buckets(np.array([0, 100, 200]), 8) == [(0, 0, 208)]
+
+
 def test_single_process_is_a_no_op():
     sys.path.insert(0, ROOT)
     from zookeeper_b200.dataparallel import DataParallel
@@ -92,3 +125,4 @@ def test_single_process_is_a_no_op():
     assert torch.equal(dp.reduce_gradients_(t.clone()), t)
     assert np.array_equal(dp.shard(np.arange(6)), np.arange(6))
     assert dp.global_count(10, sync=True) == 10.0
+    assert dp.all_reduce_sum_async_(t) is None

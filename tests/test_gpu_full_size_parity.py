@@ -8,7 +8,10 @@ each GEMM are gathered on the GPU and the same entries are recomputed on the CPU
 checked in isolation:
   * binary conv / dense forward: >= 2048 random output pixels x all channels, BIT-EXACT;
   * dgrad: >= 2048 random input pixels x all channels of ds, 1e-5 (Frobenius over the sample);
-  * wgrad: 9 taps x 8 input x 32 output channels (a dot product over ALL pixels each), 1e-5;
+  * wgrad: 9 taps x 8 input x 32 output channels (a dot product over ALL pixels each), 1e-4: an
+    entry sums up to 2.8 M products in f32 (tensor-memory accumulators, then f32 reductions of the
+    pixel splits), so what is left at this size is f32 accumulation error -- measured 1e-5..3e-5 --
+    not the bf16 hi/lo split (3e-6); the small-size GEMM tests keep 1e-5;
   * max-pool value and first-max slot, BatchNorm statistics, sign, BatchNorm backward (sums over all
     rows of sampled channels, dy at all rows of those channels), loss, dbeta: 1e-4 or tighter.
 The ste mask |a| <= 1 is a discontinuity: an element whose |a| lies within float32 rounding of 1
@@ -16,6 +19,8 @@ may legitimately be decided either way, and at 2.8 M pixels per channel a handfu
 Sums that depend on the mask are therefore compared with a slack equal to what those elements can
 contribute (oracle/sampled.py: bn_backward_columns), elementwise quantities skip them.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -25,7 +30,16 @@ pytestmark = pytest.mark.gpu
 B = 4096
 N_PIX = 2048
 GEMM_TOL = 1e-5
+WGRAD_TOL = 1e-4     # see the module docstring
 STEP_TOL = 1e-4
+REPORT = {}
+
+
+def _note(layer, what, value, tol):
+    """Record a measured deviation (written to gpurun_out/full_size_parity.json at module teardown)
+    and assert it."""
+    REPORT[f"layer{layer}.{what}"] = {"value": float(value), "tol": tol}
+    assert value < tol, f"layer {layer}: {what} = {value:.3g} (tolerance {tol:g})"
 
 
 def _rel(a, b):
@@ -76,8 +90,6 @@ def _hi_lo(L, rows=None, cols=None):
 def step4096(native_lib):
     """One batch-4096 step (no update, so kernels stay what the sign weights were prepared from) on
     the default engine and on one with the separate first-layer backward kernels (it stores ds_0)."""
-    import os
-
     from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
 
     g = torch.Generator(device="cpu").manual_seed(4096)
@@ -106,7 +118,12 @@ def step4096(native_lib):
         else:
             os.environ["ZKB_FUSE_FIRST_BWD"] = saved
     assert engines[0].fuse_first_backward and not engines[1].fuse_first_backward
-    return engines[0], engines[1], lab
+    yield engines[0], engines[1], lab
+    import json
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "full_size_parity.json"), "w") as f:
+            json.dump({"batch": B, "deviations": REPORT}, f, indent=1, sort_keys=True)
 
 
 def _gen(seed):
@@ -162,8 +179,9 @@ def test_binary_conv_layer_at_batch_4096(step4096, i):
     r = S.bn_backward_columns(ds, x, mean_e, rstd_e, beta_e, ste=True)
     for name, ref, slack in (("sum_da", r["sum_da"], r["slack_da"]), ("sum_dax", r["sum_dax"], r["slack_dax"])):
         got = _f64(getattr(L, name)[ch])
-        assert S.excess(got - ref, slack) <= STEP_TOL * np.linalg.norm(ref), f"layer {i}: {name}"
-    assert S.excess(_f64(L.dbeta[ch]) - r["sum_da"], r["slack_da"]) <= STEP_TOL * np.linalg.norm(r["sum_da"])
+        _note(i, name, S.excess(got - ref, slack) / np.linalg.norm(ref), STEP_TOL)
+    _note(i, "dbeta", S.excess(_f64(L.dbeta[ch]) - r["sum_da"], r["slack_da"]) / np.linalg.norm(r["sum_da"]), STEP_TOL)
+    REPORT[f"layer{i}.border_elements"] = {"value": int(r["border"].sum()), "tol": None}
     # dy = BatchNorm backward with the ENGINE's means (their parity is the line above), scattered
     # through the pool's first-max slot where the layer pools
     mda, mdx = _f64(L.mean_da[ch]), _f64(L.mean_dax[ch])
@@ -182,7 +200,7 @@ def test_binary_conv_layer_at_batch_4096(step4096, i):
             fkeep[:, (k >> 1):2 * ph:2, (k & 1):2 * pw:2] &= (k4 | ~sel)
         dy_ref, keep = full.reshape(-1, 16), fkeep.reshape(-1, 16)
     dy_eng = _hi_lo(L, cols=ch)
-    assert _rel(dy_eng * keep, dy_ref * keep) < GEMM_TOL, f"layer {i}: dy"
+    _note(i, "bn_backward_dy", _rel(dy_eng * keep, dy_ref * keep), GEMM_TOL)
 
     # ---- dgrad GEMM (output: gradient w.r.t. the previous sign map)
     Pd = P if P.ds is not None else eng_u.L[i - 1]
@@ -190,14 +208,14 @@ def test_binary_conv_layer_at_batch_4096(step4096, i):
     qpix = torch.randint(0, B * ih * iw, (N_PIX,), device="cuda", generator=g)
     dyp = _f64(_patches(src.dy_hi, qpix, True)) + _f64(_patches(src.dy_lo, qpix, True))
     ds_ref = S.conv_dgrad_at(dyp[..., : l.cout], w)
-    assert _rel(_f64(Pd.ds.reshape(-1, l.cin)[qpix]), ds_ref) < GEMM_TOL, f"layer {i}: dgrad"
+    _note(i, "dgrad", _rel(_f64(Pd.ds.reshape(-1, l.cin)[qpix]), ds_ref), GEMM_TOL)
 
     # ---- wgrad GEMM: every entry is a dot product over all B*oh*ow pixels
     ci = torch.randperm(l.cin, device="cuda", generator=g)[:8].sort().values
     co = torch.randperm(l.cout, device="cuda", generator=g)[:32].sort().values
     dw_ref = S.conv_wgrad_entries(_shifted_columns(P.s, ci).cpu().numpy(), _hi_lo(L, cols=co))
     dw_eng = _f64(L.dkernel.reshape(9, l.cin, l.cout)[:, ci][:, :, co])
-    assert _rel(dw_eng, dw_ref) < GEMM_TOL, f"layer {i}: wgrad"
+    _note(i, "wgrad", _rel(dw_eng, dw_ref), WGRAD_TOL)
 
 
 @pytest.mark.parametrize("i", [6, 7, 8])
@@ -238,24 +256,24 @@ def test_binary_dense_layer_at_batch_4096(step4096, i):
     r = S.bn_backward_columns(ds, x, mean_e, rstd_e, beta_e, ste=not last)
     for name, ref, slack in (("sum_da", r["sum_da"], r["slack_da"]), ("sum_dax", r["sum_dax"], r["slack_dax"])):
         got = _f64(getattr(L, name)[: l.cout])
-        assert S.excess(got - ref, slack) <= STEP_TOL * np.linalg.norm(ref), f"layer {i}: {name}"
-    assert S.excess(_f64(L.dbeta[: l.cout]) - r["sum_da"], r["slack_da"]) <= STEP_TOL * np.linalg.norm(r["sum_da"])
+        _note(i, name, S.excess(got - ref, slack) / np.linalg.norm(ref), STEP_TOL)
+    _note(i, "dbeta", S.excess(_f64(L.dbeta[: l.cout]) - r["sum_da"], r["slack_da"]) / np.linalg.norm(r["sum_da"]), STEP_TOL)
     mda, mdx = _f64(L.mean_da[: l.cout]), _f64(L.mean_dax[: l.cout])
     da = ds if last else np.where(np.abs(a) <= 1.0, ds, 0.0)
     dy_ref = rstd_e * (da - mda - r["xhat"] * mdx)
     keep = ~r["border"]
     dy_eng = _hi_lo(L)[:, : l.cout]
-    assert _rel(dy_eng * keep, dy_ref * keep) < GEMM_TOL, f"layer {i}: dy"
+    _note(i, "bn_backward_dy", _rel(dy_eng * keep, dy_ref * keep), GEMM_TOL)
     if L.cp > l.cout:
         assert float(_hi_lo(L)[:, l.cout:].__abs__().max()) == 0.0     # padded columns stay zero
     # dgrad: 64 random rows x all K columns; wgrad: 64 x min(64, N) entries over all 4096 rows
     rows = torch.randint(0, B, (64,), device="cuda", generator=g)
     ds_ref = S.dense_dgrad(_hi_lo(L, rows=rows)[:, : l.cout], w)
-    assert _rel(_f64(P.ds.reshape(B, -1)[rows]), ds_ref) < GEMM_TOL, f"layer {i}: dgrad"
+    _note(i, "dgrad", _rel(_f64(P.ds.reshape(B, -1)[rows]), ds_ref), GEMM_TOL)
     ks = torch.randperm(l.cin, device="cuda", generator=g)[:64].sort().values
     ns = torch.randperm(l.cout, device="cuda", generator=g)[: min(64, l.cout)].sort().values
     dw_ref = S.dense_wgrad_entries(s_prev8[:, ks].cpu().numpy(), _hi_lo(L, cols=ns))
-    assert _rel(_f64(L.dkernel.reshape(l.cin, l.cout)[ks][:, ns]), dw_ref) < GEMM_TOL, f"layer {i}: wgrad"
+    _note(i, "wgrad", _rel(_f64(L.dkernel.reshape(l.cin, l.cout)[ks][:, ns]), dw_ref), WGRAD_TOL)
 
 
 def test_first_layer_at_batch_4096(step4096):
@@ -289,7 +307,8 @@ def test_first_layer_at_batch_4096(step4096):
         E0 = e.L[0]
         db = _f64(E0.dbeta[ch])
         dw = _f64(E0.dkernel.reshape(9, 128)[:, ch])
-        assert S.excess(db - r["dbeta"], r["slack_dbeta"]) <= STEP_TOL * np.linalg.norm(r["dbeta"]), what
-        assert S.excess(dw - r["dw"], r["slack_dw"]) <= STEP_TOL * np.linalg.norm(r["dw"]), what
+        _note(0, f"dbeta[{what}]", S.excess(db - r["dbeta"], r["slack_dbeta"]) / np.linalg.norm(r["dbeta"]), STEP_TOL)
+        _note(0, f"dW[{what}]", S.excess(dw - r["dw"], r["slack_dw"]) / np.linalg.norm(r["dw"]), STEP_TOL)
+    REPORT["layer0.border_elements"] = {"value": int(len(np.nonzero(np.abs(np.abs(a) - 1.0) < S.BORDER_TOL)[0])), "tol": None}
     # ds_0 itself (layer 1's dgrad in swap mode, stored by the separate-kernel engine) is checked by
     # test_binary_conv_layer_at_batch_4096[1]

@@ -364,6 +364,50 @@ def test_keras_shaped_fit_runs_on_the_engine(native_lib):
         cli.commands = saved
 
 
+def test_validation_at_another_batch_size_sees_the_weights_being_trained(native_lib, tmp_path):
+    """Engines of different batch sizes that alias one state (what Sequential.fit/evaluate build
+    when validation data is batched differently from training data): the validation engine sees
+    every training step, its cached inference preparation is refreshed, the step counter and the
+    Adam moments are shared, and a checkpoint written through either holds the trained weights."""
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    rng = np.random.default_rng(9)
+    protos = rng.integers(0, 256, (10, 28, 28, 1)).astype(np.float32)
+
+    def make(n):
+        lab = rng.integers(0, 10, (n,)).astype(np.int64)
+        img = np.clip(protos[lab] * 0.6 + rng.normal(60, 40, (n, 28, 28, 1)), 0, 255).astype(np.uint8)
+        return torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda()
+
+    train = BinaryNetEngine(binarynet_layers(), (28, 28, 1), 64, 10)
+    train.init_glorot(0)
+    val = BinaryNetEngine(binarynet_layers(), (28, 28, 1), 96, 10, share_state_with=train)
+    assert val.params.data_ptr() == train.params.data_ptr() and val.moving_var.data_ptr() == train.moving_var.data_ptr()
+    vimg, vlab = make(96)
+    losses = []
+    for epoch in range(3):
+        for _ in range(8):
+            train.train_step(*make(64), None, pad_size=32, seed=1)
+        val.eval_step(vimg, vlab)
+        torch.cuda.synchronize()
+        losses.append(val.last_loss())
+    assert val.step_count == train.step_count == 24
+    assert len({round(v, 6) for v in losses}) == 3, losses          # validation follows the training
+    # the same inference on a fresh engine loaded from a checkpoint written through the VAL engine
+    ck = str(tmp_path / "shared.npz")
+    val.save_checkpoint(ck)
+    fresh = BinaryNetEngine(binarynet_layers(), (28, 28, 1), 96, 10)
+    fresh.load_checkpoint(ck)
+    fresh.eval_step(vimg, vlab)
+    torch.cuda.synchronize()
+    assert fresh.last_loss() == losses[-1] and fresh.step_count == 24
+    for k, a in train.get_params().items():
+        assert np.array_equal(a, fresh.get_params()[k])
+    m_t, _ = train.get_adam_state()
+    m_f, _ = fresh.get_adam_state()
+    assert all(np.array_equal(m_t[k], m_f[k]) for k in m_t)
+
+
 def test_cuda_graph_replay_matches_per_kernel_launches(native_lib):
     """capture_train_step / train_step_graph: same trajectory as ordinary steps (same sample
     indices, same counter-based augmentation, same Adam step sizes)."""

@@ -42,6 +42,14 @@ class DataParallel:
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t
 
+    def all_reduce_sum_async_(self, t: torch.Tensor):
+        """Start a sum all-reduce ordered behind the work already enqueued on the CURRENT stream and
+        return its handle (``None`` on one replica); ``handle.wait()`` orders the then-current stream
+        behind the collective without blocking the host."""
+        if self.world == 1:
+            return None
+        return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
     def reduce_gradients_(self, flat_grads: torch.Tensor) -> torch.Tensor:
         return self.all_reduce_sum_(flat_grads)
 

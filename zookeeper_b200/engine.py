@@ -79,6 +79,25 @@ def _round_up(x: int, m: int) -> int:
     return (x + m - 1) // m * m
 
 
+def gradient_buckets(k_off, kbase: int, min_bytes: int = 8 << 20):
+    """Slices of the flat f32 gradient arena ``[all betas | kernel 0 | kernel 1 | ...]`` in the order
+    the backward pass completes them.  ``k_off[i]`` is kernel i's offset inside the kernel part
+    (``k_off[-1]`` its length), ``kbase`` the length of the beta prefix.  Walking the layers from the
+    last to the first, a bucket is closed once it holds ``min_bytes`` of kernel gradients; the final
+    bucket takes what is left plus every beta gradient.  Each entry is (lowest layer index in the
+    bucket, start, stop): the bucket is complete when that layer's weight-gradient GEMM is (the
+    final one: when the whole backward pass is)."""
+    n_layers = len(k_off) - 1
+    buckets, stop = [], kbase + int(k_off[-1])
+    for i in range(n_layers - 1, 1, -1):
+        start = kbase + int(k_off[i])
+        if (stop - start) * 4 >= min_bytes:
+            buckets.append((i, start, stop))
+            stop = start
+    buckets.append((0, 0, stop))
+    return buckets
+
+
 class _Layer:
     """Device buffers of one block."""
 
@@ -94,7 +113,12 @@ class BinaryNetEngine:
     def __init__(self, layers: Sequence[LayerSpec], input_shape: Tuple[int, int, int], batch_size: int,
                  num_classes: int, learning_rate: float = 5e-3, device: Optional[torch.device] = None,
                  process_group=None, sync_bn: bool = False, beta_1: float = 0.9, beta_2: float = 0.999,
-                 epsilon: float = 1e-7, forward_int8: bool = True, data_parallel: bool = True):
+                 epsilon: float = 1e-7, forward_int8: bool = True, data_parallel: bool = True,
+                 share_state_with: Optional["BinaryNetEngine"] = None):
+        """``share_state_with``: another engine of the same model (any batch size) whose parameter,
+        Adam-moment and moving-statistics arenas and step counter this engine ALIASES instead of
+        allocating its own -- one set of weights seen through several batch sizes (training at one
+        batch size, validation at another) without copies that could go stale."""
         zn.load()  # fail loudly now if the CUDA library is missing
         if not torch.cuda.is_available():
             raise RuntimeError("BinaryNetEngine needs a CUDA device (B200); there is no CPU fallback")
@@ -111,7 +135,11 @@ class BinaryNetEngine:
         # forward binary GEMMs on tcgen05 kind::i8 (int8 +-1 operands, exact int32 accumulation):
         # half the operand bytes and twice the MMA rate of the bf16 path, bit-identical results
         self.forward_int8 = bool(forward_int8)
-        self.step_count = 0
+        self._shared = share_state_with
+        # step counter and a version stamp of the weights (bumped by every update / load), shared
+        # between engines that alias one state: cached inference preparations check the stamp
+        self._state = share_state_with._state if share_state_with is not None else {"step": 0, "version": 0}
+        self._eval_version = -1
         self.launches_per_step = 0
         # Two engine-owned streams: the dependent chain of a step runs on a high-priority one, the
         # weight-gradient GEMMs (nothing in the backward chain waits for them) on a low-priority
@@ -123,8 +151,9 @@ class BinaryNetEngine:
         self._side = torch.cuda.Stream(device=self.device, priority=lo_pri)
         self._side_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._wgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
-        self._dgrad_events = [torch.cuda.Event() for _ in range(len(self.layers) + 1)]
         self._prep_fork, self._prep_join, self._prep_pending = torch.cuda.Event(), torch.cuda.Event(), False
+        self._pending_reduce = []      # in-flight gradient-bucket all-reduces of the current step
+        self.reduce_gradients = True   # False: keep gradients local (accumulation / compute-only timing)
         # first layer's backward inside layer 1's dgrad epilogue (ZKB_FUSE_FIRST_BWD=0: separate kernels)
         self.fuse_first_backward = (os.environ.get("ZKB_FUSE_FIRST_BWD", "1") != "0"
                                     and self._can_fuse_first_backward())
@@ -134,12 +163,27 @@ class BinaryNetEngine:
         self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
         # inference: BatchNorm + sign as integer thresholds inside the GEMM epilogue
         self.fold_eval = self.forward_int8 and os.environ.get("ZKB_FOLD_EVAL", "1") != "0"
-        self._eval_ready = False
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
         self.watched = []      # (name, layer tag, start event, end event)
         self._tag = ""
         self._validate()
         self._allocate()
+
+    @property
+    def step_count(self) -> int:
+        return self._state["step"]
+
+    @step_count.setter
+    def step_count(self, v: int) -> None:
+        self._state["step"] = int(v)
+
+    def _touch(self) -> None:
+        """The weights or moving statistics change: cached inference preparations are stale."""
+        self._state["version"] += 1
+
+    @property
+    def _eval_ready(self) -> bool:
+        return self._eval_version == self._state["version"]
 
     # ------------------------------------------------------------------ set-up
     def _validate(self):
@@ -174,12 +218,24 @@ class BinaryNetEngine:
         self.n_kernel = int(self.k_off[-1])
         self.n_beta = int(self.b_off[-1])
         n = self.n_kernel + self.n_beta
-        self.params = torch.zeros(n, dtype=f32, device=dev)
+        # Arena order [all betas | kernel 0 | kernel 1 | ...]: the gradients that are ready LAST in the
+        # backward pass (betas of every layer, kernels of the first layers) are one contiguous
+        # prefix, those ready first (the dense kernels) a suffix -- the reverse-layer-order buckets of
+        # the gradient all-reduce are plain slices.
+        self.kbase = self.n_beta
+        if self._shared is not None:
+            o = self._shared
+            if o.params.numel() != n or o.n_kernel != self.n_kernel or o.device != dev:
+                raise ValueError("share_state_with: the other engine holds a different model or device")
+            self.params, self.adam_m, self.adam_v = o.params, o.adam_m, o.adam_v
+            self.moving_mean, self.moving_var = o.moving_mean, o.moving_var
+        else:
+            self.params = torch.zeros(n, dtype=f32, device=dev)
+            self.adam_m = torch.zeros(n, dtype=f32, device=dev)
+            self.adam_v = torch.zeros(n, dtype=f32, device=dev)
+            self.moving_mean = torch.zeros(self.n_beta, dtype=f32, device=dev)
+            self.moving_var = torch.ones(self.n_beta, dtype=f32, device=dev)
         self.grads = torch.zeros(n, dtype=f32, device=dev)
-        self.adam_m = torch.zeros(n, dtype=f32, device=dev)
-        self.adam_v = torch.zeros(n, dtype=f32, device=dev)
-        self.moving_mean = torch.zeros(self.n_beta, dtype=f32, device=dev)
-        self.moving_var = torch.ones(self.n_beta, dtype=f32, device=dev)
         # per-step accumulators (zeroed by one memset): fwd sums, bwd sums, loss, correct
         # (+ the fused first-layer path: 11 sums per channel from the dgrad epilogue, and the
         # Gram matrix of the input taps G[9][9] + S2[9])
@@ -197,15 +253,20 @@ class BinaryNetEngine:
             L.spec, L.idx = l, i
             L.cp = self._cpad(l)
             ksz = k_sizes[i]
-            L.kernel = self.params[self.k_off[i]: self.k_off[i] + ksz]
-            L.dkernel = self.grads[self.k_off[i]: self.k_off[i] + ksz]
-            bo = self.n_kernel + int(self.b_off[i])
+            ko = self.kbase + int(self.k_off[i])
+            L.kernel = self.params[ko: ko + ksz]
+            L.dkernel = self.grads[ko: ko + ksz]
+            bo = int(self.b_off[i])
             L.beta = self.params[bo: bo + L.cp]
             L.dbeta = self.grads[bo: bo + L.cp]
             so = int(self.b_off[i])
             nb = self.n_beta
-            L.sum, L.sumsq = self.acc[so: so + L.cp], self.acc[nb + so: nb + so + L.cp]
-            L.sum_da, L.sum_dax = self.acc[2 * nb + so: 2 * nb + so + L.cp], self.acc[3 * nb + so: 3 * nb + so + L.cp]
+            # accumulators of one layer are adjacent, [sum | sumsq | sum_da | sum_dax]: under
+            # synchronised BatchNorm the forward pair and the backward pair are ONE collective each
+            ao = 4 * so
+            L.sum, L.sumsq = self.acc[ao: ao + L.cp], self.acc[ao + L.cp: ao + 2 * L.cp]
+            L.sum_da, L.sum_dax = self.acc[ao + 2 * L.cp: ao + 3 * L.cp], self.acc[ao + 3 * L.cp: ao + 4 * L.cp]
+            L.fwd_sums, L.bwd_sums = self.acc[ao: ao + 2 * L.cp], self.acc[ao + 2 * L.cp: ao + 4 * L.cp]
             L.mean, L.rstd = self.stat[so: so + L.cp], self.stat[nb + so: nb + so + L.cp]
             L.mean_da, L.mean_dax = self.stat[2 * nb + so: 2 * nb + so + L.cp], self.stat[3 * nb + so: 3 * nb + so + L.cp]
             L.mm, L.mv = self.moving_mean[so: so + L.cp], self.moving_var[so: so + L.cp]
@@ -254,6 +315,10 @@ class BinaryNetEngine:
                 L.dy_hi = torch.zeros(B, L.cp, dtype=bf16, device=dev)
                 L.dy_lo = torch.zeros(B, L.cp, dtype=bf16, device=dev)
             self.L.append(L)
+        self.grad_buckets = self._make_grad_buckets()
+
+    def _make_grad_buckets(self):
+        return gradient_buckets(self.k_off, self.kbase)
 
     @staticmethod
     def _cpad(l: LayerSpec) -> int:
@@ -262,7 +327,7 @@ class BinaryNetEngine:
     # ------------------------------------------------------------------ parameters in / out
     def load_params(self, params: Dict[str, np.ndarray], moving: Optional[Dict[str, np.ndarray]] = None):
         """Inject weights in Keras layout: ``kernel{i}`` HWIO / [K, N], ``beta{i}`` [C]."""
-        self._eval_ready = False
+        self._touch()
         for L in self.L:
             k = torch.as_tensor(np.ascontiguousarray(params[f"kernel{L.idx}"]), dtype=torch.float32)
             if k.numel() != L.kernel.numel():
@@ -279,7 +344,6 @@ class BinaryNetEngine:
 
     def init_glorot(self, seed: int = 0):
         """Keras default (Glorot uniform) initialisation from ``numpy.random.default_rng(seed)``."""
-        self._eval_ready = False
         rng = np.random.default_rng(seed)
         params = {}
         for i, l in enumerate(self.layers):
@@ -315,10 +379,9 @@ class BinaryNetEngine:
     def get_adam_state(self) -> Tuple[Dict[str, np.ndarray], Dict[str, np.ndarray]]:
         """First and second Adam moments in the same keyed layout as :meth:`get_params`."""
         m, v = {}, {}
-        nk = self.n_kernel
         for L in self.L:
-            k0, ksz = int(self.k_off[L.idx]), L.kernel.numel()
-            b0 = nk + int(self.b_off[L.idx])
+            k0, ksz = self.kbase + int(self.k_off[L.idx]), L.kernel.numel()
+            b0 = int(self.b_off[L.idx])
             for dst, arena in ((m, self.adam_m), (v, self.adam_v)):
                 dst[f"kernel{L.idx}"] = arena[k0: k0 + ksz].detach().cpu().numpy().reshape(self._shape_of(L)).copy()
                 dst[f"beta{L.idx}"] = arena[b0: b0 + L.spec.cout].detach().cpu().numpy().copy()
@@ -340,15 +403,26 @@ class BinaryNetEngine:
         with np.load(path) as z:
             blob = {k: z[k] for k in z.files}
         self.load_params(blob, blob if "moving_mean0" in blob else None)
-        nk = self.n_kernel
         for L in self.L:
-            k0, ksz = int(self.k_off[L.idx]), L.kernel.numel()
-            b0 = nk + int(self.b_off[L.idx])
+            k0, ksz = self.kbase + int(self.k_off[L.idx]), L.kernel.numel()
+            b0 = int(self.b_off[L.idx])
             for tag, arena in (("adam_m", self.adam_m), ("adam_v", self.adam_v)):
                 if f"{tag}/kernel{L.idx}" in blob:
                     arena[k0: k0 + ksz].copy_(torch.as_tensor(blob[f"{tag}/kernel{L.idx}"], dtype=torch.float32).reshape(-1))
                     arena[b0: b0 + L.spec.cout].copy_(torch.as_tensor(blob[f"{tag}/beta{L.idx}"], dtype=torch.float32))
         self.step_count = int(blob.get("step_count", 0))
+
+    def average_moving_stats(self) -> None:
+        """Per-replica BatchNorm: every rank has folded its own batch statistics into its moving
+        mean / variance, so what a validation pass or a checkpoint sees would depend on the rank.
+        Replace them by their mean over the replicas.  Nothing to do on one
+        GPU or under synchronised BatchNorm (identical on every rank by construction)."""
+        if self.world == 1 or self.sync_bn:
+            return
+        for t in (self.moving_mean, self.moving_var):
+            self._all_reduce(t)
+            t.mul_(1.0 / self.world)
+        self._touch()
 
     def get_moving(self) -> Dict[str, np.ndarray]:
         out = {}
@@ -419,9 +493,7 @@ class BinaryNetEngine:
                    0 if last else zn.ptr(getattr(L, "s8", None)))
 
     def _pending_bn_sync(self, L):
-        # sum and sumsq of one layer are not adjacent in the accumulator arena: two small collectives
-        self._all_reduce(L.sum)
-        self._all_reduce(L.sumsq)
+        self._all_reduce(L.fwd_sums)     # [sum | sumsq] of this layer in one collective
 
     def forward(self, training: bool = True):
         """Forward pass over ``self.x0`` (filled by :meth:`preprocess`)."""
@@ -534,8 +606,7 @@ class BinaryNetEngine:
                    zn.ptr(L.rstd), zn.ptr(L.beta), zn.ptr(L.sum_da), zn.ptr(L.sum_dax))
         count = float(L.bn_rows)
         if self.sync_bn:
-            self._all_reduce(L.sum_da)
-            self._all_reduce(L.sum_dax)
+            self._all_reduce(L.bwd_sums)
             count *= self.world
         self._call("zkb_bn_bwd_finalize", zn.ptr(L.sum_da), zn.ptr(L.sum_dax), count,
                    (1.0 / self.world) if self.sync_bn else 1.0, L.cp, zn.ptr(L.dbeta),
@@ -566,13 +637,18 @@ class BinaryNetEngine:
             self._prep_join.record(side)
             self._prep_pending = True
 
-    def backward(self, side=None):
+    def backward(self, side=None, overlap_reduce: bool = False):
         """Backward pass.  With ``side`` (a low-priority stream) the wgrad GEMMs are issued there:
-        each waits for its layer's dy and is joined before the gradients are consumed."""
+        each waits for its layer's dy and is joined before the gradients are consumed.  With
+        ``overlap_reduce`` (data-parallel runs) the gradient buckets whose last weight-gradient GEMM
+        has been enqueued are all-reduced right behind it, next to the rest of the backward pass;
+        :meth:`finish_gradient_reduce` issues the last bucket and joins them all."""
         B = self.B
         n = len(self.L)
         main = torch.cuda.current_stream(self.device)
-        pending_wgrad = None
+        self._pending_reduce = []
+        early = ({b[0]: b for b in self.grad_buckets[:-1]}
+                 if (overlap_reduce and side is not None and self.world > 1 and self.reduce_gradients) else {})
         for i in range(n - 1, -1, -1):
             L, l = self.L[i], self.L[i].spec
             self._tag = f"bwd{i}"
@@ -590,8 +666,7 @@ class BinaryNetEngine:
                            zn.ptr(L.beta), ste, zn.ptr(L.sum_da), zn.ptr(L.sum_dax))
             count = float(rows)
             if self.sync_bn:
-                self._all_reduce(L.sum_da)
-                self._all_reduce(L.sum_dax)
+                self._all_reduce(L.bwd_sums)     # [sum_da | sum_dax] in one collective
                 count *= self.world
             if l.kind == "conv" and l.pool:
                 mode, of32, ohi, olo, arg = 2, 0, zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.arg)
@@ -624,16 +699,34 @@ class BinaryNetEngine:
                                B, ih, iw, l.cin, l.cout, l.ksize)
                 self._call("zkb_bconv2d_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
                            B, ih, iw, l.cin, l.cout, l.ksize, on=side)
-                if side is not None:
-                    pending_wgrad = self._wgrad_events[i]
-                    pending_wgrad.record(side)
             else:
                 self._call("zkb_bdense_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds),
                            B, l.cin, L.cp)
                 self._call("zkb_bdense_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel),
                            l.cout, B, l.cin, L.cp, l.cout, on=side)
+            if i in early:
+                # every kernel gradient of this bucket has been enqueued on the side stream: the
+                # collective is ordered behind them there and runs next to the remaining backward
+                _, lo, hi = early[i]
+                with torch.cuda.stream(side):
+                    self._pending_reduce.append(self.dp.all_reduce_sum_async_(self.grads[lo:hi]))
         if side is not None:
             main.wait_stream(side)       # every dW is in the arena before all-reduce / Adam
+
+    def finish_gradient_reduce(self):
+        """Sum the gradients over the replicas: the buckets :meth:`backward` has not started yet (all
+        of them without overlap -- then the arena goes out as one collective), then wait for all."""
+        if self.world == 1 or not self.reduce_gradients:
+            return
+        if not self._pending_reduce:
+            self._all_reduce(self.grads)
+            return
+        _, lo, hi = self.grad_buckets[-1]
+        self._pending_reduce.append(self.dp.all_reduce_sum_async_(self.grads[lo:hi]))
+        for work in self._pending_reduce:
+            if work is not None:
+                work.wait()          # orders the current stream behind the collective; no host block
+        self._pending_reduce = []
 
     def loss_and_grad(self):
         L = self.L[-1]
@@ -648,15 +741,15 @@ class BinaryNetEngine:
 
     def optimizer_step(self, lr_dev: Optional[torch.Tensor] = None):
         """Adam + clip.  ``lr_dev``: read the step size from device memory (captured graphs)."""
-        self._eval_ready = False
+        self._touch()
         if lr_dev is None:
             self.step_count += 1
         lr_t = self._lr_t(max(self.step_count, 1))
-        nk = self.n_kernel
+        kb = self.kbase
+        self._call("zkb_adam_clip", self.params[kb:].data_ptr(), self.grads[kb:].data_ptr(), self.adam_m[kb:].data_ptr(),
+                   self.adam_v[kb:].data_ptr(), self.n_kernel, lr_t, self.b1, self.b2, self.eps, 1.0, 1, zn.ptr(lr_dev))
         self._call("zkb_adam_clip", zn.ptr(self.params), zn.ptr(self.grads), zn.ptr(self.adam_m), zn.ptr(self.adam_v),
-                   nk, lr_t, self.b1, self.b2, self.eps, 1.0, 1, zn.ptr(lr_dev))
-        self._call("zkb_adam_clip", self.params[nk:].data_ptr(), self.grads[nk:].data_ptr(), self.adam_m[nk:].data_ptr(),
-                   self.adam_v[nk:].data_ptr(), self.n_beta, lr_t, self.b1, self.b2, self.eps, 1.0, 0, zn.ptr(lr_dev))
+                   self.n_beta, lr_t, self.b1, self.b2, self.eps, 1.0, 0, zn.ptr(lr_dev))
 
     # ------------------------------------------------------------------ public steps
     def train_step(self, images_u8: torch.Tensor, labels_i64: torch.Tensor, index: Optional[torch.Tensor] = None,
@@ -666,7 +759,7 @@ class BinaryNetEngine:
 
         Everything is enqueued on the current CUDA stream; nothing synchronises with the host.
         Read :meth:`last_loss` / :meth:`last_accuracy` afterwards (that read synchronises)."""
-        self._eval_ready = False
+        self._touch()
         # per-launch timing of everything (watch is True) wants a serial schedule
         use_side = self.overlap and self.watch is not True
         caller = torch.cuda.current_stream(self.device)
@@ -682,9 +775,8 @@ class BinaryNetEngine:
             self.prepare_weights(self._side if use_side else None)
             self.forward(training=True)
             self.loss_and_grad()
-            self.backward(self._side if use_side else None)
-            if self.world > 1:
-                self._all_reduce(self.grads)
+            self.backward(self._side if use_side else None, overlap_reduce=True)
+            self.finish_gradient_reduce()
             if apply_update:
                 self.optimizer_step()
         if use_side:
@@ -721,9 +813,8 @@ class BinaryNetEngine:
                 self.prepare_weights(self._side if self.overlap else None)
                 self.forward(training=True)
                 self.loss_and_grad()
-                self.backward(self._side if self.overlap else None)
-                if self.world > 1:
-                    self._all_reduce(self.grads)
+                self.backward(self._side if self.overlap else None)   # (one collective inside a capture)
+                self.finish_gradient_reduce()
                 self.optimizer_step(lr_dev=self._dyn_lr)
         finally:
             self.watch = saved_watch
@@ -733,7 +824,7 @@ class BinaryNetEngine:
     def train_step_graph(self, index: torch.Tensor) -> None:
         """Replay the captured step on the batch ``index`` (int32 device tensor of sample ids)."""
         caller = torch.cuda.current_stream(self.device)
-        self._eval_ready = False
+        self._touch()
         self.step_count += 1
         self.index_buf.copy_(index, non_blocking=True)
         self._dyn_step.fill_(self.step_count - 1)
@@ -762,7 +853,7 @@ class BinaryNetEngine:
                         L.thr = torch.zeros(L.cp, dtype=torch.int32, device=self.device)
                     self._call("zkb_bn_sign_thresholds", zn.ptr(L.mm), zn.ptr(L.eval_rstd), zn.ptr(L.beta), L.cp,
                                zn.ptr(L.thr))
-            self._eval_ready = True
+            self._eval_version = self._state["version"]
         self.preprocess(images_u8, labels_i64, index, False)
         if self.fold_eval:
             self._forward_eval_folded()

@@ -68,19 +68,29 @@ class DataPlan:
     def index_stream(self, epoch: int = 0) -> Iterator[np.ndarray]:
         """Batches of sample indices.  ``shuffle(buffer)`` follows tf.data's streaming shuffle: a
         buffer of ``buffer`` elements is kept full from the sequential stream and each output is
-        a uniformly random element of the buffer."""
+        a uniformly random element of the buffer.  ``.repeat()`` before ``.batch()`` (the order of
+        the reference's chain) makes one endless sample stream that is cut into batches, so the
+        ``n % batch`` tail of a pass fills the start of the next pass's first batch; without
+        ``repeat`` the incomplete last batch is dropped (the engine's batch size is fixed; the
+        reference never consumes it either: its step counts are ``n // batch_size``,
+        examples/larq_experiment.py:150-152)."""
         n, bs = len(self), self.batch_size
         if bs <= 0:
             raise ValueError("the plan has no batch size; call .batch(n)")
         rng = np.random.default_rng(self.seed + 7919 * epoch)
+        carry = np.empty(0, dtype=np.int64)
         while True:
             order = np.arange(n, dtype=np.int64)
             if self.shuffle_buffer > 1:
                 order = _streaming_shuffle(n, min(self.shuffle_buffer, n), rng)
-            for s in range(0, n - bs + 1, bs):
+            if carry.size:
+                order = np.concatenate([carry, order])
+            full = (order.size // bs) * bs
+            for s in range(0, full, bs):
                 yield order[s:s + bs]
             if not self.repeated:
                 return
+            carry = order[full:]
 
 
 def _streaming_shuffle(n: int, buffer: int, rng: np.random.Generator) -> np.ndarray:

@@ -117,7 +117,8 @@ class Sequential(Model):
         self.optimizer: Optional[Adam] = None
         self.loss = None
         self.metrics: List[str] = []
-        self.engine = None
+        self.engine = None              # the engine that holds the model's state (first one built)
+        self._engines = {}              # per-rank batch size -> engine; all alias self.engine's state
         self.history: Dict[str, List[float]] = {}
 
     # ------------------------------------------------------------------ keras-shaped API
@@ -173,26 +174,37 @@ class Sequential(Model):
         return 0, 1
 
     def _ensure_engine(self, global_batch: int):
+        """The engine for this (global) batch size.  Activation buffers are sized per batch, so
+        each batch size gets its own engine -- but all of them ALIAS one set of parameter,
+        Adam-moment and moving-statistics arenas and one step counter (``share_state_with``):
+        validating at another batch size than training sees the weights being trained, not a copy."""
         from ..engine import BinaryNetEngine
 
         rank, world = self._dist()
         if global_batch % world:
             raise ValueError(f"batch size {global_batch} is not divisible by the {world} replicas")
         per_rank = global_batch // world
-        if self.engine is not None and self.engine.B == per_rank:
-            return self.engine
+        if per_rank in self._engines:
+            return self._engines[per_rank]
         if self.optimizer is None:
             raise RuntimeError("call compile() before fit()/evaluate()")
-        old = self.engine
         opt = self.optimizer
-        self.engine = BinaryNetEngine(self.blocks, self.input_shape, per_rank, self.num_classes,
-                                      learning_rate=opt.learning_rate, beta_1=opt.beta_1, beta_2=opt.beta_2,
-                                      epsilon=opt.epsilon)
-        if old is None:
-            self.engine.init_glorot(0)
-        else:
-            self.engine.load_params(old.get_params(), old.get_moving())
-        return self.engine
+        eng = BinaryNetEngine(self.blocks, self.input_shape, per_rank, self.num_classes,
+                              learning_rate=opt.learning_rate, beta_1=opt.beta_1, beta_2=opt.beta_2,
+                              epsilon=opt.epsilon, share_state_with=self.engine)
+        if self.engine is None:
+            eng.init_glorot(0)
+            self.engine = eng
+        self._engines[per_rank] = eng
+        return eng
+
+    def _sum_over_replicas(self, *tensors):
+        """Loss / accuracy counters are sums over this replica's samples: add the other replicas'."""
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            for t in tensors:
+                dist.all_reduce(t)
 
     @staticmethod
     def _resident(plan: DataPlan, device):
@@ -257,12 +269,13 @@ class Sequential(Model):
                                 print(f"CUDA-graph capture unavailable ({exc}); continuing with per-kernel launches")
                 run_loss += eng.acc[nb4:nb4 + 1]
                 run_ok += eng.correct
+            self._sum_over_replicas(run_loss, run_ok)     # the logged metrics cover the GLOBAL batches
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
-            seen = steps_per_epoch * eng.B
+            seen = steps_per_epoch * eng.B * world
             hist["loss"].append(float(run_loss.item()) / max(seen, 1))
             hist["accuracy"].append(float(run_ok.item()) / max(seen, 1))
-            hist["images_per_sec"].append(seen * world / dt if dt > 0 else float("nan"))
+            hist["images_per_sec"].append(seen / dt if dt > 0 else float("nan"))
             msg = (f"Epoch {epoch + 1}/{epochs} - {dt:.2f}s - loss: {hist['loss'][-1]:.4f} - "
                    f"accuracy: {hist['accuracy'][-1]:.4f} - {hist['images_per_sec'][-1]:.0f} images/s")
             if validation_data is not None:
@@ -279,6 +292,7 @@ class Sequential(Model):
         """Checkpoint (weights in Keras HWIO / [K, N] layout, moving stats, Adam state) as .npz."""
         if self.engine is None:
             raise RuntimeError("nothing to save: the model has not been fitted or evaluated yet")
+        self.engine.average_moving_stats()     # per-replica BatchNorm: one checkpoint whatever the rank
         self.engine.save_checkpoint(path)
 
     def load_weights(self, path: str, batch_size: int) -> None:
@@ -290,6 +304,7 @@ class Sequential(Model):
         eng = self._ensure_engine(data.batch_size)
         rank, world = self._dist()
         _lower_plan(data, self.input_shape)
+        eng.average_moving_stats()             # per-replica BatchNorm: validate with the replicas' mean
         d_img, d_lab = self._resident(data, eng.device)
         if steps is None:
             steps = len(data) // data.batch_size
@@ -303,7 +318,8 @@ class Sequential(Model):
             eng.eval_step(d_img, d_lab, d_idx)
             run_loss += eng.acc[nb4:nb4 + 1]
             run_ok += eng.correct
-        seen = max(steps * eng.B, 1)
+        self._sum_over_replicas(run_loss, run_ok)
+        seen = max(steps * eng.B * world, 1)
         loss, acc = float(run_loss.item()) / seen, float(run_ok.item()) / seen
         if verbose and rank == 0:
             print(f"evaluate - loss: {loss:.4f} - accuracy: {acc:.4f}", flush=True)
