@@ -218,7 +218,7 @@ def algorithmic_work(eng, name, tag):
     img_bytes = B * eng.input_shape[0] * eng.input_shape[1] * eng.input_shape[2] * 4
     table = {
         "zkb_bn_stats": rows * C * xb,
-        "zkb_bn_apply_sign": rows * C * (xb + 2),
+        "zkb_bn_apply_sign": rows * C * (xb + (3 if eng.forward_int8 else 2)),   # x read; bf16 (+ int8) sign written
         "zkb_maxpool2_i16": (M * N * 2) + rows * C * 3,
         "zkb_bn_bwd_reduce": rows * C * (4 + xb),
         "zkb_bn_bwd_apply": rows * C * (4 + xb) + M * N * 4,

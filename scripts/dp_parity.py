@@ -1,4 +1,6 @@
-"""2-GPU check: SyncBN data-parallel step at global batch 2B == single-GPU step at batch 2B."""
+"""N-GPU check (N = WORLD_SIZE ranks): a SyncBN data-parallel step at global batch Bg reproduces the
+single-GPU step at batch Bg.  Rank 0 prints the gradient deviation and the
+worst tensor, and appends the same lines to gpurun_out/dp_parity_n<N>.log when that directory exists."""
 import os
 import sys
 
@@ -32,13 +34,23 @@ if rank == 0:
     single.train_step(img, lab, None, pad_size=32, aug=aug, apply_update=False)
     torch.cuda.synchronize()
     rel = ((g_dp - single.grads).norm() / single.grads.norm()).item()
-    print(f"DP({world}, SyncBN) vs single GPU at global batch {Bg}: grad rel err {rel:.3e}, "
-          f"loss {loss_dp.item() / world:.6f} vs {single.last_loss():.6f}")
+    lines = [f"DP({world}, SyncBN) vs single GPU at global batch {Bg}: grad rel err {rel:.3e}, "
+             f"loss {loss_dp.item() / world:.6f} vs {single.last_loss():.6f}"]
+    print(lines[0])
     gd = {k: v for k, v in zip(["all"], [None])}
     eng.grads.copy_(g_dp)
     a, b = eng.get_grads(), single.get_grads()
     worst = max((float(np.linalg.norm(a[k] - b[k]) / max(np.linalg.norm(b[k]), 1e-30)), k) for k in b)
-    print("worst tensor:", worst)
-    assert rel < 1e-4 and worst[0] < 1e-4
+    lines.append(f"worst tensor: {worst[1]} rel err {worst[0]:.3e}")
+    # moving statistics: identical on every rank under SyncBN and equal to the single-GPU ones
+    mv_a, mv_b = eng.get_moving(), single.get_moving()
+    mv_err = max(float(np.abs(mv_a[k] - mv_b[k]).max() / max(np.abs(mv_b[k]).max(), 1e-30)) for k in mv_b)
+    lines.append(f"moving statistics vs single GPU: max rel err {mv_err:.3e}")
+    print("\n".join(lines[1:]))
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, f"dp_parity_n{world}.log"), "w") as f:
+            f.write("\n".join(lines) + "\n")
+    assert rel < 1e-4 and worst[0] < 1e-4 and mv_err < 1e-5
 dist.barrier()
 dist.destroy_process_group()

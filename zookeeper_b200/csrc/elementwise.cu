@@ -31,7 +31,13 @@ __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
 
 // ------------------------------------------------------------------------------------------
 // Preprocessing: gather + centre zero-pad + random crop + random flip + u8 -> f32 (x/127.5 - 1).
-// One thread produces 4 consecutive output floats of one row (OW*C % 4 == 0).
+// A block works on ONE sample (blockIdx.y), so the sample's index, crop offsets and flip bit are
+// worked out once per block; a thread produces 4 consecutive output floats of one row (one 16-byte
+// store, fully coalesced across the warp) with a single division for its row number.  The 256
+// possible results of float(px) / 127.5f - 1.0f (a true IEEE division, as the reference's
+// `cast(image, float32) / (255.0 / 2.0) - 1.0` computes) are tabulated once per block in shared
+// memory, so the conversion of an element is one shared-memory load -- bit-exact by construction.
+// CT: channel count known at compile time (1, 3) or 0 for the generic path.
 // ------------------------------------------------------------------------------------------
 struct PreParams {
   const uint8_t* images;    // [n_pool, IH, IW, C]
@@ -67,53 +73,65 @@ __device__ __forceinline__ void sample_aug(const PreParams& p, int b, int& ox, i
   flip = static_cast<int>((r >> 32) & 1u);
 }
 
+template <int CT>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const PreParams p) {
-  const int row_elems = p.OW * p.C;
-  const int vec_per_img = p.OH * row_elems / 4;
-  const long long total = static_cast<long long>(p.B) * vec_per_img;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int b = static_cast<int>(i / vec_per_img);
-    const int v = static_cast<int>(i - static_cast<long long>(b) * vec_per_img);
-    const int e0 = v * 4;
-    const int oh = e0 / row_elems;
-    const int re = e0 - oh * row_elems;
+  __shared__ float s_lut[256];
+  __shared__ int s_geo[4];     // source sample, x shift, y shift, flip
+  const int b = blockIdx.y;
+  {
+    float f = static_cast<float>(threadIdx.x) / 127.5f - 1.0f;
+    if (p.binarize) f = f >= 0.0f ? 1.0f : -1.0f;
+    s_lut[threadIdx.x] = f;
+  }
+  if (threadIdx.x == 0) {
     int ox, oy, flip;
     sample_aug(p, b, ox, oy, flip);
-    const int src = p.index ? p.index[b] : b;
     // Training: pad to pad_size (centred), crop OHxOW at (oy, ox).  Eval: centre crop/pad to OHxOW.
-    const int target = p.training ? p.pad_size : 0;
-    const int padded_h = p.training ? target : p.OH;
-    const int padded_w = p.training ? target : p.OW;
+    const int padded_h = p.training ? p.pad_size : p.OH;
+    const int padded_w = p.training ? p.pad_size : p.OW;
     // offset of the source image inside the padded canvas (negative when cropping)
     const int off_h = (padded_h - p.IH) >= 0 ? (padded_h - p.IH) / 2 : -((p.IH - padded_h) / 2);
     const int off_w = (padded_w - p.IW) >= 0 ? (padded_w - p.IW) / 2 : -((p.IW - padded_w) / 2);
-    const uint8_t* img = p.images + static_cast<long long>(src) * p.IH * p.IW * p.C;
-    float o[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int e = re + j;
-      int ow = e / p.C;
-      const int c = e - ow * p.C;
-      if (flip) ow = p.OW - 1 - ow;
-      const int ih = oh + oy - off_h;
-      const int iw = ow + ox - off_w;
-      uint8_t px = 0;
-      if (ih >= 0 && ih < p.IH && iw >= 0 && iw < p.IW) px = img[(ih * p.IW + iw) * p.C + c];
-      float f = static_cast<float>(px) / 127.5f - 1.0f;
-      if (p.binarize) f = f >= 0.0f ? 1.0f : -1.0f;
-      o[j] = f;
-    }
-    *reinterpret_cast<float4*>(p.out + i * 4) = make_float4(o[0], o[1], o[2], o[3]);
-    if (v == 0) {
-      const long long lab = p.labels ? p.labels[src] : 0;
+    const int src = p.index ? p.index[b] : b;
+    s_geo[0] = src;
+    s_geo[1] = ox - off_w;      // input column = output column (after un-flipping) + this
+    s_geo[2] = oy - off_h;      // input row = output row + this
+    s_geo[3] = flip;
+    const long long lab = p.labels ? p.labels[src] : 0;
+    if (blockIdx.x == 0) {
       if (p.labels_out) p.labels_out[b] = static_cast<int>(lab);
       if (p.onehot)
         for (int k = 0; k < p.num_classes; ++k)
           p.onehot[static_cast<long long>(b) * p.num_classes + k] = (k == lab) ? 1.0f : 0.0f;
     }
   }
+  __syncthreads();
+  const int C = CT ? CT : p.C;
+  const unsigned row_elems = static_cast<unsigned>(p.OW * C);
+  const unsigned vec_per_row = row_elems >> 2;
+  const unsigned vec_per_img = static_cast<unsigned>(p.OH) * vec_per_row;
+  const unsigned v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= vec_per_img) return;
+  const unsigned oh = v / vec_per_row;
+  const unsigned re = (v - oh * vec_per_row) << 2;      // first element of this vector in its row
+  const int dx = s_geo[1], flip = s_geo[3];
+  const int ih = static_cast<int>(oh) + s_geo[2];
+  float o[4] = {s_lut[0], s_lut[0], s_lut[0], s_lut[0]};   // outside the source image: pixel value 0
+  if (ih >= 0 && ih < p.IH) {
+    const uint8_t* row = p.images + (static_cast<long long>(s_geo[0]) * p.IH + ih) * p.IW * C;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const unsigned e = re + j;
+      unsigned ow = e / static_cast<unsigned>(C);       // (a shift / multiply when CT is known)
+      const unsigned c = e - ow * C;
+      if (flip) ow = p.OW - 1 - ow;
+      const int iw = static_cast<int>(ow) + dx;
+      if (iw >= 0 && iw < p.IW) o[j] = s_lut[__ldg(row + iw * C + c)];
+    }
+  }
+  float* dst = p.out + (static_cast<long long>(b) * vec_per_img + v) * 4;
+  *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -536,7 +554,10 @@ __device__ __forceinline__ void pool_one(const int16_t* __restrict__ y, int H, i
   *reinterpret_cast<uint2*>(arg_out + r * C + cl * VEC) = make_uint2(alo, ahi);
 }
 
-__global__ void __launch_bounds__(256)
+// Register budget: 3 blocks of 256 threads per SM (the earlier form kept two pooled pixels in
+// flight plus float64 accumulators, 122 registers, 2 blocks per SM: ncu showed 24 % of the warp
+// slots filled and 4.0 TB/s).  The statistics accumulate as 64-bit integers (exact, converted once).
+__global__ void __launch_bounds__(256, 3)
 maxpool2_i16_kernel(const int16_t* __restrict__ y, int B, int H, int W, int C,
                     int16_t* __restrict__ p_out, uint8_t* __restrict__ arg_out,
                     double* __restrict__ sum, double* __restrict__ sumsq) {
@@ -547,32 +568,25 @@ maxpool2_i16_kernel(const int16_t* __restrict__ y, int B, int H, int W, int C,
   const int rl = threadIdx.x / tpr;
   const int PH = H / 2, PW = W / 2;
   const long long rows = static_cast<long long>(B) * PH * PW;
-  double a0[VEC], a1[VEC];
+  long long s0[VEC], s1[VEC];
 #pragma unroll
-  for (int j = 0; j < VEC; ++j) a0[j] = a1[j] = 0.0;
+  for (int j = 0; j < VEC; ++j) s0[j] = s1[j] = 0;
   if (rl < lanes) {
-    StatAcc<int16_t, VEC> acc;
-    acc.clear();
-    int n = 0;
     const long long step = static_cast<long long>(gridDim.x) * lanes;
-    long long r = static_cast<long long>(blockIdx.x) * lanes + rl;
-    // two pooled pixels (eight 16-byte loads) in flight per thread
-    for (; r + step < rows; r += 2 * step) {
-      Vec16<int16_t> m0, m1;
-      pool_one(y, H, W, C, PH, PW, r, cl, p_out, arg_out, m0);
-      pool_one(y, H, W, C, PH, PW, r + step, cl, p_out, arg_out, m1);
-      acc.add(m0); acc.add(m1);
-      n += 2;
-      if (n >= 126) { acc.flush(a0, a1); n = 0; }
-    }
-    for (; r < rows; r += step) {
+    for (long long r = static_cast<long long>(blockIdx.x) * lanes + rl; r < rows; r += step) {
       Vec16<int16_t> m0;
       pool_one(y, H, W, C, PH, PW, r, cl, p_out, arg_out, m0);
-      acc.add(m0);
-      if (++n >= 126) { acc.flush(a0, a1); n = 0; }
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        const int t = m0.v[j];
+        s0[j] += t;
+        s1[j] += t * t;          // |t| <= 4608: t*t fits int32
+      }
     }
-    acc.flush(a0, a1);
   }
+  double a0[VEC], a1[VEC];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { a0[j] = static_cast<double>(s0[j]); a1[j] = static_cast<double>(s1[j]); }
   block_channel_reduce<VEC>(a0, a1, tpr, C, sum, sumsq);
 }
 
@@ -927,13 +941,23 @@ adam_clip_kernel(float* __restrict__ w, const float* __restrict__ g, float* __re
 using namespace zkb;
 
 static int reduce_waves() {
-  static int w = -1;
+#ifdef ZKB_MEASURE
+  static int w = -1;     // measurement builds only: ZKB_REDUCE_WAVES, read once
   if (w < 0) {
     const char* e = getenv("ZKB_REDUCE_WAVES");
     w = (e && atoi(e) > 0) ? atoi(e) : 8;
   }
   return w;
+#else
+  return 8;
+#endif
 }
+
+// Grid of a per-channel reduction kernel: `lanes` row lanes per 256-thread block.  Every block ends
+// with one float64 atomic per channel and sum, so a block should own at least ~32 rows per lane
+// (ncu, r2: the dense layers' 4096-row reductions ran 512 blocks of 8 rows and spent their time in
+// 1 M contended atomics), and at most reduce_waves() blocks per SM.
+static int reduce_grid(long long rows, int lanes);
 
 static int grid_for(long long work_items, int block, int max_waves = 8) {
   const long long cap = static_cast<long long>(zkb_sm_count()) * max_waves;
@@ -941,6 +965,13 @@ static int grid_for(long long work_items, int block, int max_waves = 8) {
   if (g > cap) g = cap;
   if (g < 1) g = 1;
   return static_cast<int>(g);
+}
+
+static int reduce_grid(long long rows, int lanes) {
+  long long g = (rows + static_cast<long long>(lanes) * 32 - 1) / (static_cast<long long>(lanes) * 32);
+  const long long cap = static_cast<long long>(zkb_sm_count()) * reduce_waves();
+  if (g > cap) g = cap;
+  return g < 1 ? 1 : static_cast<int>(g);
 }
 
 #define ZKB_ALIGNED16(p) ((reinterpret_cast<uintptr_t>(p) & 15) == 0)
@@ -961,8 +992,13 @@ ZKB_API int zkb_preprocess_u8(const uint8_t* images, const long long* labels, co
   ZKB_REQUIRE(!onehot || (labels && num_classes > 0), "preprocess: one-hot needs labels");
   PreParams p{images, labels, index, aug, out, labels_out, onehot, B, IH, IW, C, OH, OW,
               pad_size, training, binarize, num_classes, seed, step, step_dev};
-  const long long work = static_cast<long long>(B) * OH * OW * C / 4;
-  preprocess_kernel<<<grid_for(work, 256, 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  ZKB_REQUIRE(B <= 65535, "preprocess: at most 65535 samples per call (got %d)", B);
+  const unsigned vec_per_img = static_cast<unsigned>(OH) * static_cast<unsigned>(OW * C / 4);
+  const dim3 grid((vec_per_img + 255) / 256, B);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (C == 1) preprocess_kernel<1><<<grid, 256, 0, st>>>(p);
+  else if (C == 3) preprocess_kernel<3><<<grid, 256, 0, st>>>(p);
+  else preprocess_kernel<0><<<grid, 256, 0, st>>>(p);
   ZKB_LAUNCH_CHECK("preprocess_kernel");
   return ZKB_OK;
 }
@@ -1026,7 +1062,7 @@ ZKB_API int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, dou
   ZKB_REQUIRE(sum && sumsq, "bn_stats: null accumulator");
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / vec);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
+  const int grid = reduce_grid(rows, lanes);
   const size_t smem = 0;
   if (x_is_i16)
     bn_stats_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
@@ -1112,7 +1148,7 @@ ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_
   if (B == 0) return ZKB_OK;
   const long long rows = static_cast<long long>(B) * (H / 2) * (W / 2);
   const int lanes = 256 / (C / 8);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, reduce_waves());
+  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, 12);
   const size_t smem = 0;
   maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);
@@ -1140,7 +1176,7 @@ ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long 
   ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax, "bn_bwd_reduce: null pointer");
   if (rows == 0) return ZKB_OK;
   const int lanes = 256 / (C / 4);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
+  const int grid = reduce_grid(rows, lanes);
   const size_t smem = 0;
   if (x_is_i16)
     bn_bwd_reduce_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
@@ -1318,7 +1354,7 @@ ZKB_API int zkb_bn_train_sign_static(const void* x, int x_is_i16, long long rows
   ZKB_CUDA(cudaMemsetAsync(sc->sum, 0, sizeof(double) * C, st));
   ZKB_CUDA(cudaMemsetAsync(sc->sumsq, 0, sizeof(double) * C, st));
   const int lanes = 256 / (C / vec);
-  const int grid_s = grid_for((rows + lanes - 1) / lanes * 256 / 8, 256, reduce_waves());
+  const int grid_s = reduce_grid(rows, lanes);
   const size_t smem = 0;
   const int grid_a = grid_for(rows * (C / vec), 256, 16);
   if (x_is_i16) {
@@ -1748,59 +1784,64 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
 // accumulated into).  Everything about the first layer that is quadratic in the input and does not
 // involve the incoming gradient follows from these 90 numbers: per-channel sum / sum of squares of
 // the conv output (y_c = sum_k w_kc x_k) and sum_p x_k(p) y_c(p).
-__global__ void __launch_bounds__(256)
+// (Per-thread float64 copies of the 54 running sums cost 232 registers and left one block per SM --
+// ncu, r2: 12 % of the warp slots, 98 us for a 12.8 MB read.  The float partials are now folded
+// into ONE float64 set per block in shared memory: a warp reduces each of its 54 floats by shuffles
+// and lane 0 adds the result, every 32 pixels per thread and at the end.)
+__device__ __forceinline__ void gram_flush(float (&g)[45], float (&s)[9], double (*red)[54], int warp, int lane) {
+#pragma unroll
+  for (int i = 0; i < 54; ++i) {
+    float v = i < 45 ? g[i] : s[i - 45];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][i] += static_cast<double>(v);
+  }
+#pragma unroll
+  for (int i = 0; i < 45; ++i) g[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 9; ++i) s[i] = 0.f;
+}
+
+__global__ void __launch_bounds__(256, 2)
 conv_first_gram_kernel(const float* __restrict__ x, int B, int H, int W, double* __restrict__ gram) {
   const int OH = H - 2, OW = W - 2;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned n_rows = static_cast<unsigned>(B) * OH;
+  __shared__ double red[8][54];
+  for (int i = threadIdx.x; i < 8 * 54; i += blockDim.x) (&red[0][0])[i] = 0.0;
+  __syncthreads();
   float g[45], s[9];
 #pragma unroll
   for (int i = 0; i < 45; ++i) g[i] = 0.f;
 #pragma unroll
   for (int i = 0; i < 9; ++i) s[i] = 0.f;
-  double gd[45], sd[9];
-#pragma unroll
-  for (int i = 0; i < 45; ++i) gd[i] = 0.0;
-#pragma unroll
-  for (int i = 0; i < 9; ++i) sd[i] = 0.0;
-  int n = 0;
+  int n = 0;     // warp-uniform: every lane runs the same number of iterations
   for (unsigned row = blockIdx.x * 8 + warp; row < n_rows; row += gridDim.x * 8) {
     const unsigned b = row / OH, oh = row - b * OH;
     const float* base = x + (static_cast<size_t>(b) * H + oh) * W;
-    for (int ow = lane; ow < OW; ow += 32) {
-      float xv[9];
+    for (int ow0 = 0; ow0 < OW; ow0 += 32) {
+      const int ow = ow0 + lane;
+      if (ow < OW) {
+        float xv[9];
 #pragma unroll
-      for (int kh = 0; kh < 3; ++kh)
+        for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
-        for (int kw = 0; kw < 3; ++kw) xv[kh * 3 + kw] = __ldg(base + kh * W + ow + kw);
-      int t = 0;
+          for (int kw = 0; kw < 3; ++kw) xv[kh * 3 + kw] = __ldg(base + kh * W + ow + kw);
+        int t = 0;
 #pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        s[k] += xv[k];
+        for (int k = 0; k < 9; ++k) {
+          s[k] += xv[k];
 #pragma unroll
-        for (int k2 = k; k2 < 9; ++k2) { g[t] = fmaf(xv[k], xv[k2], g[t]); ++t; }
+          for (int k2 = k; k2 < 9; ++k2) { g[t] = fmaf(xv[k], xv[k2], g[t]); ++t; }
+        }
       }
-      if (++n == 32) {   // bound the float partial sums
-#pragma unroll
-        for (int i = 0; i < 45; ++i) { gd[i] += g[i]; g[i] = 0.f; }
-#pragma unroll
-        for (int i = 0; i < 9; ++i) { sd[i] += s[i]; s[i] = 0.f; }
+      if (++n == 32) {   // bound the float partial sums (|x| <= 1: at most 32 per lane and sum)
+        gram_flush(g, s, red, warp, lane);
         n = 0;
       }
     }
   }
-#pragma unroll
-  for (int i = 0; i < 45; ++i) gd[i] += g[i];
-#pragma unroll
-  for (int i = 0; i < 9; ++i) sd[i] += s[i];
-  __shared__ double red[8][54];
-#pragma unroll
-  for (int i = 0; i < 54; ++i) {
-    double v = i < 45 ? gd[i] : sd[i - 45];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) red[warp][i] = v;
-  }
+  gram_flush(g, s, red, warp, lane);
   __syncthreads();
   if (threadIdx.x < 54) {
     double v = 0.0;
