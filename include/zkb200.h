@@ -249,6 +249,56 @@ int zkb_adam_clip(float* w, const float* g, float* m, float* v, long long n, flo
                   float beta1, float beta2, float eps, float grad_scale, int is_kernel,
                   const float* lr_t_dev, void* stream);
 
+/* ---- Bi-Real-Net style binary residual units ---------------
+ * Not in the reference tree: BASELINE.json configs[3] and [4] name larq-zoo models, which the
+ * reference reaches through the same hook as BinaryNet (a @factory model built from larq layers,
+ * examples/larq_experiment.py:41-103, quantizer names in the kwhparams dict :52-57).  Semantics are
+ * the published larq / larq-zoo ones, restated in oracle/bireal_oracle.py.  A unit is
+ *   h_next = BatchNorm(QuantConv2D(h; input_quantizer="approx_sign",
+ *                                  kernel_quantizer="magnitude_aware_sign")) + h
+ * The binary contraction runs on the entry points above (sign(h) through zkb_bn_apply_sign with
+ * mean 0 / rstd 1 / beta 0; forward zkb_bconv2d_fwd_i8_stats; backward zkb_bconv2d_dgrad / _wgrad
+ * on dy = alpha * dz, which makes the wgrad output the latent-weight gradient directly).
+ *
+ * zkb_weight_abs_mean: alpha[c] = mean over the K = ks*ks*Cin rows of |W[k][c]| (magnitude_aware_sign's
+ *   per-output-channel scale; its gradient is stopped, as in larq).
+ * zkb_bn_gain_finalize: BatchNormalization WITH scale over z = alpha*y from the integer sums of y:
+ *   mean_y; rs_bwd = alpha*rstd_z (xhat = (y - mean_y)*rs_bwd); gain = alpha*gamma*rstd_z; moving
+ *   statistics of z (bessel: unbiased variance into the moving variance, TF's fused kernel).
+ * zkb_bn_gain_add: out = (y - mean_y)*gain + beta (+ shortcut), f32.
+ * zkb_bn_gain_bwd_apply: dy = gain*(d - mean_d - xhat*mean_dx) as the bf16 hi/lo pair; the sums
+ *   behind mean_d / mean_dx (and dbeta, dgamma) come from zkb_bn_bwd_reduce(ste = 0, rstd = rs_bwd).
+ * zkb_approx_sign_bwd_add: out = d_short + ds*(2 - 2|h|)*[|h| <= 1] (approx_sign's backward, plus
+ *   the gradient arriving over the shortcut; d_short may be NULL).  n % 4 == 0. */
+int zkb_weight_abs_mean(const float* w_k_co, long long K, int Cout, float* alpha, void* stream);
+int zkb_bn_gain_finalize(const double* sum, const double* sumsq, double count, const float* alpha,
+                         const float* gamma, float eps, float momentum, int bessel, int C,
+                         float* mean_y, float* rs_bwd, float* gain, float* moving_mean,
+                         float* moving_var, void* stream);
+int zkb_bn_gain_add(const void* y_i16, long long rows, int C, const float* mean_y, const float* gain,
+                    const float* beta, const float* shortcut, float* out, void* stream);
+int zkb_bn_gain_bwd_apply(const float* d, const void* y_i16, long long rows, int C, const float* mean_y,
+                          const float* rs_bwd, const float* gain, const float* mean_d,
+                          const float* mean_dx, void* out_hi, void* out_lo, void* stream);
+int zkb_approx_sign_bwd_add(const float* ds, const float* h, const float* d_short, float* out,
+                            long long n, void* stream);
+/* Head of the larq-zoo models: global average pooling over the HW positions of [B,HW,C] (C % 4 == 0)
+ * and a float Dense layer y[M][ldy] = x[M][K] w[K][N] + bias (bias may be NULL); the backward
+ * WRITES dw[K][N], dbias[N] (optional) and dx[M][K] (optional). */
+int zkb_global_avgpool_fwd(const float* h, int B, int HW, int C, float* out, void* stream);
+int zkb_global_avgpool_bwd(const float* dout, int B, int HW, int C, float* dh, void* stream);
+int zkb_dense_f32_fwd(const float* x, const float* w_k_n, const float* bias, float* y, int M, int K,
+                      int N, int ldy, void* stream);
+int zkb_dense_f32_bwd(const float* x, const float* w_k_n, const float* dy, int lddy, float* dx,
+                      float* dw_k_n, float* dbias, int M, int K, int N, void* stream);
+/* MaxPool2D(pool_size=3, strides=2, padding="same") of the stem, float NHWC, C % 4 == 0:
+ * out [B,ceil(H/2),ceil(W/2),C]; arg (same shape, uint8) = winning window slot kh*3+kw, first
+ * maximum in row-major order; the backward gathers dout through arg into dx [B,H,W,C]. */
+int zkb_maxpool3s2_f32_fwd(const float* x, int B, int H, int W, int C, float* out, uint8_t* arg,
+                           void* stream);
+int zkb_maxpool3s2_f32_bwd(const float* dout, const uint8_t* arg, int B, int H, int W, int C, float* dx,
+                           void* stream);
+
 /* ---- for callers that cannot allocate device memory ----------------------------------------------
  * (No counterpart in the reference: this entry point exists for hosts of this library, not for
  * parity.)  BatchNorm(train) + sign in one call -- statistics, moving-average update, normalise,

@@ -1,0 +1,152 @@
+"""Bi-Real-Net style binary residual units: kernel-level parity of the new
+operators and one full train step of residual units + head against oracle/bireal_oracle.py.
+Bit-exact: the integer binary conv output (the +-1 part of magnitude_aware_sign), pool slots.
+Tolerance: loss, every gradient tensor (incl. the gradient flowing out over the float shortcut) and
+the updated weights within 1e-4 relative (Frobenius norm per tensor), as for BinaryNet."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-4
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def test_quantizer_scale_backward_and_head_kernels(native_lib):
+    from zookeeper_b200 import native as zn
+
+    rng = np.random.default_rng(0)
+    # magnitude_aware_sign scale
+    w = rng.normal(0, 0.3, (3, 3, 128, 256)).astype(np.float32)
+    dw = torch.as_tensor(w).cuda()
+    alpha = torch.zeros(256, device="cuda")
+    zn.call("zkb_weight_abs_mean", zn.ptr(dw), 9 * 128, 256, zn.ptr(alpha), 0)
+    assert _rel(alpha.cpu().numpy(), np.abs(w.astype(np.float64)).mean(axis=(0, 1, 2))) < 1e-6
+    # approx_sign backward + shortcut (values at and around the clip boundary included)
+    h = rng.normal(0, 0.8, (4, 5, 5, 128)).astype(np.float32)
+    h.reshape(-1)[:6] = [1.0, -1.0, 0.0, -0.0, 1.0000001, 0.5]
+    ds = rng.normal(size=h.shape).astype(np.float32)
+    dsh = rng.normal(size=h.shape).astype(np.float32)
+    out = torch.zeros(h.shape, device="cuda")
+    d_ds, d_h, d_dsh = (torch.as_tensor(t).cuda() for t in (ds, h, dsh))     # (keep the device copies alive)
+    zn.call("zkb_approx_sign_bwd_add", zn.ptr(d_ds), zn.ptr(d_h), zn.ptr(d_dsh), zn.ptr(out), h.size, 0)
+    torch.cuda.synchronize()
+    a = np.abs(h.astype(np.float64))
+    ref = dsh + ds * (2 - 2 * a) * (a <= 1)
+    assert _rel(out.cpu().numpy(), ref) < 1e-6
+    # global average pool and its backward
+    x = torch.as_tensor(rng.normal(size=(6, 7 * 7, 256)).astype(np.float32)).cuda()
+    pooled = torch.zeros(6, 256, device="cuda")
+    zn.call("zkb_global_avgpool_fwd", zn.ptr(x), 6, 49, 256, zn.ptr(pooled), 0)
+    assert _rel(pooled.cpu().numpy(), x.double().mean(1).cpu().numpy()) < 1e-6
+    dp = torch.as_tensor(rng.normal(size=(6, 256)).astype(np.float32)).cuda()
+    dx = torch.zeros_like(x)
+    zn.call("zkb_global_avgpool_bwd", zn.ptr(dp), 6, 49, 256, zn.ptr(dx), 0)
+    assert _rel(dx.cpu().numpy(), (dp.double() / 49)[:, None, :].expand(6, 49, 256).cpu().numpy()) < 1e-6
+    # float classifier
+    M, K, N = 9, 256, 1000
+    xs = torch.as_tensor(rng.normal(size=(M, K)).astype(np.float32)).cuda()
+    wk = torch.as_tensor(rng.normal(0, 0.05, (K, N)).astype(np.float32)).cuda()
+    bk = torch.as_tensor(rng.normal(size=(N,)).astype(np.float32)).cuda()
+    y = torch.zeros(M, N, device="cuda")
+    zn.call("zkb_dense_f32_fwd", zn.ptr(xs), zn.ptr(wk), zn.ptr(bk), zn.ptr(y), M, K, N, N, 0)
+    assert _rel(y.cpu().numpy(), (xs.double() @ wk.double() + bk.double()).cpu().numpy()) < 1e-6
+    dy = torch.as_tensor(rng.normal(size=(M, N)).astype(np.float32)).cuda()
+    dxs, dwk, dbk = torch.zeros_like(xs), torch.zeros_like(wk), torch.zeros_like(bk)
+    zn.call("zkb_dense_f32_bwd", zn.ptr(xs), zn.ptr(wk), zn.ptr(dy), N, zn.ptr(dxs), zn.ptr(dwk), zn.ptr(dbk), M, K, N, 0)
+    torch.cuda.synchronize()
+    assert _rel(dxs.cpu().numpy(), (dy.double() @ wk.double().T).cpu().numpy()) < 1e-6
+    assert _rel(dwk.cpu().numpy(), (xs.double().T @ dy.double()).cpu().numpy()) < 1e-6
+    assert _rel(dbk.cpu().numpy(), dy.double().sum(0).cpu().numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("H,W", [(14, 14), (7, 5), (8, 6)])
+def test_stem_maxpool_3x3_stride2_same(native_lib, H, W):
+    from oracle import bireal_oracle as O
+    from zookeeper_b200 import native as zn
+
+    rng = np.random.default_rng(H * 31 + W)
+    # small integers: ties in most windows, so the first-max rule is exercised
+    x = rng.integers(-3, 4, (3, H, W, 64)).astype(np.float32)
+    ref, slot = O.maxpool3s2_same(x)
+    OH, OW = ref.shape[1:3]
+    out = torch.zeros(3, OH, OW, 64, device="cuda")
+    arg = torch.zeros(3, OH, OW, 64, dtype=torch.uint8, device="cuda")
+    dx_ = torch.as_tensor(x).cuda()
+    zn.call("zkb_maxpool3s2_f32_fwd", zn.ptr(dx_), 3, H, W, 64, zn.ptr(out), zn.ptr(arg), 0)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert np.array_equal(arg.cpu().numpy(), slot)
+    dout = rng.normal(size=ref.shape).astype(np.float32)
+    dx = torch.zeros(3, H, W, 64, device="cuda")
+    d_dout = torch.as_tensor(dout).cuda()
+    zn.call("zkb_maxpool3s2_f32_bwd", zn.ptr(d_dout), zn.ptr(arg), 3, H, W, 64, zn.ptr(dx), 0)
+    torch.cuda.synchronize()
+    assert _rel(dx.cpu().numpy(), O.maxpool3s2_same_backward(dout.astype(np.float64), slot, (H, W))) < 1e-6
+
+
+@pytest.mark.parametrize("units,C,hw,B,NC", [(2, 128, (14, 14), 8, 10), (1, 256, (7, 7), 5, 1000)])
+def test_residual_units_train_step_matches_oracle(native_lib, units, C, hw, B, NC):
+    """a Bi-Real-Net-18 residual unit trains one step within 1e-4 of the oracle."""
+    from oracle import bireal_oracle as O
+    from zookeeper_b200.bireal import BiRealUnitsEngine
+
+    p = O.init_params(units, C, NC, seed=3)
+    rng = np.random.default_rng(7)
+    h0 = rng.normal(0, 0.8, (B,) + hw + (C,)).astype(np.float32)
+    lab = rng.integers(0, NC, (B,)).astype(np.int64)
+    ref = O.forward_backward(p, units, h0, lab, torch.float64, keep=True)
+
+    eng = BiRealUnitsEngine(units, C, hw, B, NC)
+    eng.load_params(p)
+    eng.train_step(torch.as_tensor(h0).cuda(), torch.as_tensor(lab).cuda(), apply_update=False)
+    torch.cuda.synchronize()
+    for u in range(units):
+        # the +-1 contraction is exact; the magnitude scale only enters through the BatchNorm gain
+        assert np.array_equal(eng.units[u].y.cpu().numpy().astype(np.int64), ref["acts"][f"y{u}"]), f"unit {u}: integers"
+        assert _rel(eng.units[u].alpha.cpu().numpy(), ref["acts"][f"alpha{u}"]) < 1e-6
+        assert _rel(eng.h[u + 1].cpu().numpy(), ref["acts"][f"h{u + 1}"]) < 1e-5, f"unit {u}: output map"
+    assert abs(eng.last_loss() - ref["loss"]) <= REL_TOL * abs(ref["loss"])
+    assert _rel(eng.logits.cpu().numpy(), ref["logits"]) < REL_TOL
+    assert eng.last_accuracy() == pytest.approx(ref["accuracy"])
+    g = eng.get_grads()
+    for k, v in ref["grads"].items():
+        assert _rel(g[k], v) < REL_TOL, f"grad {k}: rel {_rel(g[k], v):.3g}"
+    # optimizer: Adam everywhere, clip on the latent binary kernels only
+    zero = {k: np.zeros_like(v) for k, v in p.items()}
+    exp64, _, _ = O.adam_step(p, {k: ref["grads"][k] for k in p}, zero, zero, 1)
+    exp32, _, _ = O.adam_step(p, {k: g[k] for k in p}, zero, zero, 1, dtype=np.float32)
+    eng._stream = torch.cuda.current_stream().cuda_stream
+    eng.optimizer_step()
+    torch.cuda.synchronize()
+    got = eng.get_params()
+    for k in p:
+        assert _rel(got[k], exp32[k]) < 2e-6, f"adam kernel {k}"
+        if k.startswith("kernel"):
+            assert _rel(got[k], exp64[k]) < REL_TOL and np.abs(got[k]).max() <= 1.0, k
+
+
+def test_residual_units_learn(native_lib):
+    """A few hundred steps on a learnable task: the loss falls and the batch accuracy rises (the
+    quantizer gradients, the gain BatchNorm and the shortcut work together across steps)."""
+    from oracle import bireal_oracle as O
+    from zookeeper_b200.bireal import BiRealUnitsEngine
+
+    units, C, hw, B, NC = 2, 128, (7, 7), 64, 10
+    rng = np.random.default_rng(11)
+    protos = rng.normal(0, 0.7, (NC,) + hw + (C,)).astype(np.float32)
+    eng = BiRealUnitsEngine(units, C, hw, B, NC)
+    eng.load_params(O.init_params(units, C, NC, seed=5))
+    first, last = [], []
+    for s in range(120):
+        lab = rng.integers(0, NC, (B,))
+        h0 = (protos[lab] * 0.5 + rng.normal(0, 0.6, (B,) + hw + (C,))).astype(np.float32)
+        eng.train_step(torch.as_tensor(h0).cuda(), torch.as_tensor(lab).cuda())
+        (first if s < 10 else last).append((eng.last_loss(), eng.last_accuracy()))
+    assert np.mean([a for _, a in last[-10:]]) > 0.9 > np.mean([a for _, a in first])
+    assert np.mean([l for l, _ in last[-10:]]) < 0.5 * np.mean([l for l, _ in first])

@@ -73,6 +73,12 @@ __device__ __forceinline__ void sample_aug(const PreParams& p, int b, int& ox, i
   flip = static_cast<int>((r >> 32) & 1u);
 }
 
+constexpr int kPreGroupsPerThread = 4;
+
+// CT > 0 (and OW % 4 == 0): a work item is 4 consecutive output pixels of one row = CT float4
+// stores; a thread takes kPreGroupsPerThread items 256 apart (coalesced across the block), so the
+// table and the sample geometry are set up once per 4096 * CT outputs and the index arithmetic is
+// per pixel, not per element.  CT == 0: generic path, one float4 of arbitrary (pixel, channel) mix.
 template <int CT>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const PreParams p) {
@@ -107,31 +113,65 @@ preprocess_kernel(const PreParams p) {
     }
   }
   __syncthreads();
-  const int C = CT ? CT : p.C;
-  const unsigned row_elems = static_cast<unsigned>(p.OW * C);
-  const unsigned vec_per_row = row_elems >> 2;
-  const unsigned vec_per_img = static_cast<unsigned>(p.OH) * vec_per_row;
-  const unsigned v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v >= vec_per_img) return;
-  const unsigned oh = v / vec_per_row;
-  const unsigned re = (v - oh * vec_per_row) << 2;      // first element of this vector in its row
   const int dx = s_geo[1], flip = s_geo[3];
-  const int ih = static_cast<int>(oh) + s_geo[2];
-  float o[4] = {s_lut[0], s_lut[0], s_lut[0], s_lut[0]};   // outside the source image: pixel value 0
-  if (ih >= 0 && ih < p.IH) {
-    const uint8_t* row = p.images + (static_cast<long long>(s_geo[0]) * p.IH + ih) * p.IW * C;
+  const float pad_value = s_lut[0];                       // outside the source image: pixel value 0
+  if constexpr (CT > 0) {
+    const unsigned gpr = static_cast<unsigned>(p.OW) >> 2;           // 4-pixel groups per row
+    const unsigned groups = static_cast<unsigned>(p.OH) * gpr;
+    const uint8_t* img = p.images + static_cast<long long>(s_geo[0]) * p.IH * p.IW * CT;
+    float* out_img = p.out + static_cast<long long>(b) * groups * (4 * CT);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const unsigned e = re + j;
-      unsigned ow = e / static_cast<unsigned>(C);       // (a shift / multiply when CT is known)
-      const unsigned c = e - ow * C;
-      if (flip) ow = p.OW - 1 - ow;
-      const int iw = static_cast<int>(ow) + dx;
-      if (iw >= 0 && iw < p.IW) o[j] = s_lut[__ldg(row + iw * C + c)];
+    for (int k = 0; k < kPreGroupsPerThread; ++k) {
+      const unsigned g = (blockIdx.x * kPreGroupsPerThread + k) * 256u + threadIdx.x;
+      if (g >= groups) break;
+      const unsigned oh = g / gpr;
+      const unsigned ow0 = (g - oh * gpr) << 2;
+      const int ih = static_cast<int>(oh) + s_geo[2];
+      float o[4 * CT];
+#pragma unroll
+      for (int j = 0; j < 4 * CT; ++j) o[j] = pad_value;
+      if (ih >= 0 && ih < p.IH) {
+        const uint8_t* row = img + static_cast<long long>(ih) * p.IW * CT;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int ow = static_cast<int>(ow0) + q;
+          const int iw = (flip ? p.OW - 1 - ow : ow) + dx;
+          if (iw >= 0 && iw < p.IW) {
+#pragma unroll
+            for (int c = 0; c < CT; ++c) o[q * CT + c] = s_lut[__ldg(row + iw * CT + c)];
+          }
+        }
+      }
+      float4* dst = reinterpret_cast<float4*>(out_img + static_cast<size_t>(g) * (4 * CT));
+#pragma unroll
+      for (int v = 0; v < CT; ++v) dst[v] = make_float4(o[4 * v], o[4 * v + 1], o[4 * v + 2], o[4 * v + 3]);
     }
+  } else {
+    const int C = p.C;
+    const unsigned row_elems = static_cast<unsigned>(p.OW * C);
+    const unsigned vec_per_row = row_elems >> 2;
+    const unsigned vec_per_img = static_cast<unsigned>(p.OH) * vec_per_row;
+    const unsigned v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= vec_per_img) return;
+    const unsigned oh = v / vec_per_row;
+    const unsigned re = (v - oh * vec_per_row) << 2;      // first element of this vector in its row
+    const int ih = static_cast<int>(oh) + s_geo[2];
+    float o[4] = {pad_value, pad_value, pad_value, pad_value};
+    if (ih >= 0 && ih < p.IH) {
+      const uint8_t* row = p.images + (static_cast<long long>(s_geo[0]) * p.IH + ih) * p.IW * C;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const unsigned e = re + j;
+        unsigned ow = e / static_cast<unsigned>(C);
+        const unsigned c = e - ow * C;
+        if (flip) ow = p.OW - 1 - ow;
+        const int iw = static_cast<int>(ow) + dx;
+        if (iw >= 0 && iw < p.IW) o[j] = s_lut[__ldg(row + iw * C + c)];
+      }
+    }
+    float* dst = p.out + (static_cast<long long>(b) * vec_per_img + v) * 4;
+    *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
   }
-  float* dst = p.out + (static_cast<long long>(b) * vec_per_img + v) * 4;
-  *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -993,12 +1033,18 @@ ZKB_API int zkb_preprocess_u8(const uint8_t* images, const long long* labels, co
   PreParams p{images, labels, index, aug, out, labels_out, onehot, B, IH, IW, C, OH, OW,
               pad_size, training, binarize, num_classes, seed, step, step_dev};
   ZKB_REQUIRE(B <= 65535, "preprocess: at most 65535 samples per call (got %d)", B);
-  const unsigned vec_per_img = static_cast<unsigned>(OH) * static_cast<unsigned>(OW * C / 4);
-  const dim3 grid((vec_per_img + 255) / 256, B);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (C == 1) preprocess_kernel<1><<<grid, 256, 0, st>>>(p);
-  else if (C == 3) preprocess_kernel<3><<<grid, 256, 0, st>>>(p);
-  else preprocess_kernel<0><<<grid, 256, 0, st>>>(p);
+  if ((C == 1 || C == 3) && OW % 4 == 0) {
+    const unsigned groups = static_cast<unsigned>(OH) * static_cast<unsigned>(OW / 4);
+    const unsigned per_block = 256u * kPreGroupsPerThread;
+    const dim3 grid((groups + per_block - 1) / per_block, B);
+    if (C == 1) preprocess_kernel<1><<<grid, 256, 0, st>>>(p);
+    else preprocess_kernel<3><<<grid, 256, 0, st>>>(p);
+  } else {
+    const unsigned vec_per_img = static_cast<unsigned>(OH) * static_cast<unsigned>(OW * C / 4);
+    const dim3 grid((vec_per_img + 255) / 256, B);
+    preprocess_kernel<0><<<grid, 256, 0, st>>>(p);
+  }
   ZKB_LAUNCH_CHECK("preprocess_kernel");
   return ZKB_OK;
 }
@@ -1148,7 +1194,10 @@ ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_
   if (B == 0) return ZKB_OK;
   const long long rows = static_cast<long long>(B) * (H / 2) * (W / 2);
   const int lanes = 256 / (C / 8);
-  const int grid = grid_for((rows + lanes - 1) / lanes * 256 / 4, 256, 12);
+  // at least 8 pooled pixels per thread (every block ends with 2 float64 atomics per channel), at most 12 blocks per SM
+  long long gmp = (rows + static_cast<long long>(lanes) * 8 - 1) / (static_cast<long long>(lanes) * 8);
+  if (gmp > static_cast<long long>(zkb_sm_count()) * 12) gmp = static_cast<long long>(zkb_sm_count()) * 12;
+  const int grid = gmp < 1 ? 1 : static_cast<int>(gmp);
   const size_t smem = 0;
   maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);

@@ -72,6 +72,17 @@ SIGNATURES = {
     "zkb_prep_dense_weights": [P, I, I, I, P, P, P, P],
     "zkb_sign_f32": [P, P, L, P],
     "zkb_adam_clip": [P, P, P, P, L, F, F, F, F, F, I, P, P],
+    "zkb_weight_abs_mean": [P, L, I, P, P],
+    "zkb_bn_gain_finalize": [P, P, D, P, P, F, F, I, I, P, P, P, P, P, P],
+    "zkb_bn_gain_add": [P, L, I, P, P, P, P, P, P],
+    "zkb_bn_gain_bwd_apply": [P, P, L, I, P, P, P, P, P, P, P, P],
+    "zkb_approx_sign_bwd_add": [P, P, P, P, L, P],
+    "zkb_global_avgpool_fwd": [P, I, I, I, P, P],
+    "zkb_global_avgpool_bwd": [P, I, I, I, P, P],
+    "zkb_dense_f32_fwd": [P, P, P, P, I, I, I, I, P],
+    "zkb_dense_f32_bwd": [P, P, P, I, P, P, P, I, I, I, P],
+    "zkb_maxpool3s2_f32_fwd": [P, I, I, I, I, P, P, P],
+    "zkb_maxpool3s2_f32_bwd": [P, P, I, I, I, I, P, P],
     "zkb_bn_train_sign_static": [P, I, L, I, P, F, F, I, P, P, P, P, P],
 }
 
