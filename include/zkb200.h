@@ -291,6 +291,18 @@ int zkb_dense_f32_fwd(const float* x, const float* w_k_n, const float* bias, flo
                       int N, int ldy, void* stream);
 int zkb_dense_f32_bwd(const float* x, const float* w_k_n, const float* dy, int lddy, float* dx,
                       float* dw_k_n, float* dbias, int M, int K, int N, void* stream);
+/* Stride-2 binary 'same' convolutions (the down-sampling units): TensorFlow's padding rule --
+ * out = ceil(in/2), total padding max((out-1)*2 + ksize - in, 0), the smaller half first -- goes into
+ * the im2col tensor map (traversal stride 2, asymmetric corners), so the forward and the weight
+ * gradient are the same GEMM kernels reading a strided window.  y [NB,ceil(H/2),ceil(W/2),Cout];
+ * act / dw as for the stride-1 entry points.  The input gradient is the stride-1 zkb_bconv2d_dgrad
+ * over the zero-inserted gradient map [NB,H,W,Cout] that zkb_dilate2_hi_lo writes. */
+int zkb_bconv2d_fwd_i8_s2(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H, int W,
+                          int Cin, int Cout, int ksize, void* stream);
+int zkb_bconv2d_wgrad_s2(const void* act_pm1, const void* dy_hi, const void* dy_lo, float* dw_hwio, int NB,
+                         int H, int W, int Cin, int Cout, int ksize, void* stream);
+int zkb_dilate2_hi_lo(const void* dy_hi, const void* dy_lo, int B, int H, int W, int C, int ksize,
+                      void* out_hi, void* out_lo, void* stream);
 /* MaxPool2D(pool_size=3, strides=2, padding="same") of the stem, float NHWC, C % 4 == 0:
  * out [B,ceil(H/2),ceil(W/2),C]; arg (same shape, uint8) = winning window slot kh*3+kw, first
  * maximum in row-major order; the backward gathers dout through arg into dx [B,H,W,C]. */

@@ -90,6 +90,52 @@ def test_stem_maxpool_3x3_stride2_same(native_lib, H, W):
     assert _rel(dx.cpu().numpy(), O.maxpool3s2_same_backward(dout.astype(np.float64), slot, (H, W))) < 1e-6
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(3, 14, 14, 128, 256), (2, 7, 9, 128, 128), (5, 28, 28, 128, 256), (2, 13, 8, 256, 512)])
+def test_stride2_binary_conv_forward_wgrad_dgrad(native_lib, B, H, W, Cin, Cout):
+    """Down-sampling binary conv (3x3, stride 2, TensorFlow 'same' padding: asymmetric on even sizes):
+    forward integers exact, weight gradient and input gradient (stride-1 dgrad over the zero-inserted
+    map) against the float64 strided convolution, even and odd sizes."""
+    from zookeeper_b200 import native as zn
+
+    g = torch.Generator(device="cpu").manual_seed(H * 100 + W)
+    x = (torch.randint(0, 2, (B, H, W, Cin), generator=g, dtype=torch.int8) * 2 - 1).cuda()
+    w = (torch.randint(0, 2, (3, 3, Cin, Cout), generator=g, dtype=torch.int8) * 2 - 1).cuda()
+    wf = torch.empty(Cout, 9 * Cin, dtype=torch.bfloat16, device="cuda")
+    wd = torch.empty(Cin, 9 * Cout, dtype=torch.bfloat16, device="cuda")
+    wf8 = torch.empty(Cout, 9 * Cin, dtype=torch.int8, device="cuda")
+    w32 = w.float().contiguous()
+    zn.call("zkb_prep_conv_weights", zn.ptr(w32), 3, Cin, Cout, zn.ptr(wf), zn.ptr(wd), zn.ptr(wf8), 0)
+    OH, OW = (H + 1) // 2, (W + 1) // 2
+    th, tw = max((OH - 1) * 2 + 3 - H, 0), max((OW - 1) * 2 + 3 - W, 0)
+    xr = x.permute(0, 3, 1, 2).double().requires_grad_(True)
+    wr = w.permute(3, 2, 0, 1).double().requires_grad_(True)
+    xp = torch.nn.functional.pad(xr, (tw // 2, tw - tw // 2, th // 2, th - th // 2))
+    ref = torch.nn.functional.conv2d(xp, wr, stride=2)
+    assert ref.shape[2:] == (OH, OW)
+    y = torch.full((B, OH, OW, Cout), -7, dtype=torch.int16, device="cuda")
+    xc = x.contiguous()
+    zn.call("zkb_bconv2d_fwd_i8_s2", zn.ptr(xc), zn.ptr(wf8), zn.ptr(y), B, H, W, Cin, Cout, 3, 0)
+    torch.cuda.synchronize()
+    assert torch.equal(y.double(), ref.detach().permute(0, 2, 3, 1)), "stride-2 forward integers"
+    dy = torch.randn(B, OH, OW, Cout, generator=g).cuda()
+    ref.backward(dy.permute(0, 3, 1, 2).double())
+    hi = dy.to(torch.bfloat16).contiguous()
+    lo = (dy - hi.float()).to(torch.bfloat16).contiguous()
+    xb = x.to(torch.bfloat16).contiguous()
+    dw = torch.zeros(3, 3, Cin, Cout, dtype=torch.float32, device="cuda")
+    zn.call("zkb_bconv2d_wgrad_s2", zn.ptr(xb), zn.ptr(hi), zn.ptr(lo), zn.ptr(dw), B, H, W, Cin, Cout, 3, 0)
+    Dh = torch.full((B, H, W, Cout), 3.0, dtype=torch.bfloat16, device="cuda")
+    Dl = torch.full((B, H, W, Cout), 3.0, dtype=torch.bfloat16, device="cuda")
+    zn.call("zkb_dilate2_hi_lo", zn.ptr(hi), zn.ptr(lo), B, H, W, Cout, 3, zn.ptr(Dh), zn.ptr(Dl), 0)
+    dx = torch.empty(B, H, W, Cin, dtype=torch.float32, device="cuda")
+    zn.call("zkb_bconv2d_dgrad", zn.ptr(Dh), zn.ptr(Dl), zn.ptr(wd), zn.ptr(dx), B, H, W, Cin, Cout, 3, 0)
+    torch.cuda.synchronize()
+    assert int((Dh.float() != 0).sum()) <= B * OH * OW * Cout          # zeros everywhere else
+    for got, rf, what in ((dw.double(), wr.grad.permute(2, 3, 1, 0), "wgrad"), (dx.double(), xr.grad.permute(0, 2, 3, 1), "dgrad")):
+        rel = ((got - rf).norm() / rf.norm()).item()
+        assert rel < 1e-5, f"stride-2 {what}: {rel:.3g}"
+
+
 @pytest.mark.parametrize("units,C,hw,B,NC", [(2, 128, (14, 14), 8, 10), (1, 256, (7, 7), 5, 1000)])
 def test_residual_units_train_step_matches_oracle(native_lib, units, C, hw, B, NC):
     """a Bi-Real-Net-18 residual unit trains one step within 1e-4 of the oracle."""

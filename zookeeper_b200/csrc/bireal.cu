@@ -324,6 +324,37 @@ maxpool3s2_bwd_kernel(const float* __restrict__ dout, const uint8_t* __restrict_
   }
 }
 
+// Zero insertion for the input gradient of a stride-2 'same' conv: the output-resolution gradient
+// (hi/lo pair) is written to position (2 oh + 1 - pad_h, 2 ow + 1 - pad_w) of an input-resolution map
+// and zeros everywhere else; the ordinary stride-1 dgrad GEMM over that map is then the transposed
+// strided conv (ds[q] = sum_taps dy[(q - tap + pad) / 2] w[tap] wherever the division is exact).
+// Thread = (input pixel, 8 channels): every element of the map is written exactly once.
+__global__ void __launch_bounds__(256)
+dilate2_hi_lo_kernel(const uint16_t* __restrict__ hi, const uint16_t* __restrict__ lo, int B, int H, int W,
+                     int C, int OH, int OW, int off_h, int off_w, uint16_t* __restrict__ out_hi,
+                     uint16_t* __restrict__ out_lo) {
+  const int tpr = C / 8;
+  const long long total = static_cast<long long>(B) * H * W * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cl = static_cast<int>(i % tpr);
+    long long r = i / tpr;
+    const int iw = static_cast<int>(r % W);
+    r /= W;
+    const int ih = static_cast<int>(r % H);
+    const long long b = r / H;
+    uint4 vh = make_uint4(0, 0, 0, 0), vl = make_uint4(0, 0, 0, 0);
+    const int th = ih - off_h, tw = iw - off_w;
+    if (th >= 0 && tw >= 0 && !(th & 1) && !(tw & 1) && (th >> 1) < OH && (tw >> 1) < OW) {
+      const long long o = (((b * OH + (th >> 1)) * OW + (tw >> 1)) * tpr + cl) * 8;
+      vh = *reinterpret_cast<const uint4*>(hi + o);
+      vl = *reinterpret_cast<const uint4*>(lo + o);
+    }
+    *reinterpret_cast<uint4*>(out_hi + i * 8) = vh;
+    *reinterpret_cast<uint4*>(out_lo + i * 8) = vl;
+  }
+}
+
 }  // namespace zkb
 
 // ============================================================================================
@@ -470,5 +501,25 @@ ZKB_API int zkb_maxpool3s2_f32_bwd(const float* dout, const uint8_t* arg, int B,
   maxpool3s2_bwd_kernel<<<br_grid(static_cast<long long>(B) * H * W * (C / 4), 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       dout, arg, B, H, W, C, OH, OW, ph, pw, dx);
   ZKB_LAUNCH_CHECK("maxpool3s2_bwd_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_dilate2_hi_lo(const void* dy_hi, const void* dy_lo, int B, int H, int W, int C, int ksize,
+                              void* out_hi, void* out_lo, void* stream) {
+  ZKB_REQUIRE(dy_hi && dy_lo && out_hi && out_lo, "dilate2_hi_lo: null pointer");
+  ZKB_REQUIRE(B >= 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0 && ksize % 2 == 1, "dilate2_hi_lo: bad shape (C %% 8 == 0, odd ksize)");
+  ZKB_REQUIRE(ZKB_A16(dy_hi) && ZKB_A16(dy_lo) && ZKB_A16(out_hi) && ZKB_A16(out_lo), "dilate2_hi_lo: misaligned tensors");
+  if (B == 0) return ZKB_OK;
+  const int OH = (H + 1) / 2, OW = (W + 1) / 2;
+  int th = (OH - 1) * 2 + ksize - H, tw = (OW - 1) * 2 + ksize - W;
+  if (th < 0) th = 0;
+  if (tw < 0) tw = 0;
+  // forward tap kh reads input row 2 oh + kh - pad_lo; the stride-1 dgrad over the dilated map D
+  // reads D[q + pad1 - kh] with pad1 = ksize / 2, so dy[oh] must sit at row 2 oh + pad1 - pad_lo
+  const int off_h = ksize / 2 - th / 2, off_w = ksize / 2 - tw / 2;
+  dilate2_hi_lo_kernel<<<br_grid(static_cast<long long>(B) * H * W * (C / 8), 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint16_t*>(dy_hi), static_cast<const uint16_t*>(dy_lo), B, H, W, C, OH, OW, off_h, off_w,
+      static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo));
+  ZKB_LAUNCH_CHECK("dilate2_hi_lo_kernel");
   return ZKB_OK;
 }

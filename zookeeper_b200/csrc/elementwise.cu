@@ -132,13 +132,43 @@ preprocess_kernel(const PreParams p) {
       for (int j = 0; j < 4 * CT; ++j) o[j] = pad_value;
       if (ih >= 0 && ih < p.IH) {
         const uint8_t* row = img + static_cast<long long>(ih) * p.IW * CT;
+        // the four pixels are 4*CT CONTIGUOUS source bytes (descending pixel order when flipped),
+        // starting at the lowest input column iw_first
+        const int iw_first = (flip ? p.OW - 4 - static_cast<int>(ow0) : static_cast<int>(ow0)) + dx;
+        const bool tail_ok = (ih + 1 < p.IH) || ((p.IW - iw_first - 4) * CT >= 3);
+        if (iw_first >= 0 && iw_first + 4 <= p.IW && tail_ok) {
+          // Interior group: fetch the bytes as aligned 32-bit words (at most 4 loads instead of
+          // 4*CT byte loads 4*CT bytes apart across the warp) and realign them with funnel shifts.
+          // Only words that hold a needed byte are read; a word may reach up to 3 bytes past the
+          // group, which tail_ok keeps inside this image.
+          const uint8_t* a0 = row + iw_first * CT;
+          const unsigned m = static_cast<unsigned>(reinterpret_cast<uintptr_t>(a0) & 3u);
+          const uint32_t* wp = reinterpret_cast<const uint32_t*>(a0 - m);
+          const unsigned nw = (m + 4u * CT + 3u) >> 2;
+          uint32_t w[CT + 1];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int ow = static_cast<int>(ow0) + q;
-          const int iw = (flip ? p.OW - 1 - ow : ow) + dx;
-          if (iw >= 0 && iw < p.IW) {
+          for (int k = 0; k < CT + 1; ++k) w[k] = (static_cast<unsigned>(k) < nw) ? __ldg(wp + k) : 0u;
+          uint32_t r[CT];
 #pragma unroll
-            for (int c = 0; c < CT; ++c) o[q * CT + c] = s_lut[__ldg(row + iw * CT + c)];
+          for (int k = 0; k < CT; ++k) r[k] = __funnelshift_r(w[k], w[k + 1], 8u * m);
+#pragma unroll
+          for (int qs = 0; qs < 4; ++qs) {        // qs: pixel in ascending source order
+            const int q = flip ? 3 - qs : qs;     // its place in the output group
+#pragma unroll
+            for (int c = 0; c < CT; ++c) {
+              const int j = qs * CT + c;
+              o[q * CT + c] = s_lut[(r[j >> 2] >> (8 * (j & 3))) & 0xFFu];
+            }
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int ow = static_cast<int>(ow0) + q;
+            const int iw = (flip ? p.OW - 1 - ow : ow) + dx;
+            if (iw >= 0 && iw < p.IW) {
+#pragma unroll
+              for (int c = 0; c < CT; ++c) o[q * CT + c] = s_lut[__ldg(row + iw * CT + c)];
+            }
           }
         }
       }

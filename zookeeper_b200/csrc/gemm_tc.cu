@@ -53,7 +53,8 @@ struct KGemmParams {
   int stage_bytes;
   int tiles_m, tiles_n;
   int a_im2col;
-  int OH, OW, pad, kw_taps, cblocks;
+  int OH, OW, pad, kw_taps, cblocks;   // OH, OW: OUTPUT map; pad: low zero padding along W
+  int pad_h, stride;                   // low padding along H; traversal stride (1, or 2 for 'same' stride-2 convs)
   int out_kind;  // 0: f32, 1: int16 (exact integers expected)
   int is_i8;     // operands are signed int8 (+-1 / 0), accumulators int32 (kind::i8)
   int dbg;       // ZKB_MEASURE builds only: 1 = no MMA issue, 2 = no TMA loads
@@ -278,7 +279,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
               if (h >= nbox || !live[h]) continue;
               const uint32_t dst = sX + static_cast<uint32_t>(t) * term_bytes + static_cast<uint32_t>(h) * box_bytes;
               if (p.a_im2col)
-                tma_load_im2col_4d(dst, mp, full, cb * p.kelems, ow[h] - p.pad, oh[h] - p.pad, img[h],
+                tma_load_im2col_4d(dst, mp, full, cb * p.kelems, ow[h] * p.stride - p.pad, oh[h] * p.stride - p.pad_h, img[h],
                                    static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
               else
                 tma_load_2d(dst, mp, full, kb * p.kelems, m0 + h * box_px);
@@ -327,10 +328,10 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           if (elect_one()) {
           mbar_expect_tx(full, static_cast<uint32_t>(p.stage_bytes));
           if (p.a_im2col) {
-            tma_load_im2col_4d(sA, &tmA0, full, cb * p.kelems, ow - p.pad, oh - p.pad, img,
+            tma_load_im2col_4d(sA, &tmA0, full, cb * p.kelems, ow * p.stride - p.pad, oh * p.stride - p.pad_h, img,
                                static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
             if (p.a_terms == 2)
-              tma_load_im2col_4d(sA + kATileBytes, &tmA1, full, cb * p.kelems, ow - p.pad, oh - p.pad,
+              tma_load_im2col_4d(sA + kATileBytes, &tmA1, full, cb * p.kelems, ow * p.stride - p.pad, oh * p.stride - p.pad_h,
                                  img, static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
           } else {
             tma_load_2d(sA, &tmA0, full, kb * p.kelems, m0);
@@ -782,11 +783,11 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
           const uint32_t sA = smem_u32(smem + static_cast<size_t>(stage) * p.stage_bytes);
           const uint32_t sB = sA + static_cast<uint32_t>(p.a_terms) * kATileBytes;
           if (p.a_im2col && live) {
-            tma2_load_im2col_4d(sA, &tmA0, full_leader, cb * p.kelems, ow - p.pad, oh - p.pad, img,
+            tma2_load_im2col_4d(sA, &tmA0, full_leader, cb * p.kelems, ow * p.stride - p.pad, oh * p.stride - p.pad_h, img,
                                 static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
             if (p.a_terms == 2)
-              tma2_load_im2col_4d(sA + kATileBytes, &tmA1, full_leader, cb * p.kelems, ow - p.pad,
-                                  oh - p.pad, img, static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
+              tma2_load_im2col_4d(sA + kATileBytes, &tmA1, full_leader, cb * p.kelems, ow * p.stride - p.pad,
+                                  oh * p.stride - p.pad_h, img, static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
           } else {
             // plain rows, or an im2col tile entirely past the end: a 2D load whose rows are out
             // of bounds delivers zeros and still completes the expected bytes
@@ -971,7 +972,8 @@ struct WGemmParams {
                 //    halves of the accumulator are added in the epilogue
   int cols_per_tile;  // output columns one work item covers (128 when concat, else block_n)
   int a_im2col;
-  int OH, OW, pad, kw_taps, taps;
+  int OH, OW, pad, kw_taps, taps;   // OH, OW: the conv's OUTPUT map (rows of dy); pad: low padding along W
+  int pad_h, stride;
   int tpi;      // taps per work item: they share the B (dy) tile, one TMEM accumulator each
   int kpix;     // reduction rows per pipeline stage (32, 48 or 64)
   int dbg;      // ZKB_MEASURE builds only: 1 = no MMA issue, 2 = no TMA loads
@@ -1086,8 +1088,8 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const unsigned rem = pix0 - img * hw;
             const unsigned oh = rem / static_cast<unsigned>(p.OW);
             const unsigned ow = rem - oh * static_cast<unsigned>(p.OW);
-            tma_load_im2col_4d(dst, my_map, full, my_c, static_cast<int>(ow) - p.pad,
-                               static_cast<int>(oh) - p.pad, static_cast<int>(img),
+            tma_load_im2col_4d(dst, my_map, full, my_c, static_cast<int>(ow) * p.stride - p.pad,
+                               static_cast<int>(oh) * p.stride - p.pad_h, static_cast<int>(img),
                                static_cast<uint16_t>(kw), static_cast<uint16_t>(kh));
           }
         }
@@ -1222,6 +1224,21 @@ static const GemmTuning& gemm_tuning() {
   return t;
 }
 
+// 'same' padding of a stride-s conv as TensorFlow defines it: out = ceil(in / s), total padding
+// max((out - 1) s + k - in, 0), the smaller half in front.  s == 1: (k - 1) / 2 on both sides.
+struct SameGeom {
+  int out, lo, hi;
+};
+static SameGeom same_geometry(int in, int ksize, int stride) {
+  SameGeom g;
+  g.out = (in + stride - 1) / stride;
+  int total = (g.out - 1) * stride + ksize - in;
+  if (total < 0) total = 0;
+  g.lo = total / 2;
+  g.hi = total - g.lo;
+  return g;
+}
+
 static int pick_block_n(int N) {
   if (N >= 256) return 256;
   if (N > 128) return 256;
@@ -1259,7 +1276,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
                         int H, int W, int C, int ksize, int pad, cudaStream_t stream,
                         int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr,
                         const BnBackwardFuse* bn = nullptr, const StatsFuse* st = nullptr,
-                        const int* sign_thr = nullptr) {
+                        const int* sign_thr = nullptr, int stride = 1) {
   const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
   const CUtensorMapDataType dt =
       elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -1365,19 +1382,25 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   if (im2col) {
     ZKB_REQUIRE(C % kelems == 0, "kgemm: channels C=%d must be a multiple of %d", C, kelems);
     ZKB_REQUIRE(K == ksize * ksize * C, "kgemm: K=%d != ksize^2*C", K);
-    ZKB_REQUIRE(M == static_cast<long long>(NB) * H * W, "kgemm: M != NB*H*W");
     ZKB_REQUIRE(ksize == 2 * pad + 1, "kgemm: only 'same' windows (ksize == 2*pad+1)");
-    p.OH = H;
-    p.OW = W;
-    p.pad = pad;
+    ZKB_REQUIRE(stride == 1 || stride == 2, "kgemm: stride must be 1 or 2");
+    const SameGeom gh = same_geometry(H, ksize, stride), gw = same_geometry(W, ksize, stride);
+    ZKB_REQUIRE(M == static_cast<long long>(NB) * gh.out * gw.out, "kgemm: M != NB*OH*OW");
+    p.OH = gh.out;
+    p.OW = gw.out;
+    p.pad = gw.lo;
+    p.pad_h = gh.lo;
+    p.stride = stride;
     p.kw_taps = ksize;
     p.cblocks = C / kelems;
     const int abox = p.swap ? p.swap_box_px : 128;   // pixel rows per A box
-    rc = zkb_tmap_im2col_nhwc(&tmA0, dt, elem_bytes, A_hi, NB, H, W, C, ksize, pad, kelems, abox);
+    rc = zkb_tmap_im2col_nhwc_ex(&tmA0, dt, elem_bytes, A_hi, NB, H, W, C, ksize, gh.lo, gh.hi, gw.lo, gw.hi,
+                                 stride, kelems, abox);
     if (rc) return rc;
     tmA1 = tmA0;
     if (A_lo) {
-      rc = zkb_tmap_im2col_nhwc(&tmA1, dt, elem_bytes, A_lo, NB, H, W, C, ksize, pad, kelems, abox);
+      rc = zkb_tmap_im2col_nhwc_ex(&tmA1, dt, elem_bytes, A_lo, NB, H, W, C, ksize, gh.lo, gh.hi, gw.lo, gw.hi,
+                                   stride, kelems, abox);
       if (rc) return rc;
     }
   } else {
@@ -1451,7 +1474,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
 // B_hi/B_lo: bf16 [P][N].  out f32 [(taps*Ma)][ldo], accumulated into (caller zeroes it).
 static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float* out,
                         long long ldo, int Ma, int N, int n_valid, long long P, int im2col, int NB,
-                        int H, int W, int ksize, int pad, cudaStream_t stream) {
+                        int H, int W, int ksize, int pad, cudaStream_t stream, int stride = 1) {
   ZKB_REQUIRE(A && B_hi && out, "wgemm: null pointer");
   ZKB_REQUIRE(Ma > 0 && N > 0 && P > 0, "wgemm: empty problem");
   ZKB_REQUIRE(Ma % 128 == 0, "wgemm: Ma=%d must be a multiple of 128", Ma);
@@ -1488,9 +1511,14 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   p.dbg = tune.dbg;
   if (im2col && tune.wgrad_tpi >= 1 && tune.wgrad_tpi * p.block_n <= 512) p.tpi = tune.wgrad_tpi;
   if (tune.wgrad_kpix) p.kpix = tune.wgrad_kpix;
-  p.pad = pad;
-  p.OH = H;
-  p.OW = W;
+  // H, W: the A activation's map; rows of dy index the conv's output map (equal for stride 1)
+  const SameGeom wgh = same_geometry(H > 0 ? H : 1, im2col ? ksize : 1, stride);
+  const SameGeom wgw = same_geometry(W > 0 ? W : 1, im2col ? ksize : 1, stride);
+  p.pad = wgw.lo;
+  p.pad_h = wgh.lo;
+  p.stride = stride;
+  p.OH = wgh.out;
+  p.OW = wgw.out;
   p.ci_tiles = Ma / 128;
   p.n_tiles = N / p.cols_per_tile;
   const int boxes_b = p.b_terms * (p.concat ? 2 : p.block_n / 64);
@@ -1530,10 +1558,11 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   CUtensorMap tmA, tmB0, tmB1;
   int rc;
   if (im2col) {
-    ZKB_REQUIRE(P == static_cast<long long>(NB) * H * W, "wgemm: P != NB*H*W");
+    ZKB_REQUIRE(stride == 1 || stride == 2, "wgemm: stride must be 1 or 2");
+    ZKB_REQUIRE(P == static_cast<long long>(NB) * p.OH * p.OW, "wgemm: P != NB*OH*OW");
     ZKB_REQUIRE(ksize == 2 * pad + 1, "wgemm: only 'same' windows (ksize == 2*pad+1)");
-    rc = zkb_tmap_im2col_nhwc(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, NB, H, W, Ma, ksize,
-                              pad, 64, p.kpix);
+    rc = zkb_tmap_im2col_nhwc_ex(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, NB, H, W, Ma, ksize,
+                                 wgh.lo, wgh.hi, wgw.lo, wgw.hi, stride, 64, p.kpix);
   } else {
     rc = zkb_tmap_tiled_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, Ma, P,
                            static_cast<uint64_t>(Ma) * 2, 64, p.kpix);
@@ -1573,6 +1602,23 @@ ZKB_API int zkb_bconv2d_fwd_i8(const void* act_i8, const void* wq_oc_k_i8, void*
   return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout,
                       static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
                       Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1);
+}
+
+ZKB_API int zkb_bconv2d_fwd_i8_s2(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H,
+                                  int W, int Cin, int Cout, int ksize, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_fwd_i8_s2: ksize must be odd");
+  const long long OH = (H + 1) / 2, OW = (W + 1) / 2;
+  return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout, NB * OH * OW, Cout, ksize * ksize * Cin, 1,
+                      NB, H, W, Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1, nullptr, nullptr,
+                      nullptr, nullptr, 2);
+}
+
+ZKB_API int zkb_bconv2d_wgrad_s2(const void* act_pm1, const void* dy_hi, const void* dy_lo, float* dw_hwio,
+                                 int NB, int H, int W, int Cin, int Cout, int ksize, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_wgrad_s2: ksize must be odd");
+  const long long OH = (H + 1) / 2, OW = (W + 1) / 2;
+  return launch_wgemm(act_pm1, dy_hi, dy_lo, dw_hwio, Cout, Cin, Cout, Cout, NB * OH * OW, 1, NB, H, W, ksize,
+                      ksize / 2, static_cast<cudaStream_t>(stream), 2);
 }
 
 ZKB_API int zkb_bconv2d_fwd_i8_stats(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB,

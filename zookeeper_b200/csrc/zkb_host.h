@@ -55,4 +55,11 @@ int zkb_tmap_im2col_nhwc(CUtensorMap* out, CUtensorMapDataType dt, int elem_byte
                          const void* base, int N, int H, int W, int C, int ksize, int pad,
                          uint32_t channels_per_pixel, uint32_t pixels_per_column);
 
+// The same with a traversal stride and separate low / high zero padding per spatial axis (strided
+// 'same' convolutions pad asymmetrically): base pixels run from -pad_lo in steps of `stride`.
+int zkb_tmap_im2col_nhwc_ex(CUtensorMap* out, CUtensorMapDataType dt, int elem_bytes, const void* base,
+                            int N, int H, int W, int C, int ksize, int pad_lo_h, int pad_hi_h,
+                            int pad_lo_w, int pad_hi_w, int stride, uint32_t channels_per_pixel,
+                            uint32_t pixels_per_column);
+
 int zkb_sm_count();
