@@ -256,7 +256,11 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
             ow[h] = rem - oh[h] * p.OW;
           }
         }
-        const uint32_t tx = static_cast<uint32_t>(kATileBytes) + static_cast<uint32_t>(p.a_terms * n_live) * box_bytes;
+        // (ZKB_MEASURE, dbg bit 8: the second term loads one box instead of n_live -- the bytes an
+        // 8-bit residual would need)
+        const int lo_boxes = (ZKB_DBG(p, 8) && p.a_terms == 2) ? (n_live > 0 ? 1 : 0) : n_live;
+        const uint32_t tx = static_cast<uint32_t>(kATileBytes) +
+                            static_cast<uint32_t>((p.a_terms == 2 ? n_live + lo_boxes : n_live)) * box_bytes;
         int cb = 0, kw = 0, kh = 0;   // k-block -> (filter tap, channel block), advanced without divisions
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&ctl->empty[stage]), phase ^ 1u);
@@ -277,6 +281,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
               if (h >= nbox || !live[h]) continue;
+              if (t == 1 && h >= lo_boxes) continue;
               const uint32_t dst = sX + static_cast<uint32_t>(t) * term_bytes + static_cast<uint32_t>(h) * box_bytes;
               if (p.a_im2col)
                 tma_load_im2col_4d(dst, mp, full, cb * p.kelems, ow[h] * p.stride - p.pad, oh[h] * p.stride - p.pad_h, img[h],
@@ -383,12 +388,16 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
             for (int t = 0; t < p.a_terms; ++t) {
               const uint64_t ad = m_desc + t * m_step, bd = n_desc + t * n_step;
               // a 128-byte row holds 64 bf16 or 128 int8: either way 4 MMAs of 32 bytes of K
+              // (ZKB_MEASURE, dbg bit 4: the second term issues HALF its MMAs -- the instruction
+              // count an e4m3 residual on kind::f8f6f4 would need; timing only, results are wrong)
+              const int nk = (ZKB_DBG(p, 4) && t == 1) ? 2 : 4;
               if (p.is_i8) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_i8(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
               } else {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
+                for (int k = 0; k < 4; ++k)
+                  if (k < nk) umma_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
               }
             }
           }
@@ -832,12 +841,14 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
           if (elect_one()) {
           for (int t = 0; t < p.a_terms; ++t) {
             const uint64_t ad = a_desc + static_cast<uint64_t>(t) * (kATileBytes >> 4);
+            const int nk = (ZKB_DBG(p, 4) && t == 1) ? 2 : 4;     // see kgemm_body
             if (p.is_i8) {
 #pragma unroll
               for (int k = 0; k < 4; ++k) umma2_i8(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
             } else {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) umma2_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < 4; ++k)
+                if (k < nk) umma2_f16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (kb | t | k) != 0 ? 1u : 0u);
             }
           }
           umma2_commit(smem_u32(&ctl->empty[stage]));   // frees the slot in both CTAs
@@ -1125,6 +1136,7 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               // 16 reduction rows per MMA = 2 groups of 8 rows (1024 B each): 2048 B per k-step
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
+                if (ZKB_DBG(p, 4) && bt == 1 && 2 * k >= ksteps) continue;   // see kgemm_body
                 if (k < ksteps && !ZKB_DBG(p, 1))
                   umma_f16(d_tmem, a_desc + static_cast<uint64_t>(k * 128), b_desc + static_cast<uint64_t>(k * 128),
                            idesc, (ch | bt | k) != 0 ? 1u : 0u);
