@@ -114,6 +114,19 @@ int zkb_bconv2d_fwd_i8_stats(const void* act_i8, const void* wq_oc_k_i8, void* y
                              void* stream);
 int zkb_bdense_fwd_i8_stats(const void* act_i8, const void* wq_n_k_i8, void* y_i16, long long ldy,
                             int rows, int K, int N, double* sum, double* sumsq, void* stream);
+/* The int8 conv forward of a layer that is followed by MaxPool2D(2, 2): the epilogue stages each
+ * tile -- whole row pairs of the output map -- in shared memory and pools it there (first maximum
+ * in row-major window order, as zkb_maxpool2_i16), so only the pooled int16 map p [NB,H/2,W/2,Cout],
+ * the winning slot arg (uint8, same shape) and the pooled map's BatchNorm sums leave the kernel; the
+ * full-resolution map (2 B written + 2 B read per element otherwise) never reaches memory.  Needs an
+ * even map whose row pairs tile 256 MMA columns and Cout % 128 == 0: zkb_bconv2d_fwd_i8_pool_ok
+ * returns 1 for such shapes (26x26, 30x30, 6x6, ...), 0 otherwise (13x13, 15x15, 7x7: those layers
+ * keep zkb_bconv2d_fwd_i8 + zkb_maxpool2_i16).  Bit-identical to the two-kernel form.
+ * Replaces: QuantConv2D + MaxPool2D, examples/larq_experiment.py:71-74, 85-92. */
+int zkb_bconv2d_fwd_i8_pool_ok(int H, int W, int Cout);
+int zkb_bconv2d_fwd_i8_pool(const void* act_i8, const void* wq_oc_k_i8, void* p_i16, uint8_t* arg_u8, int NB,
+                            int H, int W, int Cin, int Cout, int ksize, double* sum, double* sumsq,
+                            void* stream);
 /* Inference (validation pass, examples/larq_experiment.py:133-139, 151-152): BatchNormalization with
  * moving statistics followed by ste_sign is a step function of the integer conv/dense output, so
  * the two fold into one threshold per output channel.  zkb_bn_sign_thresholds writes thr[c] = the

@@ -6,7 +6,8 @@ multi-tile loops, full-wave wgrad splits, 2-stage swap tiles, CTA pairs), and th
 oracle does not fit.  So one train step is run and, layer by layer, the engine's OWN input maps of
 each GEMM are gathered on the GPU and the same entries are recomputed on the CPU -- each GEMM is
 checked in isolation:
-  * binary conv / dense forward: >= 2048 random output pixels x all channels, BIT-EXACT;
+  * binary conv / dense forward: >= 2048 random output pixels x all channels, BIT-EXACT (layers
+    whose 2x2 pooling runs inside the GEMM epilogue: the four pixels of 2048 pooling windows);
   * dgrad: >= 2048 random input pixels x all channels of ds, 1e-5 (Frobenius over the sample);
   * wgrad: 9 taps x 8 input x 32 output channels (a dot product over ALL pixels each), 1e-4: an
     entry sums up to 2.8 M products in f32 (tensor-memory accumulators, then f32 reductions of the
@@ -144,11 +145,14 @@ def test_binary_conv_layer_at_batch_4096(step4096, i):
     g = _gen(100 + i)
     assert torch.equal(P.s.to(torch.int8), P.s8), "bf16 and int8 sign maps differ"
 
-    # ---- forward GEMM: exact integers
-    pix = torch.randint(0, M, (N_PIX,), device="cuda", generator=g)
-    y_ref = S.conv_forward_at(_patches(P.s8, pix, False).cpu().numpy(), w)
-    y_eng = L.y.reshape(-1, L.cp)[pix].cpu().numpy().astype(np.int64)
-    assert np.array_equal(y_eng, y_ref), f"layer {i}: forward integers differ"
+    # ---- forward GEMM: exact integers.  A layer whose pooling runs in the GEMM epilogue stores
+    # only the pooled map: there the reference conv is evaluated at the four pixels of sampled windows.
+    fused_pool = l.pool and eng._pool_in_epilogue(L)
+    if not fused_pool:
+        pix = torch.randint(0, M, (N_PIX,), device="cuda", generator=g)
+        y_ref = S.conv_forward_at(_patches(P.s8, pix, False).cpu().numpy(), w)
+        y_eng = L.y.reshape(-1, L.cp)[pix].cpu().numpy().astype(np.int64)
+        assert np.array_equal(y_eng, y_ref), f"layer {i}: forward integers differ"
 
     # ---- max-pool: value and first-max slot (row-major window order, strict >)
     x_map = L.y
@@ -157,7 +161,11 @@ def test_binary_conv_layer_at_batch_4096(step4096, i):
         pp = torch.randint(0, B * ph * pw, (N_PIX,), device="cuda", generator=g)
         b, r = pp // (ph * pw), pp % (ph * pw)
         py, px = r // pw, r % pw
-        win = torch.stack([L.y[b, 2 * py + (k >> 1), 2 * px + (k & 1)] for k in range(4)]).cpu().numpy().astype(np.int64)
+        if fused_pool:
+            win = np.stack([S.conv_forward_at(_patches(P.s8, (b * oh + 2 * py + (k >> 1)) * ow + 2 * px + (k & 1), False)
+                                              .cpu().numpy(), w) for k in range(4)])
+        else:
+            win = torch.stack([L.y[b, 2 * py + (k >> 1), 2 * px + (k & 1)] for k in range(4)]).cpu().numpy().astype(np.int64)
         assert np.array_equal(L.p.reshape(-1, L.cp)[pp].cpu().numpy(), win.max(0))
         assert np.array_equal(L.arg.reshape(-1, L.cp)[pp].cpu().numpy(), win.argmax(0))   # argmax = first maximum
         x_map = L.p

@@ -62,9 +62,10 @@ def test_train_step_matches_oracle(native_lib, B):
     assert agree.all(), "first-layer sign output differs from the oracle"
     for i in range(1, 9):
         L = eng.L[i]
-        y = L.y.cpu().numpy().astype(np.int64)[..., : L.spec.cout]
-        yr = np.rint(ref.acts[f"y{i}"]).astype(np.int64)
-        assert np.array_equal(y, yr), f"layer {i}: integer conv/dense output differs"
+        if not (L.spec.pool and eng._pool_in_epilogue(L)):     # (fused conv+pool layers never store y)
+            y = L.y.cpu().numpy().astype(np.int64)[..., : L.spec.cout]
+            yr = np.rint(ref.acts[f"y{i}"]).astype(np.int64)
+            assert np.array_equal(y, yr), f"layer {i}: integer conv/dense output differs"
         if L.spec.pool:
             assert np.array_equal(L.p.cpu().numpy().astype(np.int64), np.rint(ref.acts[f"p{i}"]).astype(np.int64))
     assert abs(eng.last_loss() - ref.loss) <= REL_TOL * abs(ref.loss)
@@ -131,6 +132,42 @@ def test_fused_first_layer_backward_equals_separate_kernels(native_lib, B, monke
             assert _rel(a[k], b[k]) < 5e-6, f"{k}: {_rel(a[k], b[k]):.3g}"
         else:       # same kernels on both sides (float atomics: summation order may differ)
             assert _rel(a[k], b[k]) < 1e-6, k
+
+
+@pytest.mark.parametrize("B,shape", [(5, (28, 28, 1)), (37, (28, 28, 1)), (6, (32, 32, 3))])
+def test_pool_in_forward_epilogue_equals_separate_pool_kernel(native_lib, monkeypatch, B, shape):
+    """zkb_bconv2d_fwd_i8_pool against zkb_bconv2d_fwd_i8 + zkb_maxpool2_i16 inside a full step:
+    pooled maps, winning slots, batch statistics and sign maps bit-identical (integers summed
+    exactly), gradients up to float summation order.  MNIST shape: layers 1 (26x26) and 5 (6x6) are
+    fused, layer 3 (13x13) is not; CIFAR shape: layer 1 (30x30) only."""
+    from oracle import binarynet_oracle as O
+    from zookeeper_b200.engine import BinaryNetEngine, binarynet_layers
+
+    params = O.glorot_uniform_params(O.binarynet_layers(shape, 128, 1024, 10), 0)
+    rng = np.random.default_rng(B)
+    img = torch.as_tensor(rng.integers(0, 256, (B,) + shape, dtype=np.uint8)).cuda()
+    lab = torch.as_tensor(rng.integers(0, 10, (B,)).astype(np.int64)).cuda()
+    out = []
+    for fused in ("1", "0"):
+        monkeypatch.setenv("ZKB_FUSE_POOL", fused)
+        eng = BinaryNetEngine(binarynet_layers(shape), shape, B, 10)
+        eng.load_params(params)
+        which = [i for i, L in enumerate(eng.L) if L.spec.kind == "conv" and L.spec.pool and eng._pool_in_epilogue(L)]
+        assert which == (([1, 5] if shape[0] == 28 else [1]) if fused == "1" else [])
+        for _ in range(2):       # twice: the staging slabs and accumulator stages are reused across tiles / steps
+            eng.train_step(img, lab, None, pad_size=shape[0] + 4, seed=3, apply_update=False)
+        torch.cuda.synchronize()
+        pooled = [(L.p.cpu().numpy().copy(), L.arg.cpu().numpy().copy(), L.s8.cpu().numpy().copy())
+                  for L in eng.L if L.spec.kind == "conv" and L.spec.pool]
+        stats = torch.cat([torch.cat([L.mean, L.rstd]) for L in eng.L]).cpu().numpy()
+        out.append((pooled, stats, eng.last_loss(), eng.get_grads()))
+    (pa, sa, la, ga), (pb, sb, lb, gb) = out
+    for k, (a, b) in enumerate(zip(pa, pb)):
+        for x, y, what in zip(a, b, ("pooled map", "slot", "sign map")):
+            assert np.array_equal(x, y), f"pooling layer {k}: {what} differs"
+    assert np.array_equal(sa, sb) and la == lb
+    for k in ga:
+        assert _rel(ga[k], gb[k]) < 1e-5, k
 
 
 def test_bn_backward_sums_from_dgrad_epilogue_equal_the_reduction_kernel(native_lib, monkeypatch):
@@ -266,6 +303,9 @@ def test_cifar_shaped_config_matches_oracle(native_lib):
     assert np.array_equal(eng.x0.cpu().numpy(), x)
     for i in range(1, 9):
         L = eng.L[i]
+        if L.spec.pool and eng._pool_in_epilogue(L):
+            assert np.array_equal(L.p.cpu().numpy().astype(np.int64), np.rint(ref.acts[f"p{i}"]).astype(np.int64)), f"layer {i}"
+            continue
         y = L.y.cpu().numpy().astype(np.int64)[..., : L.spec.cout]
         assert np.array_equal(y, np.rint(ref.acts[f"y{i}"]).astype(np.int64)), f"layer {i}"
     assert abs(eng.last_loss() - ref.loss) <= REL_TOL * abs(ref.loss)

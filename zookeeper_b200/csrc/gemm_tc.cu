@@ -24,7 +24,7 @@
 #include "zkb_ptx.cuh"
 
 #ifndef ZKB_KGEMM_PLAIN_REGS
-#define ZKB_KGEMM_PLAIN_REGS 112   // register cap of the plain kgemm kernel (see kgemm_bf16_kernel)
+#define ZKB_KGEMM_PLAIN_REGS 128   // register cap of the plain kgemm kernel (see kgemm_bf16_kernel)
 #endif
 
 // Timing experiments (scripts/bench_gemm.py: drop the MMA issue or the TMA loads to see which side
@@ -55,7 +55,17 @@ struct KGemmParams {
   int a_im2col;
   int OH, OW, pad, kw_taps, cblocks;   // OH, OW: OUTPUT map; pad: low zero padding along W
   int pad_h, stride;                   // low padding along H; traversal stride (1, or 2 for 'same' stride-2 convs)
-  int out_kind;  // 0: f32, 1: int16 (exact integers expected)
+  int out_kind;  // 0: f32, 1: int16 (exact integers expected), 2: int8 sign, 3: 2x2 max-pooled int16
+  // out_kind 3 (swap mode, int8 operands): a tile is pool_rp whole row PAIRS of the [NB,H,W] output
+  // map (H, W even, so row pairs are contiguous across images); the epilogue stages D^T as
+  // [pixel][channel] int16 in shared memory, takes the 2x2 / stride-2 maximum with the first-max
+  // tie rule of maxpool2_i16_kernel and writes the pooled map (out, row stride ldo), the winning
+  // slot (pool_arg) and the BatchNorm statistics of the pooled map (st_sum / st_sumsq): the
+  // full-resolution map never reaches memory.
+  int pool_w;            // W of the conv output map
+  int pool_rp;           // row pairs per tile
+  long long pool_rows;   // NB * H / 2 row pairs in total
+  uint8_t* pool_arg;
   int is_i8;     // operands are signed int8 (+-1 / 0), accumulators int32 (kind::i8)
   int dbg;       // ZKB_MEASURE builds only: 1 = no MMA issue, 2 = no TMA loads
   // Fused first-layer backward (swap mode, 128 output channels, one input channel, 3x3): the
@@ -216,7 +226,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
     tma_prefetch_desc(&tmA0);
     if (p.a_terms == 2) tma_prefetch_desc(&tmA1);
     tma_prefetch_desc(&tmB);
-    if (!kFirstLayer) tma_prefetch_desc(&tmOut);
+    if (!kFirstLayer && p.out_kind != 3) tma_prefetch_desc(&tmOut);
   }
   if (warp == 1) tmem_alloc_512(smem_u32(&ctl->tmem_base));
   tc_fence_before();
@@ -450,6 +460,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
     if (p.bn_fused) { bn_mu = p.bn_mean[bn_ch]; bn_rs = p.bn_rstd[bn_ch]; bn_be = p.bn_beta[bn_ch]; }
     // fused forward statistics: 2 units of 64 columns per warp and tile, a column pair per lane
     long long st_s[2][2] = {{0, 0}, {0, 0}}, st_q[2][2] = {{0, 0}, {0, 0}};
+    long long pool_s = 0, pool_q = 0;      // fused pooling: statistics of this thread's channel
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -465,6 +476,59 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
         // D^T: TMEM lane = output channel, column = pixel.  A unit is 32 pixels x this warp's 32
         // channels, transposed through the staging box (row = pixel, 4 bytes per lane).
         const int ch0 = tn * 128 + q * 32;
+        if (!kFirstLayer && p.out_kind == 3) {
+          // ---- fused 2x2 max-pool.  Slab of this lane quarter: [block_n pixels][32 channels] int16.
+          const uint32_t slab = smem_u32(smem + static_cast<size_t>(p.num_stages) * p.stage_bytes + 1024) +
+                                static_cast<uint32_t>(q) * static_cast<uint32_t>(p.block_n) * 64u;
+          const int n_units = (p.block_n + 31) >> 5;
+          for (int u = half; u < n_units; u += 2) {
+            if (tm * p.block_n + u * 32 >= p.M) break;
+            uint32_t r[32];
+            tmem_ld_32x32(tbase + static_cast<uint32_t>(u * 32), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (u * 32 + j < p.block_n)
+                asm volatile("st.shared.b16 [%0], %1;" ::"r"(slab + static_cast<uint32_t>(u * 32 + j) * 64u +
+                                                             static_cast<uint32_t>(lane) * 2u),
+                             "h"(static_cast<short>(static_cast<int>(r[j])))
+                             : "memory");
+            }
+          }
+          tc_fence_before();
+          mbar_arrive(smem_u32(&ctl->tempty[as]));              // the MMAs of the next tile may start
+          named_bar_sync(1u + static_cast<uint32_t>(q), 64u);   // both warps of the quarter have staged
+          const int W2 = p.pool_w, PW = W2 >> 1;
+          const int n_pp = p.pool_rp * PW;                      // pooled pixels of a tile
+          int s_acc = 0, q_acc = 0;
+          for (int pp = half; pp < n_pp; pp += 2) {
+            const int u2 = pp / PW, j2 = pp - u2 * PW;
+            const long long grp = static_cast<long long>(tm) * p.pool_rp + u2;   // global row pair
+            if (grp >= p.pool_rows) break;
+            const uint32_t a = slab + static_cast<uint32_t>(u2 * 2 * W2 + 2 * j2) * 64u + static_cast<uint32_t>(lane) * 2u;
+            short v00, v01, v10, v11;
+            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v00) : "r"(a));
+            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v01) : "r"(a + 64u));
+            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v10) : "r"(a + static_cast<uint32_t>(W2) * 64u));
+            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v11) : "r"(a + static_cast<uint32_t>(W2) * 64u + 64u));
+            int best = v00;
+            uint8_t k = 0;
+            if (v01 > best) { best = v01; k = 1; }
+            if (v10 > best) { best = v10; k = 2; }
+            if (v11 > best) { best = v11; k = 3; }
+            const long long o = (grp * PW + j2) * p.ldo + ch0 + lane;
+            static_cast<int16_t*>(p.out)[o] = static_cast<int16_t>(best);
+            p.pool_arg[o] = k;
+            s_acc += best;
+            q_acc += best * best;      // <= 30 pooled pixels x 4608^2 per tile: fits int32
+          }
+          pool_s += s_acc;
+          pool_q += q_acc;
+          named_bar_sync(1u + static_cast<uint32_t>(q), 64u);   // slab free for the next tile
+          as ^= 1;
+          if (as == 0) aphase ^= 1u;
+          continue;
+        }
         if constexpr (kFirstLayer) {
 #pragma unroll
           for (int i = 0; i < 11; ++i) l0_f[i] = 0.f;
@@ -656,6 +720,11 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           }
         }
       }
+    }
+    if (!kFirstLayer && p.out_kind == 3) {     // this CTA's tn is fixed (grid is a multiple of tiles_n)
+      const int ch = (static_cast<int>(blockIdx.x) % p.tiles_n) * 128 + q * 32 + lane;
+      atomicAdd(p.st_sum + ch, static_cast<double>(pool_s));
+      atomicAdd(p.st_sumsq + ch, static_cast<double>(pool_q));
     }
     if constexpr (kFirstLayer) {
 #pragma unroll
@@ -1277,6 +1346,22 @@ struct StatsFuse {   // see KGemmParams::st_fused
   double *sum, *sumsq;
 };
 
+struct PoolFuse {    // see KGemmParams::out_kind == 3
+  uint8_t* arg;
+};
+
+// Row pairs per tile of the fused-pool forward: the most that fit 256 MMA columns with a pixel count
+// the MMA accepts (a multiple of 16) and whose last 32-column accumulator read stays inside the
+// 256-column stage.  0: this map cannot be tiled that way (odd sizes, rows wider than 128 pixels).
+static int pool_row_pairs(int H, int W) {
+  if (H <= 0 || W <= 0 || (H & 1) || (W & 1) || 2 * W > 256) return 0;
+  for (int rp = 256 / (2 * W); rp >= 1; --rp) {
+    const int px = rp * 2 * W;
+    if (px % 16 == 0 && ((px + 31) / 32) * 32 <= 256) return rp;
+  }
+  return 0;
+}
+
 extern "C" int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum,
                             double* sumsq, void* stream);
 extern "C" int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
@@ -1288,7 +1373,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
                         int H, int W, int C, int ksize, int pad, cudaStream_t stream,
                         int elem_bytes = 2, const FirstLayerFuse* l0 = nullptr,
                         const BnBackwardFuse* bn = nullptr, const StatsFuse* st = nullptr,
-                        const int* sign_thr = nullptr, int stride = 1) {
+                        const int* sign_thr = nullptr, int stride = 1, const PoolFuse* pool = nullptr) {
   const int kelems = 128 / elem_bytes;  // K elements per 128-byte smem row
   const CUtensorMapDataType dt =
       elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -1299,6 +1384,10 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   ZKB_REQUIRE(K % kelems == 0, "kgemm: K=%d must be a multiple of %d", K, kelems);
   ZKB_REQUIRE(M < (1ll << 31) - 256, "kgemm: M=%lld too large", M);
   ZKB_REQUIRE(out_kind >= 0 && out_kind <= 2, "kgemm: out_kind must be 0 (f32), 1 (i16) or 2 (i8 sign)");
+  ZKB_REQUIRE(!pool || (out_kind == 1 && elem_bytes == 1 && im2col && stride == 1 && st && pool->arg && N % 128 == 0 &&
+                        ldo == N && pool_row_pairs(H, W) > 0),
+              "kgemm: the fused max-pool needs the int8 conv forward with statistics, Cout %% 128 == 0 and an even map "
+              "whose row pairs tile 256 columns (H=%d W=%d)", H, W);
   ZKB_REQUIRE(out_kind != 2 || (sign_thr && elem_bytes == 1 && (reinterpret_cast<uintptr_t>(sign_thr) & 15) == 0),
               "kgemm: the sign output needs int8 operands and 16-byte aligned thresholds");
   ZKB_REQUIRE(ldo >= N, "kgemm: ldo=%lld < N=%d", ldo, N);
@@ -1331,11 +1420,20 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     p.l0_x = l0->x; p.l0_wq = l0->wq; p.l0_mean = l0->mean; p.l0_rstd = l0->rstd; p.l0_beta = l0->beta;
     p.l0_acc = l0->acc; p.l0_H = l0->H; p.l0_W = l0->W;
   }
+  if (pool) p.swap = 1;
   if (p.swap) {
     // 256 pixels per tile as two 128-pixel boxes (192 pixels as three 64-pixel boxes, which fits
     // three two-term stages instead of two, measured no faster in r1 and was removed)
     p.swap_boxes = 2;
     p.swap_box_px = 128;
+    if (pool) {      // one box of pool_rp whole row pairs
+      p.pool_rp = pool_row_pairs(H, W);
+      p.pool_w = W;
+      p.pool_rows = static_cast<long long>(NB) * (H / 2);
+      p.pool_arg = pool->arg;
+      p.swap_boxes = 1;
+      p.swap_box_px = p.pool_rp * 2 * W;
+    }
     p.block_n = p.swap_boxes * p.swap_box_px;
     p.stage_bytes = kATileBytes + p.a_terms * p.block_n * 128;
   }
@@ -1366,13 +1464,19 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   if (st) {
     ZKB_REQUIRE(out_kind == 1 && ldo == N && st->sum && st->sumsq,
                 "kgemm: fused statistics need a dense int16 output and both accumulators");
-    if (!p.swap && !use_pairs) {
+    if (pool) {          // statistics of the POOLED map, accumulated by the pooling epilogue
+      p.st_sum = st->sum;
+      p.st_sumsq = st->sumsq;
+    } else if (!p.swap && !use_pairs) {
       p.st_fused = 1;
       p.st_sum = st->sum;
       p.st_sumsq = st->sumsq;
     }
   }
-  p.num_stages = (kSmemBudget - kEpiStagingBytes) / p.stage_bytes;
+  // epilogue staging: eight 4 KB TMA-store boxes, or the four [pixels][32 channels] int16 slabs of
+  // the pooling epilogue
+  const int epi_bytes = pool ? 4 * p.block_n * 64 : kEpiStagingBytes;
+  p.num_stages = (kSmemBudget - epi_bytes) / p.stage_bytes;
   if (p.num_stages > kMaxStages) p.num_stages = kMaxStages;
   ZKB_REQUIRE(p.num_stages >= 2, "kgemm: tile does not fit in shared memory");
   p.tiles_m = static_cast<int>((M + 127) / 128);
@@ -1381,6 +1485,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     p.tiles_m = static_cast<int>((M + p.block_n - 1) / p.block_n);
     p.tiles_n = N / 128;
   }
+  if (pool) out_kind = 3;
   if (use_pairs) {
     p.tiles_m = static_cast<int>((M + 255) / 256);
     p.tiles_n = N / 256;
@@ -1433,8 +1538,8 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
 
   // output through TMA stores: boxes of 128 bytes x 32 rows
   CUtensorMap tmOut{};
-  if (l0)
-    rc = ZKB_OK;            // nothing is stored: the epilogue reduces D in registers
+  if (l0 || pool)
+    rc = ZKB_OK;            // nothing goes through TMA stores: the epilogue reduces / pools D itself
   else if (out_kind == 0)
     rc = zkb_tmap_tiled_2d(&tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, N, M,
                            static_cast<uint64_t>(ldo) * 4, 32, 32);
@@ -1450,7 +1555,7 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
   if (rc) return rc;
 
   // layout: [stages][1 KB: barriers + TMEM slot][8 x 4 KB staging boxes] (+1 KB alignment slack)
-  const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + 1024 + kEpiStagingBytes + 1024;
+  const size_t smem = static_cast<size_t>(p.num_stages) * p.stage_bytes + 1024 + epi_bytes + 1024;
   ZKB_CUDA(cudaFuncSetAttribute(kgemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 227 * 1024));
   ZKB_CUDA(cudaFuncSetAttribute(kgemm_first_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1469,13 +1574,13 @@ static int launch_kgemm(const void* A_hi, const void* A_lo, const void* Bmat, vo
     return ZKB_OK;
   }
   int grid = tiles < sms ? tiles : sms;
-  if ((p.bn_fused || p.st_fused) && grid > p.tiles_n) grid -= grid % p.tiles_n;
+  if ((p.bn_fused || p.st_fused || pool) && grid > p.tiles_n) grid -= grid % p.tiles_n;
   if (p.l0_fused)
     kgemm_first_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
   else
     kgemm_bf16_kernel<<<grid, 320, smem, stream>>>(tmA0, tmA1, tmB, tmOut, p);
   ZKB_LAUNCH_CHECK("kgemm_bf16_kernel");
-  if (st && !p.st_fused) return zkb_bn_stats(out, 1, M, N, st->sum, st->sumsq, stream);
+  if (st && !p.st_fused && !pool) return zkb_bn_stats(out, 1, M, N, st->sum, st->sumsq, stream);
   if (bn && !p.bn_fused)   // tile shapes without the fused epilogue: the stand-alone reduction
     return zkb_bn_bwd_reduce(static_cast<const float*>(out), bn->x, 1, M, N, bn->mean, bn->rstd,
                              bn->beta, 1, bn->sum_da, bn->sum_dax, stream);
@@ -1614,6 +1719,22 @@ ZKB_API int zkb_bconv2d_fwd_i8(const void* act_i8, const void* wq_oc_k_i8, void*
   return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout,
                       static_cast<long long>(NB) * H * W, Cout, ksize * ksize * Cin, 1, NB, H, W,
                       Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1);
+}
+
+ZKB_API int zkb_bconv2d_fwd_i8_pool_ok(int H, int W, int Cout) {
+  return (pool_row_pairs(H, W) > 0 && Cout > 0 && Cout % 128 == 0) ? 1 : 0;
+}
+
+ZKB_API int zkb_bconv2d_fwd_i8_pool(const void* act_i8, const void* wq_oc_k_i8, void* p_i16, uint8_t* arg_u8,
+                                    int NB, int H, int W, int Cin, int Cout, int ksize, double* sum,
+                                    double* sumsq, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_fwd_i8_pool: ksize must be odd");
+  ZKB_REQUIRE(p_i16 && arg_u8 && sum && sumsq, "bconv2d_fwd_i8_pool: null output");
+  StatsFuse st{sum, sumsq};
+  PoolFuse pool{arg_u8};
+  return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, p_i16, 1, Cout, static_cast<long long>(NB) * H * W, Cout,
+                      ksize * ksize * Cin, 1, NB, H, W, Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream),
+                      1, nullptr, nullptr, &st, nullptr, 1, &pool);
 }
 
 ZKB_API int zkb_bconv2d_fwd_i8_s2(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H,

@@ -161,6 +161,9 @@ class BinaryNetEngine:
         self.fuse_bn_backward_sums = os.environ.get("ZKB_FUSE_BN_BWD", "1") != "0"
         # BatchNorm batch statistics inside the forward GEMM epilogue (layers that do not pool)
         self.fuse_forward_stats = os.environ.get("ZKB_FUSE_FWD_STATS", "1") != "0"
+        # 2x2 max-pool (+ statistics) inside the forward GEMM epilogue of pooling layers whose map
+        # tiles into whole row pairs (ZKB_FUSE_POOL=0: separate zkb_maxpool2_i16)
+        self.fuse_pool = self.forward_int8 and os.environ.get("ZKB_FUSE_POOL", "1") != "0"
         # inference: BatchNorm + sign as integer thresholds inside the GEMM epilogue
         self.fold_eval = self.forward_int8 and os.environ.get("ZKB_FOLD_EVAL", "1") != "0"
         self.watch = None      # None | True | set of entry-point names to time with CUDA events
@@ -512,6 +515,13 @@ class BinaryNetEngine:
                 else:
                     ih, iw = L.in_hw
                     fused_stats = self.forward_int8 and self.fuse_forward_stats and training and not l.pool
+                    if l.pool and training and self._pool_in_epilogue(L):
+                        # conv + pool + statistics in one launch; the full-resolution map is never stored
+                        self._call("zkb_bconv2d_fwd_i8_pool", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.p), zn.ptr(L.arg),
+                                   B, ih, iw, l.cin, l.cout, l.ksize, zn.ptr(L.sum), zn.ptr(L.sumsq))
+                        self._bn_forward(L, L.p, True, L.bn_rows, True, training)
+                        prev = L
+                        continue
                     if fused_stats:
                         self._call("zkb_bconv2d_fwd_i8_stats", zn.ptr(prev.s8), zn.ptr(L.w_fwd8), zn.ptr(L.y), B, ih, iw,
                                    l.cin, l.cout, l.ksize, zn.ptr(L.sum), zn.ptr(L.sumsq))
@@ -561,6 +571,15 @@ class BinaryNetEngine:
             mean, rstd = L.mm, L.eval_rstd
         self._call("zkb_conv_first_bn_sign", zn.ptr(self.x0), zn.ptr(L.wq), *geom, zn.ptr(mean), zn.ptr(rstd),
                    zn.ptr(L.beta), zn.ptr(L.s), zn.ptr(L.s8))
+
+    def _pool_in_epilogue(self, L) -> bool:
+        """zkb_bconv2d_fwd_i8_pool covers this pooling layer (even map whose row pairs tile 256 MMA
+        columns, channel count a multiple of 128)."""
+        if not self.fuse_pool or L.spec.kind != "conv" or not L.spec.pool or L.cp != L.spec.cout:
+            return False
+        oh, ow = L.out_hw
+        lib = zn.load()
+        return bool(lib.zkb_bconv2d_fwd_i8_pool_ok(int(oh), int(ow), int(L.spec.cout)))
 
     def _can_fuse_first_backward(self) -> bool:
         """zkb_bconv2d_dgrad_first_bwd is built for: 3x3 'valid' conv of one input channel into 128

@@ -83,6 +83,7 @@ SIGNATURES = {
     "zkb_dense_f32_bwd": [P, P, P, I, P, P, P, I, I, I, P],
     "zkb_maxpool3s2_f32_fwd": [P, I, I, I, I, P, P, P],
     "zkb_maxpool3s2_f32_bwd": [P, P, I, I, I, I, P, P],
+    "zkb_bconv2d_fwd_i8_pool": [P, P, P, P, I, I, I, I, I, I, P, P, P],
     "zkb_bconv2d_fwd_i8_s2": [P, P, P, I, I, I, I, I, I, P],
     "zkb_bconv2d_wgrad_s2": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_dilate2_hi_lo": [P, P, I, I, I, I, I, P, P, P],
@@ -107,6 +108,9 @@ def load() -> ctypes.CDLL:
     lib.zkb_last_error_string.restype = ctypes.c_char_p
     lib.zkb_last_error_string.argtypes = []
     lib.zkb_abi_version.restype = c_int
+    if hasattr(lib, "zkb_bconv2d_fwd_i8_pool_ok"):
+        lib.zkb_bconv2d_fwd_i8_pool_ok.restype = c_int
+        lib.zkb_bconv2d_fwd_i8_pool_ok.argtypes = [c_int, c_int, c_int]
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name, None)
         if fn is None:
