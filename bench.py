@@ -209,7 +209,7 @@ def algorithmic_work(eng, name, tag):
         M, N, K = B, l.cout, l.cin
     # (zkb_bconv2d_dgrad_first_bwd: the tensor-pipe figure counts the GEMM only; the CUDA-core work
     # of its fused first-layer epilogue is not added)
-    if name in ("zkb_bconv2d_dgrad_first_bwd", "zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
+    if name in ("zkb_bconv2d_dgrad_first_bwd", "zkb_bconv2d_fwd_i8_pool", "zkb_bconv2d_fwd", "zkb_bdense_fwd", "zkb_bconv2d_fwd_i8", "zkb_bdense_fwd_i8", "zkb_bconv2d_dgrad", "zkb_bdense_dgrad",
                 "zkb_bconv2d_wgrad", "zkb_bdense_wgrad", "zkb_bconv2d_fwd_i8_stats", "zkb_bdense_fwd_i8_stats",
                 "zkb_bconv2d_dgrad_bn"):
         return ("flop", 2.0 * M * N * K)  # split terms are implementation overhead, not counted
@@ -548,6 +548,8 @@ def main():
             if "_fwd_i8" not in name:
                 continue
             w = algorithmic_work(eng, name, tag)
+            if not w:
+                continue
             ms = sum(v) / len(v)
             tot_ops += w[1]
             tot_ms += ms

@@ -24,7 +24,7 @@
 #include "zkb_ptx.cuh"
 
 #ifndef ZKB_KGEMM_PLAIN_REGS
-#define ZKB_KGEMM_PLAIN_REGS 128   // register cap of the plain kgemm kernel (see kgemm_bf16_kernel)
+#define ZKB_KGEMM_PLAIN_REGS 144   // register cap of the plain kgemm kernel (see kgemm_bf16_kernel)
 #endif
 
 // Timing experiments (scripts/bench_gemm.py: drop the MMA issue or the TMA loads to see which side
@@ -197,8 +197,9 @@ __device__ __forceinline__ void bn_sums_from_box(const KGemmParams& p, uint32_t 
 }
 
 // kFirstLayer: the instantiation whose swap epilogue is the fused first-layer backward.  It needs
-// 168 registers per thread; the plain instantiation stays small enough that HBM-bound kernels of
-// another stream can share an SM with a resident GEMM CTA.
+// 168 registers per thread; the plain instantiation is capped at 144 (no spills; 320 x 144 leaves
+// 19 K registers of the SM free, enough for a 256-thread elementwise block of the other stream to
+// share the SM with a resident GEMM CTA).
 template <bool kFirstLayer>
 __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtensorMap& tmA1,
                                            const CUtensorMap& tmB, const CUtensorMap& tmOut,
@@ -460,7 +461,7 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
     if (p.bn_fused) { bn_mu = p.bn_mean[bn_ch]; bn_rs = p.bn_rstd[bn_ch]; bn_be = p.bn_beta[bn_ch]; }
     // fused forward statistics: 2 units of 64 columns per warp and tile, a column pair per lane
     long long st_s[2][2] = {{0, 0}, {0, 0}}, st_q[2][2] = {{0, 0}, {0, 0}};
-    long long pool_s = 0, pool_q = 0;      // fused pooling: statistics of this thread's channel
+    long long pool_s[4] = {0, 0, 0, 0}, pool_q[4] = {0, 0, 0, 0};   // fused pooling: statistics of this lane's 4 channels
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -498,32 +499,50 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
           tc_fence_before();
           mbar_arrive(smem_u32(&ctl->tempty[as]));              // the MMAs of the next tile may start
           named_bar_sync(1u + static_cast<uint32_t>(q), 64u);   // both warps of the quarter have staged
+          // Pooling: a lane owns 4 channels (8 bytes of a slab row) of one of the 4 pooled pixels a
+          // warp takes per iteration; the two warps of the quarter interleave groups of 4 pixels.
+          // Maximum and first-max slot are computed on int16 pairs with the SIMD video instructions.
           const int W2 = p.pool_w, PW = W2 >> 1;
           const int n_pp = p.pool_rp * PW;                      // pooled pixels of a tile
-          int s_acc = 0, q_acc = 0;
-          for (int pp = half; pp < n_pp; pp += 2) {
+          const int cg = lane & 7, sub = lane >> 3;
+          int s_acc[4] = {0, 0, 0, 0}, q_acc[4] = {0, 0, 0, 0};
+          for (int pp0 = half * 4; pp0 < n_pp; pp0 += 8) {
+            const int pp = pp0 + sub;
             const int u2 = pp / PW, j2 = pp - u2 * PW;
             const long long grp = static_cast<long long>(tm) * p.pool_rp + u2;   // global row pair
-            if (grp >= p.pool_rows) break;
-            const uint32_t a = slab + static_cast<uint32_t>(u2 * 2 * W2 + 2 * j2) * 64u + static_cast<uint32_t>(lane) * 2u;
-            short v00, v01, v10, v11;
-            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v00) : "r"(a));
-            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v01) : "r"(a + 64u));
-            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v10) : "r"(a + static_cast<uint32_t>(W2) * 64u));
-            asm volatile("ld.shared.b16 %0, [%1];" : "=h"(v11) : "r"(a + static_cast<uint32_t>(W2) * 64u + 64u));
-            int best = v00;
-            uint8_t k = 0;
-            if (v01 > best) { best = v01; k = 1; }
-            if (v10 > best) { best = v10; k = 2; }
-            if (v11 > best) { best = v11; k = 3; }
-            const long long o = (grp * PW + j2) * p.ldo + ch0 + lane;
-            static_cast<int16_t*>(p.out)[o] = static_cast<int16_t>(best);
-            p.pool_arg[o] = k;
-            s_acc += best;
-            q_acc += best * best;      // <= 30 pooled pixels x 4608^2 per tile: fits int32
+            if (pp >= n_pp || grp >= p.pool_rows) continue;
+            const uint32_t a = slab + static_cast<uint32_t>(u2 * 2 * W2 + 2 * j2) * 64u + static_cast<uint32_t>(cg) * 8u;
+            uint32_t v[4][2];
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v[0][0]), "=r"(v[0][1]) : "r"(a));
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v[1][0]), "=r"(v[1][1]) : "r"(a + 64u));
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v[2][0]), "=r"(v[2][1]) : "r"(a + static_cast<uint32_t>(W2) * 64u));
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v[3][0]), "=r"(v[3][1]) : "r"(a + static_cast<uint32_t>(W2) * 64u + 64u));
+            uint32_t best[2], slot[2];
+#pragma unroll
+            for (int w2 = 0; w2 < 2; ++w2) {
+              uint32_t bv = v[0][w2], kv = 0u;
+#pragma unroll
+              for (int k = 1; k < 4; ++k) {
+                const uint32_t m = __vcmpgts2(v[k][w2], bv);      // 0xFFFF where window element k is strictly greater
+                bv = (v[k][w2] & m) | (bv & ~m);
+                kv = ((static_cast<uint32_t>(k) * 0x00010001u) & m) | (kv & ~m);
+              }
+              best[w2] = bv;
+              slot[w2] = kv;
+            }
+            const long long o = (grp * PW + j2) * p.ldo + ch0 + cg * 4;
+            *reinterpret_cast<uint2*>(static_cast<int16_t*>(p.out) + o) = make_uint2(best[0], best[1]);
+            *reinterpret_cast<uint32_t*>(p.pool_arg + o) = (slot[0] & 0xFFu) | ((slot[0] >> 16) << 8) |
+                                                           ((slot[1] & 0xFFu) << 16) | ((slot[1] >> 16) << 24);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int val = static_cast<int16_t>((best[c >> 1] >> (16 * (c & 1))) & 0xFFFFu);
+              s_acc[c] += val;
+              q_acc[c] += val * val;    // <= 8 pooled pixels x 4608^2 per lane and tile: fits int32
+            }
           }
-          pool_s += s_acc;
-          pool_q += q_acc;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) { pool_s[c] += s_acc[c]; pool_q[c] += q_acc[c]; }
           named_bar_sync(1u + static_cast<uint32_t>(q), 64u);   // slab free for the next tile
           as ^= 1;
           if (as == 0) aphase ^= 1u;
@@ -722,9 +741,18 @@ __device__ __forceinline__ void kgemm_body(const CUtensorMap& tmA0, const CUtens
       }
     }
     if (!kFirstLayer && p.out_kind == 3) {     // this CTA's tn is fixed (grid is a multiple of tiles_n)
-      const int ch = (static_cast<int>(blockIdx.x) % p.tiles_n) * 128 + q * 32 + lane;
-      atomicAdd(p.st_sum + ch, static_cast<double>(pool_s));
-      atomicAdd(p.st_sumsq + ch, static_cast<double>(pool_q));
+      // the four pixel lanes (lane >> 3) of a channel group are combined by shuffles first
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        long long a = pool_s[c], b2 = pool_q[c];
+        a += __shfl_xor_sync(0xffffffffu, a, 8);  b2 += __shfl_xor_sync(0xffffffffu, b2, 8);
+        a += __shfl_xor_sync(0xffffffffu, a, 16); b2 += __shfl_xor_sync(0xffffffffu, b2, 16);
+        if (lane < 8) {
+          const int ch = (static_cast<int>(blockIdx.x) % p.tiles_n) * 128 + q * 32 + lane * 4 + c;
+          atomicAdd(p.st_sum + ch, static_cast<double>(a));
+          atomicAdd(p.st_sumsq + ch, static_cast<double>(b2));
+        }
+      }
     }
     if constexpr (kFirstLayer) {
 #pragma unroll
