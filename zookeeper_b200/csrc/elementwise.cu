@@ -1526,6 +1526,55 @@ struct FirstConv {
         for (int j = 0; j < (KS - 1) * CIN; ++j) win[kh][j] = win[kh][j + CIN];
     }
   };
+  // K > 9 (the 3-channel first layer): sign(W) comes from shared memory, 27 float4 loads per pixel
+  // and thread against 108 FMAs -- shared-memory bandwidth, not arithmetic, bounded those kernels
+  // (ncu, r2: 24 % of the CIFAR-shaped step).  NPX consecutive output pixels of a row (4; 2 in the
+  // weight-gradient kernel, whose 108 accumulators leave no room for more) share their input window
+  // and every weight vector that is fetched: 1/NPX of the shared-memory traffic per pixel, the same FMA order per pixel as `dot` (k ascending), hence
+  // the same floats.
+  template <int NPX>
+  struct Group {
+    float win[KS][(KS - 1 + NPX) * CIN];
+    __device__ __forceinline__ void load(const float* __restrict__ row_base, int W, int ow0) {
+      // columns ow0 .. ow0 + KS + NPX - 2 of the KS input rows; columns past the image edge are
+      // clamped (they only feed output pixels past the row end, which the callers skip)
+#pragma unroll
+      for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+        for (int cc = 0; cc < KS - 1 + NPX; ++cc) {
+          int col = ow0 + cc;
+          col = col < W ? col : W - 1;
+#pragma unroll
+          for (int ci = 0; ci < CIN; ++ci) win[kh][cc * CIN + ci] = __ldg(row_base + (kh * W + col) * CIN + ci);
+        }
+    }
+    __device__ __forceinline__ void dot4(const float* s_w, int Cout, int c4, float (&y)[NPX][4]) const {
+#pragma unroll
+      for (int q = 0; q < NPX; ++q) y[q][0] = y[q][1] = y[q][2] = y[q][3] = 0.f;
+#pragma unroll
+      for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+        for (int r = 0; r < KS * CIN; ++r) {
+          const float4 w = *reinterpret_cast<const float4*>(s_w + (kh * KS * CIN + r) * Cout + c4);
+#pragma unroll
+          for (int q = 0; q < NPX; ++q) {
+            const float x = win[kh][q * CIN + r];
+            y[q][0] = fmaf(x, w.x, y[q][0]);
+            y[q][1] = fmaf(x, w.y, y[q][1]);
+            y[q][2] = fmaf(x, w.z, y[q][2]);
+            y[q][3] = fmaf(x, w.w, y[q][3]);
+          }
+        }
+    }
+    // tap k = (kh, kw, ci) of pixel q of the quad
+    __device__ __forceinline__ float tap(int q, int k) const { return win[k / (KS * CIN)][q * CIN + k % (KS * CIN)]; }
+  };
+  __device__ static __forceinline__ const float* row_base(const float* __restrict__ x, unsigned row, int H, int W) {
+    const unsigned OH = H - KS + 1;
+    const unsigned b = row / OH;
+    const unsigned oh = row - b * OH;
+    return x + static_cast<size_t>(b * H + oh) * W * CIN;
+  }
   __device__ static __forceinline__ void dot(const float (&xv)[K], const float* s_w,
                                              const float4 (&wr)[KR], int Cout, int c4, float (&y)[4]) {
     y[0] = y[1] = y[2] = y[3] = 0.f;
@@ -1599,10 +1648,30 @@ conv_first_bn_stats_kernel(const float* __restrict__ x, const float* __restrict_
   const unsigned OWr = W - KS + 1;
   const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
   for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   if constexpr (!FC::kRegW) {
+    const float* rb = FC::row_base(x, row, H, W);
+    for (unsigned ow0 = 0; ow0 < OWr; ow0 += 4) {
+      typename FC::template Group<4> quad;
+      quad.load(rb, W, ow0);
+      float y4[4][4];
+      quad.dot4(s_w, Cout, cl * 4, y4);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (ow0 + q >= OWr) break;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { f0[j] += y4[q][j]; f1[j] = fmaf(y4[q][j], y4[q][j], f1[j]); }
+        if (++n == 32) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
+          n = 0;
+        }
+      }
+    }
+    continue;
+   }
    typename FC::Row walk;
    walk.begin(x, row, H, W);
    for (unsigned owi = 0; owi < OWr; ++owi) {
-    const long long pix = static_cast<long long>(row) * OWr + owi;
     float xv[FC::K], y[4];
     walk.step(owi, xv);
     FC::dot(xv, s_w, wr, Cout, cl * 4, y);
@@ -1696,12 +1765,40 @@ __device__ __forceinline__ void conv_first_bn_sign_body(const float* __restrict_
     return;
   }
   for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
-   typename FC::Row walk;
-   walk.begin(x, row, H, W);
    // output pointers of this thread's 4 channels, advanced by one pixel (Cout elements) per step
    const size_t o0 = static_cast<size_t>(row) * OWr * Cout + cl * 4;
    uint16_t* so = s_out ? s_out + o0 : nullptr;
    int8_t* so8 = s8_out ? s8_out + o0 : nullptr;
+   if constexpr (!FC::kRegW) {
+    const float* rb = FC::row_base(x, row, H, W);
+    for (unsigned ow0 = 0; ow0 < OWr; ow0 += 4) {
+      typename FC::template Group<4> quad;
+      quad.load(rb, W, ow0);
+      float y4[4][4];
+      quad.dot4(s_w, Cout, cl * 4, y4);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (ow0 + q >= OWr) break;
+        uint32_t neg = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) neg |= (((y4[q][j] - mu[j]) * rs[j] + be[j] >= 0.0f) ? 0u : 1u) << j;
+        if (so) {
+          *reinterpret_cast<uint2*>(so) =
+              make_uint2(0x3F803F80u | ((neg & 1u) << 15) | ((neg & 2u) << 30),
+                         0x3F803F80u | ((neg & 4u) << 13) | ((neg & 8u) << 28));
+          so += Cout;
+        }
+        if (so8) {
+          const uint32_t spread = (neg * 0x00204081u) & 0x01010101u;
+          *reinterpret_cast<uint32_t*>(so8) = spread * 0xFEu + 0x01010101u;
+          so8 += Cout;
+        }
+      }
+    }
+    continue;
+   }
+   typename FC::Row walk;
+   walk.begin(x, row, H, W);
    for (unsigned owi = 0; owi < OWr; ++owi) {
     float xv[FC::K], y[4];
     walk.step(owi, xv);
@@ -1765,6 +1862,38 @@ conv_first_bwd_reduce_kernel(const float* __restrict__ x, const float* __restric
   const unsigned OWr = W - KS + 1;
   const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
   for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   if constexpr (!FC::kRegW) {
+    const float* rb = FC::row_base(x, row, H, W);
+    for (unsigned ow0 = 0; ow0 < OWr; ow0 += 4) {
+      typename FC::template Group<4> quad;
+      quad.load(rb, W, ow0);
+      float gq[4][4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const unsigned ow = ow0 + q < OWr ? ow0 + q : OWr - 1;
+        load4(g + (static_cast<long long>(row) * OWr + ow) * Cout + cl * 4, gq[q]);
+      }
+      float y4[4][4];
+      quad.dot4(s_w, Cout, cl * 4, y4);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (ow0 + q >= OWr) break;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float xh = (y4[q][j] - mu[j]) * rs[j];
+          const float da = (fabsf(xh + be[j]) > 1.0f) ? 0.f : gq[q][j];
+          f0[j] += da;
+          f1[j] = fmaf(da, xh, f1[j]);
+        }
+        if (++n == 64) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { a0[j] += f0[j]; a1[j] += f1[j]; f0[j] = f1[j] = 0.f; }
+          n = 0;
+        }
+      }
+    }
+    continue;
+   }
    typename FC::Row walk;
    walk.begin(x, row, H, W);
    for (unsigned owi = 0; owi < OWr; ++owi) {
@@ -1821,6 +1950,39 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
   const unsigned OWr = W - KS + 1;
   const unsigned n_rows = static_cast<unsigned>(pixels / OWr);
   for (unsigned row = blockIdx.x * lanes + rl; row < n_rows; row += gridDim.x * lanes) {
+   if constexpr (!FC::kRegW) {
+    const float* rb = FC::row_base(x, row, H, W);
+    for (unsigned ow0 = 0; ow0 < OWr; ow0 += 2) {
+      typename FC::template Group<2> quad;
+      quad.load(rb, W, ow0);
+      float gq[2][4];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const unsigned ow = ow0 + q < OWr ? ow0 + q : OWr - 1;
+        load4(g + (static_cast<long long>(row) * OWr + ow) * Cout + cl * 4, gq[q]);
+      }
+      float y4[2][4];
+      quad.dot4(s_w, Cout, cl * 4, y4);
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const bool live = ow0 + q < OWr;      // (no branch: pixels past the row end contribute zeros)
+        float dy[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float xh = (y4[q][j] - mu[j]) * rs[j];
+          const float da = (fabsf(xh + be[j]) > 1.0f) ? 0.f : gq[q][j];
+          dy[j] = live ? rs[j] * (da - mda[j] - xh * mdx[j]) : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < FC::K; ++k) {
+          const float xk = quad.tap(q, k);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[k][j] = fmaf(xk, dy[j], acc[k][j]);
+        }
+      }
+    }
+    continue;
+   }
    typename FC::Row walk;
    walk.begin(x, row, H, W);
    for (unsigned owi = 0; owi < OWr; ++owi) {
@@ -1845,6 +2007,7 @@ conv_first_bwd_wgrad_kernel(const float* __restrict__ x, const float* __restrict
   // combine the pixel lanes of the block through shared memory, one tap at a time
   __syncthreads();
   float* s_acc = reinterpret_cast<float*>(first_conv_weights_smem());  // weights no longer needed
+#pragma unroll   // (acc[] must be indexed by constants to stay in registers)
   for (int k = 0; k < FC::K; ++k) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) s_acc[rl * Cout + cl * 4 + j] = acc[k][j];
@@ -1972,19 +2135,20 @@ static size_t first_conv_smem(int K, int Cout) {
   return w > lanes_acc ? w : lanes_acc;
 }
 
-static int first_conv_grid(int B, int H, int W, int Cout) {
+static int first_conv_grid(int B, int H, int W, int Cout, int waves = 6) {
   const long long pixels = static_cast<long long>(B) * (H - 2) * (W - 2);
   const int lanes = 256 / (Cout / 4);
   long long g = (pixels + lanes * 16 - 1) / (lanes * 16);
-  const long long cap = static_cast<long long>(zkb_sm_count()) * 6;
+  const long long cap = static_cast<long long>(zkb_sm_count()) * waves;
   if (g > cap) g = cap;
   return g < 1 ? 1 : static_cast<int>(g);
 }
 
-#define ZKB_FIRST_DISPATCH(kernel, ...)                                                   \
+#define ZKB_FIRST_DISPATCH(kernel, ...) ZKB_FIRST_DISPATCH_W(6, kernel, __VA_ARGS__)
+#define ZKB_FIRST_DISPATCH_W(waves__, kernel, ...)                                        \
   do {                                                                                    \
     const size_t smem__ = first_conv_smem(9 * Cin, Cout);                                 \
-    const int grid__ = first_conv_grid(B, H, W, Cout);                                    \
+    const int grid__ = first_conv_grid(B, H, W, Cout, waves__);                           \
     cudaStream_t st__ = static_cast<cudaStream_t>(stream);                                \
     if (Cin == 1) {                                                                       \
       kernel<3, 1><<<grid__, 256, smem__, st__>>>(__VA_ARGS__);                           \
@@ -2066,7 +2230,9 @@ ZKB_API int zkb_conv_first_bwd_wgrad(const float* x, const float* wq_k_co, const
               "conv_first_bwd_wgrad: null pointer");
   ZKB_REQUIRE(ZKB_ALIGNED16(g), "conv_first_bwd_wgrad: g must be 16-byte aligned");
   if (B == 0) return ZKB_OK;
-  ZKB_FIRST_DISPATCH(conv_first_bwd_wgrad_kernel, x, wq_k_co, g, B, H, W, Cout, mean, rstd, beta,
-                     mean_da, mean_dax, dw_k_co);
+  // one resident block per SM (its ~250 registers per thread) and a per-block epilogue of K
+  // shared-memory reductions + atomics: two long blocks per SM instead of six short ones
+  ZKB_FIRST_DISPATCH_W(2, conv_first_bwd_wgrad_kernel, x, wq_k_co, g, B, H, W, Cout, mean, rstd, beta,
+                       mean_da, mean_dax, dw_k_co);
   return ZKB_OK;
 }
