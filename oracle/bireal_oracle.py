@@ -117,7 +117,7 @@ def forward_backward(params: Dict[str, np.ndarray], units: int, h0: np.ndarray, 
     grads = {k: v.grad.detach().numpy() for k, v in p.items()}
     grads["h0"] = h.grad.detach().numpy()
     acc = float((logits.argmax(1) == lab).float().mean())
-    return {"loss": float(loss), "logits": logits.detach().numpy(), "grads": grads, "acts": acts, "accuracy": acc}
+    return {"loss": float(loss.detach()), "logits": logits.detach().numpy(), "grads": grads, "acts": acts, "accuracy": acc}
 
 
 def adam_step(params, grads, m, v, step: int, lr: float = 5e-3, b1=0.9, b2=0.999, eps=1e-7, dtype=np.float64):
