@@ -295,6 +295,18 @@ int zkb_bn_gain_bwd_apply(const float* d, const void* y_i16, long long rows, int
                           const float* mean_dx, void* out_hi, void* out_lo, void* stream);
 int zkb_approx_sign_bwd_add(const float* ds, const float* h, const float* d_short, float* out,
                             long long n, void* stream);
+/* The float side of a down-sampling unit's shortcut (AveragePooling2D(2, 2) -> Conv2D 1x1 without
+ * bias -> BatchNormalization): the pool and its backward, and the gain BatchNorm pair for a FLOAT
+ * input map (alpha = 1: pass ones to zkb_bn_gain_finalize; statistics from zkb_bn_stats(x_is_i16 = 0),
+ * backward sums from zkb_bn_bwd_reduce(x_is_i16 = 0, ste = 0)).  The 1x1 conv itself is
+ * zkb_dense_f32_fwd / _bwd over the [pixels, C] view of the map. */
+int zkb_avgpool2_f32_fwd(const float* x, int B, int H, int W, int C, float* out, void* stream);
+int zkb_avgpool2_f32_bwd(const float* dout, int B, int H, int W, int C, float* dx, void* stream);
+int zkb_bn_gain_add_f32(const float* x, long long rows, int C, const float* mean, const float* gain,
+                        const float* beta, const float* shortcut, float* out, void* stream);
+int zkb_bn_gain_bwd_apply_f32(const float* d, const float* x, long long rows, int C, const float* mean,
+                              const float* rs_bwd, const float* gain, const float* mean_d,
+                              const float* mean_dx, float* out, void* stream);
 /* Head of the larq-zoo models: global average pooling over the HW positions of [B,HW,C] (C % 4 == 0)
  * and a float Dense layer y[M][ldy] = x[M][K] w[K][N] + bias (bias may be NULL); the backward
  * WRITES dw[K][N], dbias[N] (optional) and dx[M][K] (optional). */

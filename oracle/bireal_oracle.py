@@ -21,6 +21,12 @@ PUBLISHED definitions (marked [EXT] there):
                kernel_quantizer=magnitude_aware_sign, kernel_constraint=weight_clip)(h)) + h
       (Keras BatchNormalization defaults here: scale and centre, epsilon 1e-3; momentum does not
       enter a train step's gradients)
+  larq_zoo BiRealNet down-sampling unit (first unit of stages 2-4):
+      main     = BatchNormalization()(QuantConv2D(3x3, strides=2, same, ... as above)(h))   (C -> 2C)
+      shortcut = BatchNormalization()(Conv2D(2C, 1, use_bias=False)(AveragePooling2D(2, 2)(h)))   (float)
+      h_next   = main + shortcut
+      (TensorFlow 'same' at stride 2: out = ceil(in/2), total padding max((out-1)*2 + 3 - in, 0), the
+      smaller half in front -- even maps pad 0 before and 1 after)
   head: GlobalAveragePooling2D -> Dense(num_classes) (float, with bias) -> softmax, sparse CE.
   stem pool: MaxPool2D(pool_size=3, strides=2, padding="same"); ties go to the first maximum in
       row-major window order (the same rule as the 2x2 pool).
@@ -69,44 +75,75 @@ def magnitude_aware_sign(w_hwio: torch.Tensor) -> torch.Tensor:
     return scale * _SteSign.apply(w_hwio)
 
 
-def init_params(units: int, channels: int, num_classes: int, seed: int = 0) -> Dict[str, np.ndarray]:
-    """Glorot-uniform kernels, gamma 1 + noise, beta noise (so that no gradient is trivially zero)."""
+def _plan(units):
+    return ["plain"] * units if isinstance(units, int) else list(units)
+
+
+def init_params(units, channels: int, num_classes: int, seed: int = 0) -> Dict[str, np.ndarray]:
+    """Glorot-uniform kernels, gamma 1 + noise, beta noise (so that no gradient is trivially zero).
+    ``units``: a count of plain units or a sequence of "plain" / "down"."""
     rng = np.random.default_rng(seed)
     p = {}
-    for u in range(units):
-        lim = np.sqrt(6.0 / (9 * channels + 9 * channels))
-        p[f"kernel{u}"] = rng.uniform(-lim, lim, size=(3, 3, channels, channels)).astype(np.float32)
-        p[f"gamma{u}"] = (1.0 + 0.1 * rng.standard_normal(channels)).astype(np.float32)
-        p[f"beta{u}"] = (0.1 * rng.standard_normal(channels)).astype(np.float32)
-    lim = np.sqrt(6.0 / (channels + num_classes))
-    p["dense_kernel"] = rng.uniform(-lim, lim, size=(channels, num_classes)).astype(np.float32)
+    c = channels
+    for u, kind in enumerate(_plan(units)):
+        co = 2 * c if kind == "down" else c
+        lim = np.sqrt(6.0 / (9 * c + 9 * co))
+        p[f"kernel{u}"] = rng.uniform(-lim, lim, size=(3, 3, c, co)).astype(np.float32)
+        p[f"gamma{u}"] = (1.0 + 0.1 * rng.standard_normal(co)).astype(np.float32)
+        p[f"beta{u}"] = (0.1 * rng.standard_normal(co)).astype(np.float32)
+        if kind == "down":
+            lim = np.sqrt(6.0 / (c + co))
+            p[f"sc_kernel{u}"] = rng.uniform(-lim, lim, size=(c, co)).astype(np.float32)
+            p[f"sc_gamma{u}"] = (1.0 + 0.1 * rng.standard_normal(co)).astype(np.float32)
+            p[f"sc_beta{u}"] = (0.1 * rng.standard_normal(co)).astype(np.float32)
+        c = co
+    lim = np.sqrt(6.0 / (c + num_classes))
+    p["dense_kernel"] = rng.uniform(-lim, lim, size=(c, num_classes)).astype(np.float32)
     p["dense_bias"] = (0.01 * rng.standard_normal(num_classes)).astype(np.float32)
     return p
 
 
-def forward_backward(params: Dict[str, np.ndarray], units: int, h0: np.ndarray, labels: np.ndarray,
+def _batchnorm(z, gamma, beta):
+    mean = z.mean(dim=(0, 1, 2))
+    var = z.var(dim=(0, 1, 2), unbiased=False)
+    return (z - mean) * torch.rsqrt(var + BN_EPS) * gamma + beta, mean, var
+
+
+def _same_pad_stride2(x_nchw, k=3):
+    h, w = x_nchw.shape[2:]
+    th = max((((h + 1) // 2) - 1) * 2 + k - h, 0)
+    tw = max((((w + 1) // 2) - 1) * 2 + k - w, 0)
+    return torch.nn.functional.pad(x_nchw, (tw // 2, tw - tw // 2, th // 2, th - th // 2))
+
+
+def forward_backward(params: Dict[str, np.ndarray], units, h0: np.ndarray, labels: np.ndarray,
                      dtype=torch.float64, keep: bool = False):
-    """One train-mode forward + backward of `units` residual units and the head.  h0: [B,H,W,C]
-    float activations entering the first unit.  Returns dict(loss, logits, grads, acts)."""
+    """One train-mode forward + backward of the residual units and the head.  h0: [B,H,W,C] float
+    activations entering the first unit.  Returns dict(loss, logits, grads, acts)."""
     p = {k: torch.tensor(v, dtype=dtype, requires_grad=True) for k, v in params.items()}
     h = torch.tensor(h0, dtype=dtype, requires_grad=True)
     acts: Dict[str, np.ndarray] = {}
     x = h
-    for u in range(units):
+    for u, kind in enumerate(_plan(units)):
         s = approx_sign(x)
         wq = magnitude_aware_sign(p[f"kernel{u}"])
-        z = torch.nn.functional.conv2d(s.permute(0, 3, 1, 2), wq.permute(3, 2, 0, 1), padding=1).permute(0, 2, 3, 1)
-        mean = z.mean(dim=(0, 1, 2))
-        var = z.var(dim=(0, 1, 2), unbiased=False)
-        bn = (z - mean) * torch.rsqrt(var + BN_EPS) * p[f"gamma{u}"] + p[f"beta{u}"]
+        sn = s.permute(0, 3, 1, 2)
+        if kind == "down":
+            z = torch.nn.functional.conv2d(_same_pad_stride2(sn), wq.permute(3, 2, 0, 1), stride=2).permute(0, 2, 3, 1)
+            pooled = torch.nn.functional.avg_pool2d(x.permute(0, 3, 1, 2), 2).permute(0, 2, 3, 1)
+            t = pooled @ p[f"sc_kernel{u}"]                                   # 1x1 conv, no bias
+            shortcut, _, _ = _batchnorm(t, p[f"sc_gamma{u}"], p[f"sc_beta{u}"])
+        else:
+            z = torch.nn.functional.conv2d(sn, wq.permute(3, 2, 0, 1), padding=1).permute(0, 2, 3, 1)
+            shortcut = x
+        bn, mean, var = _batchnorm(z, p[f"gamma{u}"], p[f"beta{u}"])
         if keep:
             with torch.no_grad():
-                alpha = params[f"kernel{u}"].astype(np.float64)
-                alpha = np.abs(alpha).mean(axis=(0, 1, 2))
+                alpha = np.abs(params[f"kernel{u}"].astype(np.float64)).mean(axis=(0, 1, 2))
                 acts[f"y{u}"] = np.rint((z.detach().numpy() / alpha)).astype(np.int64)   # integer conv output
                 acts[f"alpha{u}"] = alpha
                 acts[f"mean_z{u}"], acts[f"var_z{u}"] = mean.detach().numpy(), var.detach().numpy()
-        x = bn + x
+        x = bn + shortcut
         if keep:
             acts[f"h{u + 1}"] = x.detach().numpy()
     pooled = x.mean(dim=(1, 2))

@@ -136,9 +136,13 @@ def test_stride2_binary_conv_forward_wgrad_dgrad(native_lib, B, H, W, Cin, Cout)
         assert rel < 1e-5, f"stride-2 {what}: {rel:.3g}"
 
 
-@pytest.mark.parametrize("units,C,hw,B,NC", [(2, 128, (14, 14), 8, 10), (1, 256, (7, 7), 5, 1000)])
+@pytest.mark.parametrize("units,C,hw,B,NC", [(2, 128, (14, 14), 8, 10), (1, 256, (7, 7), 5, 1000),
+                                             (("plain", "down", "plain"), 128, (14, 14), 4, 10),
+                                             (("down", "down"), 128, (12, 8), 3, 10)])
 def test_residual_units_train_step_matches_oracle(native_lib, units, C, hw, B, NC):
-    """a Bi-Real-Net-18 residual unit trains one step within 1e-4 of the oracle."""
+    """a Bi-Real-Net-18 residual unit trains one step within 1e-4 of the oracle --
+    plain units, and stacks with down-sampling units (stride-2 binary conv; average-pool + 1x1 float
+    conv + BatchNorm shortcut)."""
     from oracle import bireal_oracle as O
     from zookeeper_b200.bireal import BiRealUnitsEngine
 
@@ -152,7 +156,7 @@ def test_residual_units_train_step_matches_oracle(native_lib, units, C, hw, B, N
     eng.load_params(p)
     eng.train_step(torch.as_tensor(h0).cuda(), torch.as_tensor(lab).cuda(), apply_update=False)
     torch.cuda.synchronize()
-    for u in range(units):
+    for u in range(eng.U):
         # the +-1 contraction is exact; the magnitude scale only enters through the BatchNorm gain
         assert np.array_equal(eng.units[u].y.cpu().numpy().astype(np.int64), ref["acts"][f"y{u}"]), f"unit {u}: integers"
         assert _rel(eng.units[u].alpha.cpu().numpy(), ref["acts"][f"alpha{u}"]) < 1e-6

@@ -136,6 +136,99 @@ bn_gain_bwd_apply_kernel(const float* __restrict__ d, const int16_t* __restrict_
   }
 }
 
+// The same pair for a FLOAT input map (BatchNorm after the 1x1 float conv of a down-sampling
+// shortcut; alpha = 1 there): out = (x - mean) * gain + beta (+ shortcut), and the backward
+// dx = gain * (d - mean_d - xhat * mean_dx) written as f32.  4 channels per thread.
+__global__ void __launch_bounds__(256)
+bn_gain_add_f32_kernel(const float* __restrict__ x, long long rows, int C, const float* __restrict__ mean,
+                       const float* __restrict__ gain, const float* __restrict__ beta,
+                       const float* __restrict__ shortcut, float* __restrict__ out) {
+  const int tpr = C / 4;
+  const long long total = rows * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % tpr) * 4;
+    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    float o[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = (o[j] - mean[c0 + j]) * gain[c0 + j] + beta[c0 + j];
+    if (shortcut) {
+      const float4 s4 = reinterpret_cast<const float4*>(shortcut)[i];
+      o[0] += s4.x; o[1] += s4.y; o[2] += s4.z; o[3] += s4.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = make_float4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_gain_bwd_apply_f32_kernel(const float* __restrict__ d, const float* __restrict__ x, long long rows, int C,
+                             const float* __restrict__ mean, const float* __restrict__ rs_bwd,
+                             const float* __restrict__ gain, const float* __restrict__ mean_d,
+                             const float* __restrict__ mean_dx, float* __restrict__ out) {
+  const int tpr = C / 4;
+  const long long total = rows * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % tpr) * 4;
+    const float4 g4 = reinterpret_cast<const float4*>(d)[i];
+    const float4 x4 = reinterpret_cast<const float4*>(x)[i];
+    const float gg[4] = {g4.x, g4.y, g4.z, g4.w}, xv[4] = {x4.x, x4.y, x4.z, x4.w};
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c0 + j;
+      const float xh = (xv[j] - mean[c]) * rs_bwd[c];
+      o[j] = gain[c] * (gg[j] - mean_d[c] - xh * mean_dx[c]);
+    }
+    reinterpret_cast<float4*>(out)[i] = make_float4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// AveragePooling2D(2, 2) of the down-sampling shortcut, float NHWC ('valid': a trailing odd row /
+// column is dropped), and its backward (every input of a window gets a quarter of the gradient).
+__global__ void __launch_bounds__(256)
+avgpool2_fwd_kernel(const float* __restrict__ x, int B, int H, int W, int C, float* __restrict__ out) {
+  const int PH = H / 2, PW = W / 2, tpr = C / 4;
+  const long long total = static_cast<long long>(B) * PH * PW * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cl = static_cast<int>(i % tpr);
+    long long r = i / tpr;
+    const int pw = static_cast<int>(r % PW);
+    r /= PW;
+    const int ph = static_cast<int>(r % PH);
+    const long long b = r / PH;
+    const float* p0 = x + ((b * H + 2 * ph) * W + 2 * pw) * C + cl * 4;
+    const float4 a = *reinterpret_cast<const float4*>(p0);
+    const float4 b4 = *reinterpret_cast<const float4*>(p0 + C);
+    const float4 c4 = *reinterpret_cast<const float4*>(p0 + static_cast<long long>(W) * C);
+    const float4 d4 = *reinterpret_cast<const float4*>(p0 + static_cast<long long>(W) * C + C);
+    reinterpret_cast<float4*>(out)[i] = make_float4((a.x + b4.x + c4.x + d4.x) * 0.25f, (a.y + b4.y + c4.y + d4.y) * 0.25f,
+                                                    (a.z + b4.z + c4.z + d4.z) * 0.25f, (a.w + b4.w + c4.w + d4.w) * 0.25f);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+avgpool2_bwd_kernel(const float* __restrict__ dout, int B, int H, int W, int C, float* __restrict__ dx) {
+  const int PH = H / 2, PW = W / 2, tpr = C / 4;
+  const long long total = static_cast<long long>(B) * H * W * tpr;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cl = static_cast<int>(i % tpr);
+    long long r = i / tpr;
+    const int iw = static_cast<int>(r % W);
+    r /= W;
+    const int ih = static_cast<int>(r % H);
+    const long long b = r / H;
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+    if ((ih >> 1) < PH && (iw >> 1) < PW) {
+      const float4 g = *reinterpret_cast<const float4*>(dout + (((b * PH + (ih >> 1)) * PW + (iw >> 1)) * tpr + cl) * 4);
+      o = make_float4(g.x * 0.25f, g.y * 0.25f, g.z * 0.25f, g.w * 0.25f);
+    }
+    reinterpret_cast<float4*>(dx)[i] = o;
+  }
+}
+
 // approx_sign backward plus the float shortcut: out = d_short + ds * (2 - 2|h|) * [|h| <= 1]
 __global__ void __launch_bounds__(256)
 approx_sign_bwd_add_kernel(const float* __restrict__ ds, const float* __restrict__ h,
@@ -521,5 +614,47 @@ ZKB_API int zkb_dilate2_hi_lo(const void* dy_hi, const void* dy_lo, int B, int H
       static_cast<const uint16_t*>(dy_hi), static_cast<const uint16_t*>(dy_lo), B, H, W, C, OH, OW, off_h, off_w,
       static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo));
   ZKB_LAUNCH_CHECK("dilate2_hi_lo_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_gain_add_f32(const float* x, long long rows, int C, const float* mean, const float* gain,
+                                const float* beta, const float* shortcut, float* out, void* stream) {
+  ZKB_REQUIRE(x && mean && gain && beta && out, "bn_gain_add_f32: null pointer");
+  ZKB_REQUIRE(rows >= 0 && C > 0 && C % 4 == 0, "bn_gain_add_f32: C=%d must be a multiple of 4", C);
+  ZKB_REQUIRE(ZKB_A16(x) && ZKB_A16(out) && ZKB_A16(shortcut), "bn_gain_add_f32: tensors must be 16-byte aligned");
+  if (rows == 0) return ZKB_OK;
+  bn_gain_add_f32_kernel<<<br_grid(rows * (C / 4), 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, rows, C, mean, gain, beta, shortcut, out);
+  ZKB_LAUNCH_CHECK("bn_gain_add_f32_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_bn_gain_bwd_apply_f32(const float* d, const float* x, long long rows, int C, const float* mean,
+                                      const float* rs_bwd, const float* gain, const float* mean_d,
+                                      const float* mean_dx, float* out, void* stream) {
+  ZKB_REQUIRE(d && x && mean && rs_bwd && gain && mean_d && mean_dx && out, "bn_gain_bwd_apply_f32: null pointer");
+  ZKB_REQUIRE(rows >= 0 && C > 0 && C % 4 == 0, "bn_gain_bwd_apply_f32: C=%d must be a multiple of 4", C);
+  ZKB_REQUIRE(ZKB_A16(d) && ZKB_A16(x) && ZKB_A16(out), "bn_gain_bwd_apply_f32: misaligned tensors");
+  if (rows == 0) return ZKB_OK;
+  bn_gain_bwd_apply_f32_kernel<<<br_grid(rows * (C / 4), 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      d, x, rows, C, mean, rs_bwd, gain, mean_d, mean_dx, out);
+  ZKB_LAUNCH_CHECK("bn_gain_bwd_apply_f32_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_avgpool2_f32_fwd(const float* x, int B, int H, int W, int C, float* out, void* stream) {
+  ZKB_REQUIRE(x && out && B >= 0 && H >= 2 && W >= 2 && C > 0 && C % 4 == 0, "avgpool2_fwd: bad arguments (C %% 4 == 0)");
+  ZKB_REQUIRE(ZKB_A16(x) && ZKB_A16(out), "avgpool2_fwd: misaligned tensors");
+  if (B == 0) return ZKB_OK;
+  avgpool2_fwd_kernel<<<br_grid(static_cast<long long>(B) * (H / 2) * (W / 2) * (C / 4), 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, B, H, W, C, out);
+  ZKB_LAUNCH_CHECK("avgpool2_fwd_kernel");
+  return ZKB_OK;
+}
+
+ZKB_API int zkb_avgpool2_f32_bwd(const float* dout, int B, int H, int W, int C, float* dx, void* stream) {
+  ZKB_REQUIRE(dout && dx && B >= 0 && H >= 2 && W >= 2 && C > 0 && C % 4 == 0, "avgpool2_bwd: bad arguments (C %% 4 == 0)");
+  ZKB_REQUIRE(ZKB_A16(dout) && ZKB_A16(dx), "avgpool2_bwd: misaligned tensors");
+  if (B == 0) return ZKB_OK;
+  avgpool2_bwd_kernel<<<br_grid(static_cast<long long>(B) * H * W * (C / 4), 16), 256, 0, static_cast<cudaStream_t>(stream)>>>(dout, B, H, W, C, dx);
+  ZKB_LAUNCH_CHECK("avgpool2_bwd_kernel");
   return ZKB_OK;
 }

@@ -87,6 +87,10 @@ SIGNATURES = {
     "zkb_bconv2d_fwd_i8_s2": [P, P, P, I, I, I, I, I, I, P],
     "zkb_bconv2d_wgrad_s2": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_dilate2_hi_lo": [P, P, I, I, I, I, I, P, P, P],
+    "zkb_avgpool2_f32_fwd": [P, I, I, I, I, P, P],
+    "zkb_avgpool2_f32_bwd": [P, I, I, I, I, P, P],
+    "zkb_bn_gain_add_f32": [P, L, I, P, P, P, P, P, P],
+    "zkb_bn_gain_bwd_apply_f32": [P, P, L, I, P, P, P, P, P, P, P],
     "zkb_bn_train_sign_static": [P, I, L, I, P, F, F, I, P, P, P, P, P],
 }
 
