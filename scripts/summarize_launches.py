@@ -14,7 +14,7 @@ for r in csv.DictReader(lines):
         rows.append((name, float(r["Metric Value"].replace(",", "")) / 1e3, r["Grid Size"], r["Block Size"]))
 if len(sys.argv) > 2 and sys.argv[2] == "--last-step":
     # one train step = the launches from one preprocess_kernel up to the next one
-    marks = [i for i, r in enumerate(rows) if r[0].endswith("preprocess_kernel")]
+    marks = [i for i, r in enumerate(rows) if "preprocess_kernel" in r[0]]
     if len(marks) >= 2:
         rows = rows[marks[-2]: marks[-1]]
 tot = sum(t for _, t, _, _ in rows)
