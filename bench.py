@@ -557,12 +557,16 @@ def main():
                    "frac_nominal": round(w[1] / (ms * 1e-3) / 4.5e15, 3)}
             if "sustained_pops" in i8:
                 row["frac_measured"] = round(w[1] / (ms * 1e-3) / 1e15 / i8["sustained_pops"], 3)
+            if name.endswith("_pool"):
+                row["note"] = "launch also does the 2x2 max-pool and its BatchNorm statistics in its epilogue"
             layers_bg[tag] = row
         binary_gemm = {"pipe": "tcgen05 kind::i8 (+-1 as int8, int32 accumulate)", "int8_peak_measured": i8,
                        "int8_peak_nominal_pops": 4.5, "layers": layers_bg,
                        "achieved_pops": tot_ops / (tot_ms * 1e-3) / 1e15 if tot_ms else None,
                        "ops_per_step": tot_ops, "ms_per_step": tot_ms,
-                       "frac_nominal": tot_ops / (tot_ms * 1e-3) / 4.5e15 if tot_ms else None}
+                       "frac_nominal": tot_ops / (tot_ms * 1e-3) / 4.5e15 if tot_ms else None,
+                       "note": "ops = 2*M*N*K of every forward binary GEMM of a step / their launch times (serial pass); launches "
+                               "marked in `layers` also pool in their epilogue, which lowers their rate and shortens the step"}
         if "sustained_pops" in i8 and tot_ms:
             binary_gemm["frac"] = binary_gemm["achieved_pops"] / i8["sustained_pops"]
             binary_gemm["frac_vs_burst"] = binary_gemm["achieved_pops"] / i8["burst_pops"]
