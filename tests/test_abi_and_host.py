@@ -57,6 +57,10 @@ def test_engine_refuses_to_run_without_cuda():
 
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         BinaryNetEngine(binarynet_layers(), (28, 28, 1), 8, 10)
+    from zookeeper_b200.bireal import BiRealUnitsEngine
+
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        BiRealUnitsEngine(("plain", "down"), 128, (14, 14), 4, 10)
 
 
 def test_product_code_never_imports_the_oracle():

@@ -239,7 +239,10 @@ class Sequential(Model):
         nb4 = 4 * eng.n_beta
         pad = spec.pad_size if spec.random_crop else 0
         seed = train_data.seed + rank
-        use_graph = os.environ.get("ZKB_NO_GRAPH", "0") != "1"
+        # CUDA-graph replay of the step on one GPU only: a captured step that holds NCCL work kept
+        # the process-group teardown from returning at the end of an 8-GPU run (r2), so data-parallel
+        # runs stay on per-kernel launches (at their per-GPU batch sizes the step is not launch-bound)
+        use_graph = os.environ.get("ZKB_NO_GRAPH", "0") != "1" and world == 1
         captured = False
         hist = {"loss": [], "accuracy": [], "images_per_sec": []}
         if validation_data is not None:
