@@ -58,6 +58,16 @@ def parse():
     return args
 
 
+def config_dict(args, world, sync_bn):
+    """The `config` object of the JSON line.  Both arms emit the same object for the same command
+    line: it names the workload (BASELINE.json config, per-GPU and global batch, how it is split);
+    what an arm actually ran of it is said in its own keys (`cpu_baseline.sample` for the CPU arm)."""
+    return {"workload": workload_name(args), "global_batch": args.batch * world, "parallelism": f"dp{world}",
+            "batchnorm": "sync" if sync_bn else "per-replica",
+            "launch": "cuda-graph replay" if args.graph else "per-kernel launches, 2 streams",
+            "l2": "working set (GBs of activations per step) far larger than the 126 MB L2; no flush"}
+
+
 def workload_name(args, batch=None):
     return (f"BinaryNet (examples/larq_experiment.py) {CONFIGS[args.config]['name']} synthetic, "
             f"batch {args.batch if batch is None else batch}/GPU")
@@ -125,8 +135,11 @@ def run_reference(args):
         "steps": len(times), "warmup": warm, "ms_per_step": 1e3 * total / len(times),
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": workload_name(args), "global_batch": args.batch, "parallelism": "cpu",
-                   "steps_requested": args.steps, "warmup_requested": args.warmup},
+        # the GPU arm's config object for this command line (see config_dict); what this arm ran of it
+        # -- one rank's batch on the host cores, a bounded number of steps -- is in cpu_baseline.sample
+        "config": config_dict(args, args.gpus, args.sync_bn and args.gpus > 1),
+        "reference_run": {"batch": args.batch, "steps_requested": args.steps, "warmup_requested": args.warmup,
+                          "ranks_computing": 1},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -625,10 +638,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
-            "config": {"workload": workload_name(args), "global_batch": B * world, "parallelism": f"dp{world}",
-                       "batchnorm": "sync" if eng.sync_bn else "per-replica",
-                       "launch": "cuda-graph replay" if args.graph else "per-kernel launches, 2 streams",
-                       "l2": "working set (GBs of activations per step) far larger than the 126 MB L2; no flush"},
+            "config": config_dict(args, world, eng.sync_bn),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms / args.steps, "last_loss": loss},
             "gpu_launches": launches, "clocks": clock_info, "roofline": roofline,

@@ -226,10 +226,14 @@ def test_bench_reference_arm_prints_one_contract_line():
     assert d["e2e"]["value"] == d["value"] and "workload" in d["config"]
     # the arm runs the batch it was asked for (the GPU arm's), and says so
     assert d["config"]["global_batch"] == 32 and "batch 32/GPU" in d["config"]["workload"]
-    assert "batch 32" in d["cpu_baseline"]["sample"]
+    assert "batch 32" in d["cpu_baseline"]["sample"] and d["reference_run"]["batch"] == 32
+    # the same config object the GPU arm prints for this command line
+    assert set(d["config"]) == {"workload", "global_batch", "parallelism", "batchnorm", "launch", "l2"}
+    assert d["config"]["parallelism"] == "dp1" and d["config"]["batchnorm"] == "per-replica"
     # BASELINE.json configs[2] (CIFAR-10-shaped), strong split of its batch over 8 ranks: 256 / 8 per rank
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
                         "--config", "cifar", "--scaling", "strong", "--gpus", "8"], capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     d = json.loads([ln for ln in r.stdout.splitlines() if ln.strip()][0])
-    assert "CIFAR-10-shaped 32x32x3" in d["config"]["workload"] and d["config"]["global_batch"] == 32 and d["scaling"] == "strong"
+    assert "CIFAR-10-shaped 32x32x3" in d["config"]["workload"] and d["scaling"] == "strong"
+    assert d["config"]["global_batch"] == 256 and d["config"]["parallelism"] == "dp8" and d["reference_run"]["batch"] == 32
