@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-int zkb_abi_version(void);
+int zkb_abi_version(void);   /* 2 */
 const char* zkb_last_error_string(void);
 
 /* ---- data pipeline --------------------------------------------------------------------------

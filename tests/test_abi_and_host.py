@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol(native_lib):
                and s not in ("zkb_abi_version", "zkb_last_error_string", "zkb_bn_train_sign_static_max_channels",
                             "zkb_bconv2d_fwd_i8_pool_ok")]
     assert not untyped, f"no ctypes signature for: {untyped}"
-    assert native_lib.zkb_abi_version() == 1
+    assert native_lib.zkb_abi_version() == 2
     # pure host query: which pooled maps the fused conv+pool forward tiles (even sizes only)
     ok = native_lib.zkb_bconv2d_fwd_i8_pool_ok
     assert [ok(26, 26, 128), ok(6, 6, 512), ok(30, 30, 128), ok(13, 13, 256), ok(7, 7, 512), ok(26, 26, 96)] == [1, 1, 1, 0, 0, 0]

@@ -19,7 +19,9 @@ int zkb_fail(int code, const char* fmt, ...) {
 
 ZKB_API const char* zkb_last_error_string() { return g_err; }
 
-ZKB_API int zkb_abi_version() { return 1; }
+// 2: round 2 -- four experiment entry points removed, zkb_bconv2d_dgrad_first_bwd lost its mask
+// argument, zkb_bn_train_sign_static_max_channels takes the input type; everything else was added.
+ZKB_API int zkb_abi_version() { return 2; }
 
 int zkb_sm_count() {
   static int cached[64] = {0};
