@@ -90,7 +90,8 @@ int zkb_conv_first_bwd_wgrad(const float* x, const float* wq_k_co, const float* 
 /* ---- binary conv / dense on tcgen05 -------------------------------------------------------------
  * Forward: act_pm1 [NB,H,W,Cin] (conv) or [rows,K] (dense), pm1 bf16; weights as written by
  * zkb_prep_*_weights; y int16 (exact integer sums, |y| <= ks*ks*Cin).  'same' zero padding is
- * produced by TMA im2col out-of-bounds fill.  Cin % 64 == 0 (wgrad: % 128), K % 64 == 0.
+ * produced by TMA im2col out-of-bounds fill.  Cin % 64 == 0, K % 64 == 0 (wgrad: the
+ * reduced operand's width an odd multiple of 64 is handled by M tiles of two 64-row units that may span taps).
  * Replaces: lq.layers.QuantConv2D(padding="same", ste_sign/ste_sign)
  *           examples/larq_experiment.py:71-73,76-78,80-82,85-87,89-91 and lq.layers.QuantDense :95,97,99. */
 int zkb_bconv2d_fwd(const void* act_pm1, const void* wq_oc_k, void* y_i16, int NB, int H, int W,
@@ -324,6 +325,12 @@ int zkb_dense_f32_bwd(const float* x, const float* w_k_n, const float* dy, int l
  * over the zero-inserted gradient map [NB,H,W,Cout] that zkb_dilate2_hi_lo writes. */
 int zkb_bconv2d_fwd_i8_s2(const void* act_i8, const void* wq_oc_k_i8, void* y_i16, int NB, int H, int W,
                           int Cin, int Cout, int ksize, void* stream);
+/* The same on bf16 +-1 operands (exact: products accumulate in f32 below 2^24), for channel counts
+ * that are multiples of 64 but not of 128 -- the 64-channel first stage of Bi-Real-Net-18 -- which
+ * the int8 forward (128 channels per shared-memory row) cannot read.  The stride-1 forward of such
+ * layers is zkb_bconv2d_fwd; zkb_bconv2d_dgrad / _wgrad / _wgrad_s2 accept Cin, Cout % 64 == 0. */
+int zkb_bconv2d_fwd_s2(const void* act_pm1, const void* wq_oc_k, void* y_i16, int NB, int H, int W, int Cin,
+                       int Cout, int ksize, void* stream);
 int zkb_bconv2d_wgrad_s2(const void* act_pm1, const void* dy_hi, const void* dy_lo, float* dw_hwio, int NB,
                          int H, int W, int Cin, int Cout, int ksize, void* stream);
 int zkb_dilate2_hi_lo(const void* dy_hi, const void* dy_lo, int B, int H, int W, int C, int ksize,
@@ -335,6 +342,16 @@ int zkb_maxpool3s2_f32_fwd(const float* x, int B, int H, int W, int C, float* ou
                            void* stream);
 int zkb_maxpool3s2_f32_bwd(const float* dout, const uint8_t* arg, int B, int H, int W, int C, float* dx,
                            void* stream);
+/* Float stem convolutions on the 3-channel image x f32 [B,H,W,3] with TensorFlow 'same' padding:
+ * Conv2D(Cout, 7, strides=2) of Bi-Real-Net-18 and the 11x11 / stride-4 first layer of BinaryAlexNet
+ * (pass the quantised kernel for a QuantConv2D).  w / dw: f32 HWIO [ksize,ksize,3,Cout], Cout % 64 == 0;
+ * y / dy: f32 [B,ceil(H/stride),ceil(W/stride),Cout].  (ksize, stride) is (7, 2) or (11, 4).  The
+ * weight gradient is ACCUMULATED into dw (the caller zeroes it); there is no input gradient.
+ * FP32 FMA kernels on shared-memory patches (K = 147 / 363 on 12-byte pixels is not a TMA operand). */
+int zkb_conv_stem_f32_fwd(const float* x, const float* w_hwio, float* y, int B, int H, int W, int Cin,
+                          int Cout, int ksize, int stride, void* stream);
+int zkb_conv_stem_f32_wgrad(const float* x, const float* dy, float* dw_hwio, int B, int H, int W, int Cin,
+                            int Cout, int ksize, int stride, void* stream);
 
 /* ---- for callers that cannot allocate device memory ----------------------------------------------
  * (No counterpart in the reference: this entry point exists for hosts of this library, not for

@@ -30,6 +30,9 @@ PUBLISHED definitions (marked [EXT] there):
   head: GlobalAveragePooling2D -> Dense(num_classes) (float, with bias) -> softmax, sparse CE.
   stem pool: MaxPool2D(pool_size=3, strides=2, padding="same"); ties go to the first maximum in
       row-major window order (the same rule as the 2x2 pool).
+  larq_zoo BiRealNet stem: Conv2D(64, 7, strides=2, padding="same", use_bias=False) on the image (float
+      weights, no quantizer, no constraint) -> BatchNormalization() -> the stem pool; then four
+      64-channel units and three stages that open with a down-sampling unit (``bireal18_plan``).
 """
 from __future__ import annotations
 
@@ -79,12 +82,22 @@ def _plan(units):
     return ["plain"] * units if isinstance(units, int) else list(units)
 
 
-def init_params(units, channels: int, num_classes: int, seed: int = 0) -> Dict[str, np.ndarray]:
+def bireal18_plan():
+    return ["plain"] * 4 + (["down"] + ["plain"] * 3) * 3
+
+
+def init_params(units, channels: int, num_classes: int, seed: int = 0, stem_ksize: int = 0) -> Dict[str, np.ndarray]:
     """Glorot-uniform kernels, gamma 1 + noise, beta noise (so that no gradient is trivially zero).
-    ``units``: a count of plain units or a sequence of "plain" / "down"."""
+    ``units``: a count of plain units or a sequence of "plain" / "down".  ``stem_ksize`` > 0 adds the
+    stem's parameters (``channels`` filters on a 3-channel image)."""
     rng = np.random.default_rng(seed)
     p = {}
     c = channels
+    if stem_ksize:
+        lim = np.sqrt(6.0 / (stem_ksize * stem_ksize * (3 + c)))
+        p["stem_kernel"] = rng.uniform(-lim, lim, size=(stem_ksize, stem_ksize, 3, c)).astype(np.float32)
+        p["stem_gamma"] = (1.0 + 0.1 * rng.standard_normal(c)).astype(np.float32)
+        p["stem_beta"] = (0.1 * rng.standard_normal(c)).astype(np.float32)
     for u, kind in enumerate(_plan(units)):
         co = 2 * c if kind == "down" else c
         lim = np.sqrt(6.0 / (9 * c + 9 * co))
@@ -109,21 +122,44 @@ def _batchnorm(z, gamma, beta):
     return (z - mean) * torch.rsqrt(var + BN_EPS) * gamma + beta, mean, var
 
 
-def _same_pad_stride2(x_nchw, k=3):
+def _same_pad(x_nchw, k, s, value=0.0):
+    """TensorFlow 'same': out = ceil(in / s), total padding max((out-1) s + k - in, 0), smaller half first."""
     h, w = x_nchw.shape[2:]
-    th = max((((h + 1) // 2) - 1) * 2 + k - h, 0)
-    tw = max((((w + 1) // 2) - 1) * 2 + k - w, 0)
-    return torch.nn.functional.pad(x_nchw, (tw // 2, tw - tw // 2, th // 2, th - th // 2))
+    th = max((-(-h // s) - 1) * s + k - h, 0)
+    tw = max((-(-w // s) - 1) * s + k - w, 0)
+    return torch.nn.functional.pad(x_nchw, (tw // 2, tw - tw // 2, th // 2, th - th // 2), value=value)
+
+
+def _same_pad_stride2(x_nchw, k=3):
+    return _same_pad(x_nchw, k, 2)
+
+
+def stem(p, images, stride: int = 2):
+    """Conv2D(k, strides, 'same', no bias) -> BatchNormalization -> MaxPool2D(3, 2, 'same') on NHWC
+    images; returns (h [B,H2,W2,C], conv output z, BatchNorm output a)."""
+    k = p["stem_kernel"].shape[0]
+    z = torch.nn.functional.conv2d(_same_pad(images.permute(0, 3, 1, 2), k, stride), p["stem_kernel"].permute(3, 2, 0, 1),
+                                   stride=stride).permute(0, 2, 3, 1)
+    a, _, _ = _batchnorm(z, p["stem_gamma"], p["stem_beta"])
+    # -inf padding: a padded position never wins; torch's CPU pool keeps the first maximum in scan order
+    h = torch.nn.functional.max_pool2d(_same_pad(a.permute(0, 3, 1, 2), 3, 2, value=float("-inf")), 3, 2).permute(0, 2, 3, 1)
+    return h, z, a
 
 
 def forward_backward(params: Dict[str, np.ndarray], units, h0: np.ndarray, labels: np.ndarray,
                      dtype=torch.float64, keep: bool = False):
     """One train-mode forward + backward of the residual units and the head.  h0: [B,H,W,C] float
-    activations entering the first unit.  Returns dict(loss, logits, grads, acts)."""
+    activations entering the first unit -- or, when ``params`` holds ``stem_kernel``, the float images
+    [B,H,W,3] entering the stem (``stem_stride`` from the kernel size: 7 -> 2, 11 -> 4).
+    Returns dict(loss, logits, grads, acts)."""
     p = {k: torch.tensor(v, dtype=dtype, requires_grad=True) for k, v in params.items()}
     h = torch.tensor(h0, dtype=dtype, requires_grad=True)
     acts: Dict[str, np.ndarray] = {}
     x = h
+    if "stem_kernel" in p:
+        x, z0, a0 = stem(p, h, stride=2 if params["stem_kernel"].shape[0] == 7 else 4)
+        if keep:
+            acts["stem_z"], acts["stem_a"], acts["h0"] = z0.detach().numpy(), a0.detach().numpy(), x.detach().numpy()
     for u, kind in enumerate(_plan(units)):
         s = approx_sign(x)
         wq = magnitude_aware_sign(p[f"kernel{u}"])

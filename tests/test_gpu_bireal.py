@@ -138,7 +138,9 @@ def test_stride2_binary_conv_forward_wgrad_dgrad(native_lib, B, H, W, Cin, Cout)
 
 @pytest.mark.parametrize("units,C,hw,B,NC", [(2, 128, (14, 14), 8, 10), (1, 256, (7, 7), 5, 1000),
                                              (("plain", "down", "plain"), 128, (14, 14), 4, 10),
-                                             (("down", "down"), 128, (12, 8), 3, 10)])
+                                             (("down", "down"), 128, (12, 8), 3, 10),
+                                             (("plain", "plain"), 64, (14, 14), 6, 10),           # Bi-Real-Net-18 stage 1
+                                             (("plain", "down", "plain"), 64, (12, 12), 4, 10)])  # ... into stage 2
 def test_residual_units_train_step_matches_oracle(native_lib, units, C, hw, B, NC):
     """a Bi-Real-Net-18 residual unit trains one step within 1e-4 of the oracle --
     plain units, and stacks with down-sampling units (stride-2 binary conv; average-pool + 1x1 float
@@ -200,3 +202,67 @@ def test_residual_units_learn(native_lib):
         (first if s < 10 else last).append((eng.last_loss(), eng.last_accuracy()))
     assert np.mean([a for _, a in last[-10:]]) > 0.9 > np.mean([a for _, a in first])
     assert np.mean([l for l, _ in last[-10:]]) < 0.5 * np.mean([l for l, _ in first])
+
+
+@pytest.mark.parametrize("plan,hw,B,NC,seed", [(("plain", "down", "plain"), (32, 32), 4, 10, 4),
+                                               ("bireal18", (64, 64), 2, 10, 4),
+                                               (("plain",), (30, 22), 3, 1000, 5)])
+def test_whole_net_with_stem_train_step_matches_oracle(native_lib, plan, hw, B, NC, seed):
+    """Stem (float 7x7/2 conv -> BatchNorm -> 3x3/2 max-pool) + residual units + head: one train step
+    of the whole model -- Bi-Real-Net-18's own unit plan in one case -- within 1e-4 of the oracle."""
+    from oracle import bireal_oracle as O
+    from zookeeper_b200.bireal import BiRealNetEngine, bireal18_plan
+
+    if plan == "bireal18":
+        plan = O.bireal18_plan()
+        assert plan == bireal18_plan()
+    p = O.init_params(plan, 64, NC, seed=seed, stem_ksize=7)
+    rng = np.random.default_rng(seed + 100)
+    img = rng.uniform(-1, 1, (B,) + hw + (3,)).astype(np.float32)
+    lab = rng.integers(0, NC, (B,)).astype(np.int64)
+    ref = O.forward_backward(p, plan, img, lab, torch.float64, keep=True)
+
+    eng = BiRealNetEngine(plan, hw, B, NC)
+    eng.load_params(p)
+    eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda(), apply_update=False)
+    torch.cuda.synchronize()
+    assert _rel(eng.z.cpu().numpy(), ref["acts"]["stem_z"]) < 1e-6, "stem conv output"
+    assert _rel(eng.a.cpu().numpy(), ref["acts"]["stem_a"]) < 1e-5, "stem BatchNorm output"
+    assert _rel(eng.body.h[0].cpu().numpy(), ref["acts"]["h0"]) < 1e-5, "stem pool output"
+    for u in range(eng.body.U):
+        assert np.array_equal(eng.body.units[u].y.cpu().numpy().astype(np.int64), ref["acts"][f"y{u}"]), f"unit {u}: integers"
+    assert abs(eng.last_loss() - ref["loss"]) <= REL_TOL * abs(ref["loss"])
+    assert _rel(eng.body.logits.cpu().numpy(), ref["logits"]) < REL_TOL
+    g = eng.get_grads()
+    worst = {k: _rel(g[k], v) for k, v in ref["grads"].items() if k != "h0"}
+    bad = {k: f"{r:.3g}" for k, r in worst.items() if not r < REL_TOL}
+    assert not bad, f"gradients outside 1e-4: {bad}"
+    # optimizer: the stem kernel is a float Conv2D -- Adam without the clip
+    zero = {k: np.zeros_like(v) for k, v in p.items()}
+    exp32, _, _ = O.adam_step(p, {k: g[k] for k in p}, zero, zero, 1, dtype=np.float32)
+    eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda(), apply_update=True)
+    torch.cuda.synchronize()
+    got = eng.get_params()
+    for k in p:
+        assert _rel(got[k], exp32[k]) < 2e-6, f"adam kernel {k}"
+    assert eng.launches_per_step > 0
+
+
+def test_whole_net_learns(native_lib):
+    """A hundred steps of the stem + units + head on a learnable task: the loss falls."""
+    from oracle import bireal_oracle as O
+    from zookeeper_b200.bireal import BiRealNetEngine
+
+    plan, hw, B, NC = ("plain", "down", "plain"), (32, 32), 32, 10
+    rng = np.random.default_rng(21)
+    protos = rng.uniform(-1, 1, (NC,) + hw + (3,)).astype(np.float32)
+    eng = BiRealNetEngine(plan, hw, B, NC)
+    eng.load_params(O.init_params(plan, 64, NC, seed=6, stem_ksize=7))
+    first, last = [], []
+    for s in range(100):
+        lab = rng.integers(0, NC, (B,))
+        img = np.clip(protos[lab] * 0.6 + rng.normal(0, 0.3, (B,) + hw + (3,)), -1, 1).astype(np.float32)
+        eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda())
+        (first if s < 10 else last).append(eng.last_loss())
+    assert np.isfinite(last).all()
+    assert np.mean(last[-10:]) < 0.5 * np.mean(first), (np.mean(first), np.mean(last[-10:]))

@@ -22,9 +22,15 @@ A unit is either "plain" (C -> C, stride 1, identity shortcut) or "down" (C -> 2
 TensorFlow 'same' padding; shortcut = AveragePooling2D(2, 2) -> Conv2D 1x1 without bias ->
 BatchNormalization, all float), so the stack below is the body of a Bi-Real-Net from any stage on.
 
-What is NOT here: the float 7x7/2 stem conv and a Keras functional-API front end -- the stack takes
-float activations [B,H,W,C] as input (``zkb_maxpool3s2_f32_*``, the stem's pool, is available as a
-kernel).  The 1x1 float conv of the down-sampling shortcut runs on plain SIMT kernels.
+``BiRealNetEngine`` puts the zoo model's stem in front of such a stack -- float Conv2D(64, 7,
+strides=2, "same") on the image, BatchNormalization, MaxPool2D(3, 2, "same") -- which makes the whole
+Bi-Real-Net-18 (``bireal18_plan()``: four 64-channel units, then three stages that open with a
+down-sampling unit) one engine.  Channel counts are multiples of 64; layers whose input width is
+not a multiple of 128 (the 64-channel stage) run the bf16 +-1 forward GEMM instead of the int8 one
+(same integers, half the tensor-pipe rate).
+
+What is NOT here: a Keras functional-API front end (the plan is a list of unit kinds).  The 1x1 float
+conv of the down-sampling shortcut runs on plain SIMT kernels, the stem conv on FP32 FMA kernels.
 """
 from __future__ import annotations
 
@@ -46,8 +52,8 @@ class _Unit:
 class BiRealUnitsEngine:
     """A stack of binary residual units on a [B, H, W, channels] float map, then global average
     pooling and a float classifier.  ``units``: a count of plain units, or a sequence of "plain" /
-    "down".  Channel counts must be multiples of 128 (the int8 forward GEMM reads 128 channels per
-    shared-memory row); "down" needs an even map."""
+    "down".  Channel counts must be multiples of 64 (a shared-memory row of the bf16 GEMM operands;
+    multiples of 128 take the int8 forward); "down" needs an even map."""
 
     def __init__(self, units, channels: int, hw, batch_size: int, num_classes: int,
                  learning_rate: float = 5e-3, bn_momentum: float = 0.99, beta_1: float = 0.9,
@@ -58,8 +64,8 @@ class BiRealUnitsEngine:
         self.plan = ["plain"] * units if isinstance(units, int) else [str(u) for u in units]
         if not self.plan or any(u not in ("plain", "down") for u in self.plan):
             raise ValueError('units: a positive count or a sequence of "plain" / "down"')
-        if channels % 128 != 0:
-            raise ValueError(f"channels={channels} must be a multiple of 128")
+        if channels % 64 != 0:
+            raise ValueError(f"channels={channels} must be a multiple of 64")
         self.device = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         self.U, self.C, self.B, self.NC = len(self.plan), int(channels), int(batch_size), int(num_classes)
         self.H, self.W = int(hw[0]), int(hw[1])
@@ -221,12 +227,20 @@ class BiRealUnitsEngine:
             # approx_sign forward = sign(h) (+1 at 0): the BatchNorm+sign kernel with an identity affine
             self._call("zkb_bn_apply_sign", zn.ptr(self.h[u]), 0, rows_in, ci, zn.ptr(self.zeros_c), zn.ptr(self.ones_c),
                        zn.ptr(self.zeros_c), zn.ptr(X.s), 0, zn.ptr(X.s8))
+            i8 = ci % 128 == 0        # the int8 GEMM reads 128 channels per shared-memory row
             if X.kind == "plain":
-                self._call("zkb_bconv2d_fwd_i8_stats", zn.ptr(X.s8), zn.ptr(X.w_fwd8), zn.ptr(X.y), B, hi, wi, ci, co, 3,
-                           zn.ptr(X.sum), zn.ptr(X.sumsq))
+                if i8:
+                    self._call("zkb_bconv2d_fwd_i8_stats", zn.ptr(X.s8), zn.ptr(X.w_fwd8), zn.ptr(X.y), B, hi, wi, ci, co, 3,
+                               zn.ptr(X.sum), zn.ptr(X.sumsq))
+                else:
+                    self._call("zkb_bconv2d_fwd", zn.ptr(X.s), zn.ptr(X.w_fwd), zn.ptr(X.y), B, hi, wi, ci, co, 3)
+                    self._call("zkb_bn_stats", zn.ptr(X.y), 1, rows, co, zn.ptr(X.sum), zn.ptr(X.sumsq))
                 shortcut = self.h[u]
             else:
-                self._call("zkb_bconv2d_fwd_i8_s2", zn.ptr(X.s8), zn.ptr(X.w_fwd8), zn.ptr(X.y), B, hi, wi, ci, co, 3)
+                if i8:
+                    self._call("zkb_bconv2d_fwd_i8_s2", zn.ptr(X.s8), zn.ptr(X.w_fwd8), zn.ptr(X.y), B, hi, wi, ci, co, 3)
+                else:
+                    self._call("zkb_bconv2d_fwd_s2", zn.ptr(X.s), zn.ptr(X.w_fwd), zn.ptr(X.y), B, hi, wi, ci, co, 3)
                 self._call("zkb_bn_stats", zn.ptr(X.y), 1, rows, co, zn.ptr(X.sum), zn.ptr(X.sumsq))
                 # shortcut: average pool -> 1x1 float conv -> BatchNorm (with scale)
                 self._call("zkb_avgpool2_f32_fwd", zn.ptr(self.h[u]), B, hi, wi, ci, zn.ptr(X.pool))
@@ -329,3 +343,132 @@ class BiRealUnitsEngine:
 
     def last_accuracy(self) -> float:
         return float(self.correct.item()) / self.B
+
+
+def bireal18_plan():
+    """Unit kinds of larq-zoo's Bi-Real-Net-18 after the stem: four 64-channel units, then three
+    stages (128, 256, 512 channels) of a down-sampling unit followed by three plain ones."""
+    return ["plain"] * 4 + (["down"] + ["plain"] * 3) * 3
+
+
+class BiRealNetEngine:
+    """The whole zoo model: stem (float Conv2D(filters, 7, strides=2, "same", use_bias=False) ->
+    BatchNormalization -> MaxPool2D(3, 2, "same")) in front of a ``BiRealUnitsEngine``.  Images are
+    float32 [B,H,W,3] (what ``zkb_preprocess_u8`` writes).  The stem kernel is a plain float Conv2D:
+    Adam without the latent-weight clip."""
+
+    def __init__(self, units, image_hw, batch_size: int, num_classes: int, stem_filters: int = 64,
+                 stem_ksize: int = 7, stem_stride: int = 2, **kw):
+        zn.load()
+        if not torch.cuda.is_available():
+            raise RuntimeError("BiRealNetEngine needs a CUDA device (B200); there is no CPU fallback")
+        if (stem_ksize, stem_stride) not in ((7, 2), (11, 4)):
+            raise ValueError("stem: (ksize, stride) is (7, 2) or (11, 4)")
+        if stem_filters % 64 != 0:
+            raise ValueError(f"stem_filters={stem_filters} must be a multiple of 64")
+        H, W = int(image_hw[0]), int(image_hw[1])
+        self.H, self.W, self.B, self.F = H, W, int(batch_size), int(stem_filters)
+        self.ks, self.stride = int(stem_ksize), int(stem_stride)
+        self.H1, self.W1 = -(-H // self.stride), -(-W // self.stride)      # conv output ('same')
+        self.H2, self.W2 = (self.H1 + 1) // 2, (self.W1 + 1) // 2           # pooled
+        self.body = BiRealUnitsEngine(units, self.F, (self.H2, self.W2), batch_size, num_classes, **kw)
+        dev, f32, B, F = self.body.device, torch.float32, self.B, self.F
+        self.device = dev
+        nk = self.ks * self.ks * 3 * F
+        n = nk + 2 * F
+        self.params = torch.zeros(n, dtype=f32, device=dev)
+        self.grads = torch.zeros(n, dtype=f32, device=dev)
+        self.adam_m = torch.zeros(n, dtype=f32, device=dev)
+        self.adam_v = torch.zeros(n, dtype=f32, device=dev)
+        self.kernel, self.dkernel = self.params[:nk], self.grads[:nk]
+        self.gamma, self.dgamma = self.params[nk:nk + F], self.grads[nk:nk + F]
+        self.beta, self.dbeta = self.params[nk + F:], self.grads[nk + F:]
+        self.gamma.fill_(1.0)
+        self.acc = torch.zeros(4 * F, dtype=torch.float64, device=dev)
+        self.sum, self.sumsq, self.sum_d, self.sum_dx = (self.acc[i * F:(i + 1) * F] for i in range(4))
+        self.mean, self.rs, self.gain, self.mean_d, self.mean_dx = (torch.zeros(F, dtype=f32, device=dev) for _ in range(5))
+        self.mm, self.mv = torch.zeros(F, dtype=f32, device=dev), torch.ones(F, dtype=f32, device=dev)
+        self.ones = torch.ones(F, dtype=f32, device=dev)
+        self.scratch = torch.zeros(2 * F, dtype=f32, device=dev)
+        self.x = torch.zeros(B, H, W, 3, dtype=f32, device=dev)
+        self.z = torch.zeros(B, self.H1, self.W1, F, dtype=f32, device=dev)     # conv output
+        self.a = torch.zeros(B, self.H1, self.W1, F, dtype=f32, device=dev)     # BatchNorm(z)
+        self.da = torch.zeros(B, self.H1, self.W1, F, dtype=f32, device=dev)
+        self.dz = torch.zeros(B, self.H1, self.W1, F, dtype=f32, device=dev)
+        self.arg = torch.zeros(B, self.H2, self.W2, F, dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ parameters in / out
+    def load_params(self, p: Dict[str, np.ndarray]):
+        """The body's names (``BiRealUnitsEngine.load_params``) plus ``stem_kernel`` HWIO [k,k,3,F],
+        ``stem_gamma``, ``stem_beta`` [F]."""
+        self.body.load_params(p)
+        self.kernel.copy_(torch.as_tensor(np.ascontiguousarray(p["stem_kernel"]), dtype=torch.float32).reshape(-1))
+        self.gamma.copy_(torch.as_tensor(p["stem_gamma"], dtype=torch.float32))
+        self.beta.copy_(torch.as_tensor(p["stem_beta"], dtype=torch.float32))
+
+    def _stem_named(self, t):
+        nk, F = self.ks * self.ks * 3 * self.F, self.F
+        t = t.detach().cpu().numpy()
+        return {"stem_kernel": t[:nk].reshape(self.ks, self.ks, 3, F).copy(), "stem_gamma": t[nk:nk + F].copy(),
+                "stem_beta": t[nk + F:].copy()}
+
+    def get_params(self) -> Dict[str, np.ndarray]:
+        return {**self.body.get_params(), **self._stem_named(self.params)}
+
+    def get_grads(self) -> Dict[str, np.ndarray]:
+        out = {**self.body.get_grads(), **self._stem_named(self.grads)}
+        out.pop("h0")           # the gradient entering the stem's pool; not a parameter
+        return out
+
+    # ------------------------------------------------------------------ one step
+    def stem_forward(self, training: bool = True):
+        c, B, F = self.body._call, self.B, self.F
+        rows = B * self.H1 * self.W1
+        mm = (lambda t: zn.ptr(t)) if training else (lambda t: 0)
+        c("zkb_conv_stem_f32_fwd", zn.ptr(self.x), zn.ptr(self.kernel), zn.ptr(self.z), B, self.H, self.W, 3, F, self.ks, self.stride)
+        c("zkb_bn_stats", zn.ptr(self.z), 0, rows, F, zn.ptr(self.sum), zn.ptr(self.sumsq))
+        c("zkb_bn_gain_finalize", zn.ptr(self.sum), zn.ptr(self.sumsq), float(rows), zn.ptr(self.ones), zn.ptr(self.gamma),
+          BN_EPS, self.body.momentum, 1, F, zn.ptr(self.mean), zn.ptr(self.rs), zn.ptr(self.gain), mm(self.mm), mm(self.mv))
+        c("zkb_bn_gain_add_f32", zn.ptr(self.z), rows, F, zn.ptr(self.mean), zn.ptr(self.gain), zn.ptr(self.beta), 0, zn.ptr(self.a))
+        c("zkb_maxpool3s2_f32_fwd", zn.ptr(self.a), B, self.H1, self.W1, F, zn.ptr(self.body.h[0]), zn.ptr(self.arg))
+
+    def stem_backward(self):
+        c, B, F = self.body._call, self.B, self.F
+        rows = B * self.H1 * self.W1
+        c("zkb_maxpool3s2_f32_bwd", zn.ptr(self.body.dh[0]), zn.ptr(self.arg), B, self.H1, self.W1, F, zn.ptr(self.da))
+        c("zkb_bn_bwd_reduce", zn.ptr(self.da), zn.ptr(self.z), 0, rows, F, zn.ptr(self.mean), zn.ptr(self.rs), zn.ptr(self.beta), 0,
+          zn.ptr(self.sum_d), zn.ptr(self.sum_dx))
+        c("zkb_bn_bwd_finalize", zn.ptr(self.sum_d), zn.ptr(self.sum_dx), float(rows), 1.0, F, zn.ptr(self.dbeta), zn.ptr(self.mean_d),
+          zn.ptr(self.mean_dx))
+        c("zkb_bn_bwd_finalize", zn.ptr(self.sum_dx), zn.ptr(self.sum_d), float(rows), 1.0, F, zn.ptr(self.dgamma), zn.ptr(self.scratch),
+          self.scratch[F:].data_ptr())
+        c("zkb_bn_gain_bwd_apply_f32", zn.ptr(self.da), zn.ptr(self.z), rows, F, zn.ptr(self.mean), zn.ptr(self.rs), zn.ptr(self.gain),
+          zn.ptr(self.mean_d), zn.ptr(self.mean_dx), zn.ptr(self.dz))
+        c("zkb_conv_stem_f32_wgrad", zn.ptr(self.x), zn.ptr(self.dz), zn.ptr(self.dkernel), B, self.H, self.W, 3, F, self.ks, self.stride)
+
+    def train_step(self, images: torch.Tensor, labels: torch.Tensor, apply_update: bool = True):
+        """images: float32 [B,H,W,3]; labels: integer [B]."""
+        body = self.body
+        body._stream = torch.cuda.current_stream(self.device).cuda_stream
+        body._n_launch = 0
+        for t in (self.acc, self.grads, body.acc, body.correct, body.grads):
+            t.zero_()
+        if images.data_ptr() != self.x.data_ptr():
+            self.x.copy_(images)
+        body.labels.copy_(labels.to(torch.int32))
+        body.prepare_weights()
+        self.stem_forward(training=True)
+        body.forward(training=True)
+        body.backward()
+        self.stem_backward()
+        if apply_update:
+            body.optimizer_step()
+            body._call("zkb_adam_clip", zn.ptr(self.params), zn.ptr(self.grads), zn.ptr(self.adam_m), zn.ptr(self.adam_v),
+                       self.params.numel(), body._lr_t(body.step_count), body.b1, body.b2, body.eps, 1.0, 0, 0)
+        self.launches_per_step = body._n_launch
+
+    def last_loss(self) -> float:
+        return self.body.last_loss()
+
+    def last_accuracy(self) -> float:
+        return self.body.last_accuracy()

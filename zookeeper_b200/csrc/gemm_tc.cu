@@ -1070,7 +1070,7 @@ kgemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_consta
 
 // --------------------------------------------------------------------------------------------
 struct WGemmParams {
-  int Ma;       // rows of D per tap (reduced operand A has Ma channels), multiple of 128
+  int Ma;       // rows of D per tap (reduced operand A has Ma channels), multiple of 64
   int N;        // columns of the B operand (multiple of 64)
   int n_valid;  // columns of D actually written (<= N)
   long long P;  // reduction length (pixels / batch rows)
@@ -1082,7 +1082,12 @@ struct WGemmParams {
   int a_im2col;
   int OH, OW, pad, kw_taps, taps;   // OH, OW: the conv's OUTPUT map (rows of dy); pad: low padding along W
   int pad_h, stride;
-  int tpi;      // taps per work item: they share the B (dy) tile, one TMEM accumulator each
+  int tpi;      // M tiles per work item: they share the B (dy) tile, one TMEM accumulator each
+  int mt;       // M tiles along the tap axis: taps, or ceil(units / 2) when flat64
+  int flat64;   // Ma is an odd multiple of 64: D's rows [tap][Ma] are cut into 64-row units
+                //   u = tap * ci64s + c64, and an M tile is the units (2j, 2j+1) -- its two 64-channel
+                //   A boxes may come from different taps; rows past the last unit are not written
+  int units, ci64s;
   int kpix;     // reduction rows per pipeline stage (32, 48 or 64)
   int dbg;      // ZKB_MEASURE builds only: 1 = no MMA issue, 2 = no TMA loads
   int ci_tiles, n_tiles, splits;
@@ -1120,11 +1125,11 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   wi /= p.n_tiles;
   const int tc = wi % p.ci_tiles;
   wi /= p.ci_tiles;
-  const int groups = (p.taps + p.tpi - 1) / p.tpi;
+  const int groups = (p.mt + p.tpi - 1) / p.tpi;
   const int group = wi % groups;     // all tap groups of a split are neighbours in launch order:
   const int split = wi / groups;     // they read the same pixels at about the same time (L2 reuse)
-  const int tap0 = group * p.tpi;
-  const int tcount = (p.taps - tap0) < p.tpi ? (p.taps - tap0) : p.tpi;  // taps of this item
+  const int tap0 = group * p.tpi;    // first M tile (= tap unless flat64) of this item
+  const int tcount = (p.mt - tap0) < p.tpi ? (p.mt - tap0) : p.tpi;  // M tiles of this item
 
   const long long total_chunks = (p.P + p.kpix - 1) / p.kpix;
   const long long chunk_lo = static_cast<long long>(split) * p.chunks_per_split;
@@ -1162,19 +1167,26 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (warp == 0) {
       // Producer warp: lane l owns TMA load l of a stage so that they are issued in parallel
       // (measured r1: one elected lane issuing the 10-12 loads of a stage in turn is 10-20 % slower).
-      // l < nB -> B box (term = l / boxes_per_term); l >= nB -> A box (tap = (l-nB)/2, half = (l-nB)%2).
+      // l < nB -> B box (term = l / boxes_per_term); l >= nB -> A box (M tile = (l-nB)/2, half = (l-nB)%2).
       const int n_loads = nB + 2 * tcount;
       const uint32_t tx_bytes = static_cast<uint32_t>(n_loads * box_bytes);
       const bool is_b = lane < nB;
       const int bt = is_b ? lane / boxes_per_term : 0, bj = is_b ? lane % boxes_per_term : 0;
       const int at = is_b ? 0 : (lane - nB) >> 1, ah = is_b ? 0 : (lane - nB) & 1;
-      const int tap = tap0 + at;
+      int tap = tap0 + at;
+      int a_c = tc * 128 + ah * 64;
+      if (p.flat64) {   // half ah of M tile j is unit 2j + ah (the half past the last unit re-reads it)
+        int u = 2 * (tap0 + at) + ah;
+        if (u >= p.units) u = p.units - 1;
+        tap = u / p.ci64s;
+        a_c = (u - tap * p.ci64s) * 64;
+      }
       const int kh = tap / p.kw_taps;
       const int kw = tap - kh * p.kw_taps;
       const uint32_t my_off = is_b ? static_cast<uint32_t>(a_bytes + (bt * boxes_per_term + bj) * box_bytes)
                                    : static_cast<uint32_t>(at * a_tile_bytes + ah * box_bytes);
       const CUtensorMap* my_map = is_b ? (bt == 0 ? &tmB0 : &tmB1) : &tmA;
-      const int my_c = is_b ? tn * p.cols_per_tile + bj * 64 : tc * 128 + ah * 64;
+      const int my_c = is_b ? tn * p.cols_per_tile + bj * 64 : a_c;
       const unsigned hw = static_cast<unsigned>(p.OH * p.OW);
       int stage = 0;
       uint32_t phase = 0;
@@ -1257,7 +1269,9 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tc_fence_after();
       const int row_in_tap = tc * 128 + q * 32 + lane;  // channel of A
       for (int t = 0; t < tcount; ++t) {
-        const long long orow = static_cast<long long>(tap0 + t) * p.Ma + row_in_tap;
+        const long long orow = p.flat64 ? static_cast<long long>(tap0 + t) * 128 + q * 32 + lane
+                                        : static_cast<long long>(tap0 + t) * p.Ma + row_in_tap;
+        const bool row_ok = p.flat64 ? orow < static_cast<long long>(p.units) * 64 : row_in_tap < p.Ma;
         const uint32_t tbase =
             tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * p.block_n);
         for (int c = 0; c < p.cols_per_tile / 32; ++c) {
@@ -1273,7 +1287,7 @@ wgemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
           }
           const int col0 = tn * p.cols_per_tile + c * 32;
-          if (row_in_tap < p.Ma) {
+          if (row_ok) {
             float* o = p.out + orow * p.ldo + col0;
             if (col0 + 32 <= p.n_valid && (p.ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0) {
               // whole 32-column chunk, 16-byte aligned rows: vector reductions (8 instead of 32)
@@ -1622,7 +1636,7 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
                         int H, int W, int ksize, int pad, cudaStream_t stream, int stride = 1) {
   ZKB_REQUIRE(A && B_hi && out, "wgemm: null pointer");
   ZKB_REQUIRE(Ma > 0 && N > 0 && P > 0, "wgemm: empty problem");
-  ZKB_REQUIRE(Ma % 128 == 0, "wgemm: Ma=%d must be a multiple of 128", Ma);
+  ZKB_REQUIRE(Ma % 64 == 0, "wgemm: Ma=%d must be a multiple of 64", Ma);
   ZKB_REQUIRE(N % 64 == 0, "wgemm: N=%d must be a multiple of 64", N);
   ZKB_REQUIRE(P < (1ll << 31) - 256, "wgemm: P too large");
   ZKB_REQUIRE(n_valid > 0 && n_valid <= N && ldo >= n_valid, "wgemm: bad n_valid / ldo");
@@ -1645,12 +1659,19 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   } else {
     p.block_n = 64; p.concat = 0; p.cols_per_tile = 64;
   }
-  // taps per work item: as many accumulators as fit the 512 TMEM columns, at most a filter row
+  // 64, 192, ... channels: M tiles of two 64-row units (see WGemmParams::flat64)
+  p.flat64 = Ma % 128 != 0;
+  p.ci64s = Ma / 64;
+  p.units = p.taps * p.ci64s;
+  p.mt = p.flat64 ? (p.units + 1) / 2 : p.taps;
+  // M tiles per work item: as many accumulators as fit the 512 TMEM columns, at most a filter row
   p.tpi = 1;
   if (im2col) {
     p.tpi = 512 / p.block_n;
     if (p.tpi > ksize) p.tpi = ksize;
   }
+  if (p.flat64) p.tpi = 512 / p.block_n < 4 ? 512 / p.block_n : 4;
+  if (p.tpi > p.mt) p.tpi = p.mt;
   p.kpix = 64;
   const GemmTuning& tune = gemm_tuning();
   p.dbg = tune.dbg;
@@ -1664,7 +1685,7 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   p.stride = stride;
   p.OH = wgh.out;
   p.OW = wgw.out;
-  p.ci_tiles = Ma / 128;
+  p.ci_tiles = p.flat64 ? 1 : Ma / 128;
   p.n_tiles = N / p.cols_per_tile;
   const int boxes_b = p.b_terms * (p.concat ? 2 : p.block_n / 64);
   // Three pipeline stages hide the TMA latency, two do not (measured r1: -5..12 % with three):
@@ -1683,7 +1704,7 @@ static int launch_wgemm(const void* A, const void* B_hi, const void* B_lo, float
   // CTAs spilling into one more wave cost a whole extra work item of time (measured 10-13 %), and
   // one long wave beats two short ones (fewer pipeline fills and atomic epilogues; measured in the
   // step, r1) unless the output tiles divide the SMs badly.
-  const int out_tiles = ((p.taps + p.tpi - 1) / p.tpi) * p.ci_tiles * p.n_tiles;
+  const int out_tiles = ((p.mt + p.tpi - 1) / p.tpi) * p.ci_tiles * p.n_tiles;
   int waves = tune.wgrad_waves;
   if (waves == 0) {
     double best = 0.0;
@@ -1771,6 +1792,15 @@ ZKB_API int zkb_bconv2d_fwd_i8_s2(const void* act_i8, const void* wq_oc_k_i8, vo
   const long long OH = (H + 1) / 2, OW = (W + 1) / 2;
   return launch_kgemm(act_i8, nullptr, wq_oc_k_i8, y_i16, 1, Cout, NB * OH * OW, Cout, ksize * ksize * Cin, 1,
                       NB, H, W, Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 1, nullptr, nullptr,
+                      nullptr, nullptr, 2);
+}
+
+ZKB_API int zkb_bconv2d_fwd_s2(const void* act_pm1, const void* wq_oc_k, void* y_i16, int NB, int H, int W,
+                               int Cin, int Cout, int ksize, void* stream) {
+  ZKB_REQUIRE(ksize % 2 == 1, "bconv2d_fwd_s2: ksize must be odd");
+  const long long OH = (H + 1) / 2, OW = (W + 1) / 2;
+  return launch_kgemm(act_pm1, nullptr, wq_oc_k, y_i16, 1, Cout, NB * OH * OW, Cout, ksize * ksize * Cin, 1,
+                      NB, H, W, Cin, ksize, ksize / 2, static_cast<cudaStream_t>(stream), 2, nullptr, nullptr,
                       nullptr, nullptr, 2);
 }
 

@@ -85,6 +85,9 @@ SIGNATURES = {
     "zkb_maxpool3s2_f32_bwd": [P, P, I, I, I, I, P, P],
     "zkb_bconv2d_fwd_i8_pool": [P, P, P, P, I, I, I, I, I, I, P, P, P],
     "zkb_bconv2d_fwd_i8_s2": [P, P, P, I, I, I, I, I, I, P],
+    "zkb_bconv2d_fwd_s2": [P, P, P, I, I, I, I, I, I, P],
+    "zkb_conv_stem_f32_fwd": [P, P, P, I, I, I, I, I, I, I, P],
+    "zkb_conv_stem_f32_wgrad": [P, P, P, I, I, I, I, I, I, I, P],
     "zkb_bconv2d_wgrad_s2": [P, P, P, P, I, I, I, I, I, I, P],
     "zkb_dilate2_hi_lo": [P, P, I, I, I, I, I, P, P, P],
     "zkb_avgpool2_f32_fwd": [P, I, I, I, I, P, P],
