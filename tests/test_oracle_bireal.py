@@ -67,3 +67,35 @@ def test_step_shapes_gradients_and_clip():
     new, _, _ = O.adam_step(p, big, zero, zero, 1, lr=2.0)
     assert all(np.abs(new[n]).max() <= 1.0 for n in new if n.startswith("kernel"))      # latent binary kernels are clipped
     assert np.abs(new["dense_kernel"]).max() > 1.0                                      # float weights are not
+
+
+def test_stem_conv_follows_tf_same_padding_and_feeds_the_units():
+    """The stem restated two ways: torch conv2d over explicit TensorFlow 'same' padding (what the oracle
+    runs) against a direct numpy loop over the definition out[oy,ox] = sum x[oy*s - pad + kh, ...];
+    7x7/2 on even and odd sizes, 11x11/4; the pool behind it against the numpy pool; and the whole
+    model's gradient dictionary holds the stem's parameters."""
+    rng = np.random.default_rng(0)
+    for k, s, (h, w) in ((7, 2, (12, 9)), (7, 2, (16, 16)), (11, 4, (21, 18))):
+        x = rng.uniform(-1, 1, (2, h, w, 3))
+        wk = rng.normal(size=(k, k, 3, 4))
+        oh, ow = -(-h // s), -(-w // s)
+        ph, pw = max((oh - 1) * s + k - h, 0) // 2, max((ow - 1) * s + k - w, 0) // 2
+        ref = np.zeros((2, oh, ow, 4))
+        for oy in range(oh):
+            for ox in range(ow):
+                for kh in range(k):
+                    for kw in range(k):
+                        iy, ix = oy * s - ph + kh, ox * s - pw + kw
+                        if 0 <= iy < h and 0 <= ix < w:
+                            ref[:, oy, ox] += x[:, iy, ix] @ wk[kh, kw]
+        got = torch.nn.functional.conv2d(O._same_pad(torch.tensor(x).permute(0, 3, 1, 2), k, s),
+                                         torch.tensor(wk).permute(3, 2, 0, 1), stride=s).permute(0, 2, 3, 1).numpy()
+        np.testing.assert_allclose(got, ref, rtol=1e-12, atol=1e-12)
+    plan = ("plain", "down")
+    p = O.init_params(plan, 64, 10, seed=1, stem_ksize=7)
+    img = rng.uniform(-1, 1, (2, 32, 32, 3)).astype(np.float32)
+    r = O.forward_backward(p, plan, img, rng.integers(0, 10, (2,)), torch.float64, keep=True)
+    out, _ = O.maxpool3s2_same(r["acts"]["stem_a"])
+    assert np.array_equal(out, r["acts"]["h0"]) and r["acts"]["h0"].shape == (2, 8, 8, 64)
+    assert r["grads"]["stem_kernel"].shape == (7, 7, 3, 64) and np.abs(r["grads"]["stem_kernel"]).max() > 0
+    assert O.bireal18_plan().count("down") == 3 and len(O.bireal18_plan()) == 16
