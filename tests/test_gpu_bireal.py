@@ -65,6 +65,40 @@ def test_quantizer_scale_backward_and_head_kernels(native_lib):
     assert _rel(dbk.cpu().numpy(), dy.double().sum(0).cpu().numpy()) < 1e-6
 
 
+@pytest.mark.parametrize("M,K,N,ld", [(5000, 64, 128, 128), (777, 70, 10, 12), (130, 512, 1000, 1000), (1, 3, 5, 5),
+                                      (20000, 128, 256, 256)])
+def test_float_gemm_all_directions(native_lib, M, K, N, ld):
+    """zkb_dense_f32_fwd / _bwd (classifier and 1x1 shortcut conv): ragged and tile-aligned shapes, a
+    row pitch wider than N, outputs written (not accumulated) whatever they held before."""
+    from zookeeper_b200 import native as zn
+
+    g = torch.Generator(device="cpu").manual_seed(M + K)
+    x = torch.randn(M, K, generator=g).cuda()
+    w = (torch.randn(K, N, generator=g) * 0.1).cuda()
+    b = torch.randn(N, generator=g).cuda()
+    y = torch.full((M, ld), 7.0, device="cuda")
+    zn.call("zkb_dense_f32_fwd", zn.ptr(x), zn.ptr(w), zn.ptr(b), zn.ptr(y), M, K, N, ld, 0)
+    torch.cuda.synchronize()
+    ref = x.double() @ w.double() + b.double()
+    assert _rel(y[:, :N].cpu().numpy(), ref.cpu().numpy()) < 1e-6
+    assert bool((y[:, N:] == 7.0).all()), "columns past N were written"
+    dy = torch.zeros(M, ld, device="cuda")
+    dy[:, :N] = torch.randn(M, N, generator=g).cuda()
+    dy[:, N:] = 1e6          # padding columns must not be read
+    dx, dw, db = torch.full((M, K), 3.0, device="cuda"), torch.full((K, N), 3.0, device="cuda"), torch.full((N,), 3.0, device="cuda")
+    zn.call("zkb_dense_f32_bwd", zn.ptr(x), zn.ptr(w), zn.ptr(dy), ld, zn.ptr(dx), zn.ptr(dw), zn.ptr(db), M, K, N, 0)
+    torch.cuda.synchronize()
+    d64 = dy[:, :N].double()
+    assert _rel(dx.cpu().numpy(), (d64 @ w.double().T).cpu().numpy()) < 1e-6
+    assert _rel(dw.cpu().numpy(), (x.double().T @ d64).cpu().numpy()) < 2e-6
+    assert _rel(db.cpu().numpy(), d64.sum(0).cpu().numpy()) < 2e-6
+    # optional outputs
+    dw2 = torch.full((K, N), 3.0, device="cuda")
+    zn.call("zkb_dense_f32_bwd", zn.ptr(x), zn.ptr(w), zn.ptr(dy), ld, 0, zn.ptr(dw2), 0, M, K, N, 0)
+    torch.cuda.synchronize()
+    assert _rel(dw2.cpu().numpy(), (x.double().T @ d64).cpu().numpy()) < 2e-6
+
+
 @pytest.mark.parametrize("H,W", [(14, 14), (7, 5), (8, 6)])
 def test_stem_maxpool_3x3_stride2_same(native_lib, H, W):
     from oracle import bireal_oracle as O
@@ -238,10 +272,16 @@ def test_whole_net_with_stem_train_step_matches_oracle(native_lib, plan, hw, B, 
     bad = {k: f"{r:.3g}" for k, r in worst.items() if not r < REL_TOL}
     assert not bad, f"gradients outside 1e-4: {bad}"
     # optimizer: the stem kernel is a float Conv2D -- Adam without the clip
-    zero = {k: np.zeros_like(v) for k, v in p.items()}
-    exp32, _, _ = O.adam_step(p, {k: g[k] for k in p}, zero, zero, 1, dtype=np.float32)
+    # (step 1 of Adam moves every weight by ~lr * sign(g): the expectation is built from the gradients of
+    # the SAME pass -- the weight-gradient sums are atomic, so a gradient within rounding of zero may
+    # change sign between two passes over the same batch)
     eng.train_step(torch.as_tensor(img).cuda(), torch.as_tensor(lab).cuda(), apply_update=True)
     torch.cuda.synchronize()
+    g2 = eng.get_grads()
+    for k in p:
+        assert _rel(g2[k], g[k]) < 1e-5, f"second pass over the same batch: grad {k}"
+    zero = {k: np.zeros_like(v) for k, v in p.items()}
+    exp32, _, _ = O.adam_step(p, {k: g2[k] for k in p}, zero, zero, 1, dtype=np.float32)
     got = eng.get_params()
     for k in p:
         assert _rel(got[k], exp32[k]) < 2e-6, f"adam kernel {k}"

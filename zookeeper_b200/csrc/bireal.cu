@@ -283,57 +283,95 @@ global_avgpool_bwd_kernel(const float* __restrict__ dout, int B, int HW, int C, 
   }
 }
 
-// Float classifier (tf.keras.layers.Dense after the pooling): y = x W + b.  The head is tiny next
-// to the binary body (B x C x classes), so these are plain SIMT kernels with f32 FMA chains.
-__global__ void __launch_bounds__(256)
-dense_f32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                     float* __restrict__ y, int M, int K, int N, int ldy) {
-  const long long total = static_cast<long long>(M) * N;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int n = static_cast<int>(i % N);
-    const long long m = i / N;
-    float acc = bias ? bias[n] : 0.f;
-    const float* xr = x + m * K;
-    for (int k = 0; k < K; ++k) acc = fmaf(xr[k], w[static_cast<long long>(k) * N + n], acc);
-    y[m * ldy + n] = acc;
-  }
-}
+// Float GEMMs of the zoo models: the classifier (tf.keras.layers.Dense after the pooling) and the
+// 1x1 shortcut convolution of a down-sampling unit over the [pixels, C] view of the map -- the latter
+// at 200 704 x 64 x 128 per direction for Bi-Real-Net-18 at batch 256, about 1.8 % of the model's
+// multiply-adds but float x float, so not work for the +-1 GEMM engines.  One register-tiled FP32
+// kernel serves all three directions:
+//     C[i][j] (+)= sum_r A(i,r) * B(r,j) (+ bias[j])
+//     A(i,r) = AT ? A[r*lda + i] : A[i*lda + r]        B(r,j) = BT ? B[j*ldb + r] : B[r*ldb + j]
+// forward  y  = x w + b      : A = x,  B = w           (I, J, R) = (M, N, K)
+// dgrad    dx = dy w^T       : A = dy, B = w    (BT)   (I, J, R) = (M, K, N)
+// wgrad    dw = x^T dy, db   : A = x (AT), B = dy      (I, J, R) = (K, N, M), the reduction split over
+//                              blockIdx.y and added atomically into a zeroed dw / db
+// Tile 128 (i) x 64 (j) x 16 (r), 256 threads, 8 x 4 outputs per thread; scalar global loads, so no
+// alignment or divisibility rule on any dimension (the 10- and 1000-class heads are ragged).
+constexpr int kSgI = 128, kSgJ = 64, kSgR = 16;
 
-// dx[m][k] = sum_n dy[m][n] w[k][n]
+template <bool AT, bool BT, bool SPLIT>
 __global__ void __launch_bounds__(256)
-dense_f32_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w, float* __restrict__ dx,
-                       int M, int K, int N, int lddy) {
-  const long long total = static_cast<long long>(M) * K;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int k = static_cast<int>(i % K);
-    const long long m = i / K;
-    const float* wr = w + static_cast<long long>(k) * N;
-    const float* dr = dy + m * lddy;
-    float acc = 0.f;
-    for (int n = 0; n < N; ++n) acc = fmaf(dr[n], wr[n], acc);
-    dx[i] = acc;
-  }
-}
+sgemm_f32_kernel(const float* __restrict__ A, long long lda, const float* __restrict__ Bm, long long ldb,
+                 float* __restrict__ C, long long ldc, const float* __restrict__ bias, float* __restrict__ colsum,
+                 int I, int J, int R, int r_chunk, int j_tiles) {
+  __shared__ __align__(16) float sA[kSgR][kSgI + 4];
+  __shared__ __align__(16) float sB[kSgR][kSgJ + 4];
+  const int ti = blockIdx.x / j_tiles, tj = blockIdx.x - ti * j_tiles;
+  const int i0 = ti * kSgI, j0 = tj * kSgJ;
+  const int r_lo = SPLIT ? static_cast<int>(blockIdx.y) * r_chunk : 0;
+  const int r_hi = SPLIT ? (r_lo + r_chunk < R ? r_lo + r_chunk : R) : R;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  float acc[8][4];
+#pragma unroll
+  for (int a = 0; a < 8; ++a) acc[a][0] = acc[a][1] = acc[a][2] = acc[a][3] = 0.f;
+  float cs[4] = {0.f, 0.f, 0.f, 0.f};
+  const bool do_colsum = SPLIT && colsum != nullptr && ti == 0 && ty == 0;
 
-// dw[k][n] = sum_m x[m][k] dy[m][n];  db[n] = sum_m dy[m][n]   (written, not accumulated)
-__global__ void __launch_bounds__(256)
-dense_f32_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dw,
-                       float* __restrict__ db, int M, int K, int N, int lddy) {
-  const long long total = static_cast<long long>(K + 1) * N;
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int n = static_cast<int>(i % N);
-    const long long k = i / N;
-    float acc = 0.f;
-    if (k < K) {
-      for (int m = 0; m < M; ++m) acc = fmaf(x[static_cast<long long>(m) * K + k], dy[static_cast<long long>(m) * lddy + n], acc);
-      dw[k * N + n] = acc;
-    } else if (db) {
-      for (int m = 0; m < M; ++m) acc += dy[static_cast<long long>(m) * lddy + n];
-      db[n] = acc;
+  for (int r0 = r_lo; r0 < r_hi; r0 += kSgR) {
+    __syncthreads();
+    // A tile: kSgR x kSgI
+    for (int e = threadIdx.x; e < kSgR * kSgI; e += 256) {
+      int rr, ii;
+      if (AT) { rr = e / kSgI; ii = e - rr * kSgI; }     // memory runs along i
+      else    { ii = e / kSgR; rr = e - ii * kSgR; }     // memory runs along r
+      const int r = r0 + rr, i = i0 + ii;
+      float v = 0.f;
+      if (r < r_hi && i < I) v = AT ? __ldg(A + static_cast<long long>(r) * lda + i) : __ldg(A + static_cast<long long>(i) * lda + r);
+      sA[rr][ii] = v;
     }
+    for (int e = threadIdx.x; e < kSgR * kSgJ; e += 256) {
+      int rr, jj;
+      if (BT) { jj = e / kSgR; rr = e - jj * kSgR; }
+      else    { rr = e / kSgJ; jj = e - rr * kSgJ; }
+      const int r = r0 + rr, j = j0 + jj;
+      float v = 0.f;
+      if (r < r_hi && j < J) v = BT ? __ldg(Bm + static_cast<long long>(j) * ldb + r) : __ldg(Bm + static_cast<long long>(r) * ldb + j);
+      sB[rr][jj] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int rr = 0; rr < kSgR; ++rr) {
+      const float4 a0 = *reinterpret_cast<const float4*>(&sA[rr][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&sA[rr][64 + ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&sB[rr][tx * 4]);
+      const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[a][c] = fmaf(av[a], bv[c], acc[a][c]);
+      if (do_colsum) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) cs[c] += bv[c];
+      }
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < 8; ++a) {
+    const int i = i0 + (a < 4 ? ty * 4 + a : 64 + ty * 4 + (a - 4));
+    if (i >= I) continue;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int j = j0 + tx * 4 + c;
+      if (j >= J) continue;
+      float* o = C + static_cast<long long>(i) * ldc + j;
+      if (SPLIT) atomicAdd(o, acc[a][c]);
+      else *o = acc[a][c] + (bias ? __ldg(bias + j) : 0.f);
+    }
+  }
+  if (do_colsum) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (j0 + tx * 4 + c < J) atomicAdd(colsum + j0 + tx * 4 + c, cs[c]);
   }
 }
 
@@ -544,8 +582,10 @@ ZKB_API int zkb_dense_f32_fwd(const float* x, const float* w_k_n, const float* b
                               int N, int ldy, void* stream) {
   ZKB_REQUIRE(x && w_k_n && y && M >= 0 && K > 0 && N > 0 && ldy >= N, "dense_f32_fwd: bad arguments");
   if (M == 0) return ZKB_OK;
-  dense_f32_fwd_kernel<<<br_grid(static_cast<long long>(M) * N), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, w_k_n, bias, y, M, K, N, ldy);
-  ZKB_LAUNCH_CHECK("dense_f32_fwd_kernel");
+  const int it = (M + kSgI - 1) / kSgI, jt = (N + kSgJ - 1) / kSgJ;
+  sgemm_f32_kernel<false, false, false><<<dim3(static_cast<unsigned>(it) * jt, 1), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, K, w_k_n, N, y, ldy, bias, nullptr, M, N, K, 0, jt);
+  ZKB_LAUNCH_CHECK("sgemm_f32_kernel (forward)");
   return ZKB_OK;
 }
 
@@ -554,11 +594,26 @@ ZKB_API int zkb_dense_f32_bwd(const float* x, const float* w_k_n, const float* d
   ZKB_REQUIRE(x && w_k_n && dy && dw_k_n && M > 0 && K > 0 && N > 0 && lddy >= N, "dense_f32_bwd: bad arguments");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dx) {
-    dense_f32_dgrad_kernel<<<br_grid(static_cast<long long>(M) * K), 256, 0, st>>>(dy, w_k_n, dx, M, K, N, lddy);
-    ZKB_LAUNCH_CHECK("dense_f32_dgrad_kernel");
+    const int it = (M + kSgI - 1) / kSgI, jt = (K + kSgJ - 1) / kSgJ;
+    sgemm_f32_kernel<false, true, false><<<dim3(static_cast<unsigned>(it) * jt, 1), 256, 0, st>>>(
+        dy, lddy, w_k_n, N, dx, K, nullptr, nullptr, M, K, N, 0, jt);
+    ZKB_LAUNCH_CHECK("sgemm_f32_kernel (dgrad)");
   }
-  dense_f32_wgrad_kernel<<<br_grid(static_cast<long long>(K + 1) * N), 256, 0, st>>>(x, dy, dw_k_n, dbias, M, K, N, lddy);
-  ZKB_LAUNCH_CHECK("dense_f32_wgrad_kernel");
+  // dw = x^T dy over M rows: split the rows so that the grid fills the GPU a few times over; the
+  // partial tiles are added into a zeroed dw (and dbias)
+  ZKB_CUDA(cudaMemsetAsync(dw_k_n, 0, static_cast<size_t>(K) * N * sizeof(float), st));
+  if (dbias) ZKB_CUDA(cudaMemsetAsync(dbias, 0, static_cast<size_t>(N) * sizeof(float), st));
+  const int it = (K + kSgI - 1) / kSgI, jt = (N + kSgJ - 1) / kSgJ;
+  int splits = (4 * zkb_sm_count() + it * jt - 1) / (it * jt);
+  const int max_splits = (M + 4 * kSgR - 1) / (4 * kSgR);      // at least 64 rows per block
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  int r_chunk = (M + splits - 1) / splits;
+  r_chunk = (r_chunk + kSgR - 1) / kSgR * kSgR;
+  splits = (M + r_chunk - 1) / r_chunk;
+  sgemm_f32_kernel<true, false, true><<<dim3(static_cast<unsigned>(it) * jt, static_cast<unsigned>(splits)), 256, 0, st>>>(
+      x, K, dy, lddy, dw_k_n, N, nullptr, dbias, K, N, M, r_chunk, jt);
+  ZKB_LAUNCH_CHECK("sgemm_f32_kernel (wgrad)");
   return ZKB_OK;
 }
 
