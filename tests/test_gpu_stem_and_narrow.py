@@ -28,6 +28,10 @@ def _rel(got, ref):
     (2, 12, 12, 128, 64, 3, 1),      # narrow output
     (2, 12, 12, 128, 256, 5, 1),     # 5x5 kernel on the int8 path
     (2, 10, 9, 64, 128, 5, 1),       # 5x5 kernel, 64 input channels
+    (2, 27, 27, 64, 192, 5, 1),      # BinaryAlexNet block 2 (output channels not a multiple of the MMA tile)
+    (2, 13, 13, 192, 384, 3, 1),     # ... block 3
+    (2, 13, 13, 384, 384, 3, 1),     # ... block 4
+    (3, 13, 13, 384, 256, 3, 1),     # ... block 5
 ], ids=lambda v: str(v))
 def test_binary_conv_narrow_and_5x5(native_lib, B, H, W, Cin, Cout, ks, stride):
     from zookeeper_b200 import native as zn
