@@ -342,6 +342,16 @@ int zkb_maxpool3s2_f32_fwd(const float* x, int B, int H, int W, int C, float* ou
                            void* stream);
 int zkb_maxpool3s2_f32_bwd(const float* dout, const uint8_t* arg, int B, int H, int W, int C, float* dx,
                            void* stream);
+/* The same pool for either padding and for the INTEGER conv outputs BinaryAlexNet pools between a
+ * QuantConv2D and its BatchNormalization (larq-zoo; MaxPool2D(pool_size=3, strides=2), "valid":
+ * out = (in - 3) / 2 + 1): x / out int16 (x_is_i16 = 1) or f32, same != 0 for "same" padding.  The
+ * backward gathers (every input pixel sums the windows it won; overlapping windows need no atomics)
+ * and writes either dx_f32 or the bf16 pair dx_hi / dx_lo the backward GEMMs read -- pass the other
+ * as NULL. */
+int zkb_maxpool3s2_fwd(const void* x, int x_is_i16, int B, int H, int W, int C, int same, void* out,
+                       uint8_t* arg, void* stream);
+int zkb_maxpool3s2_bwd(const float* dout, const uint8_t* arg, int B, int H, int W, int C, int same,
+                       float* dx_f32, void* dx_hi, void* dx_lo, void* stream);
 /* Float stem convolutions on the 3-channel image x f32 [B,H,W,3] with TensorFlow 'same' padding:
  * Conv2D(Cout, 7, strides=2) of Bi-Real-Net-18 and the 11x11 / stride-4 first layer of BinaryAlexNet
  * (pass the quantised kernel for a QuantConv2D).  w / dw: f32 HWIO [ksize,ksize,3,Cout], Cout % 64 == 0;

@@ -394,8 +394,10 @@ struct StatAcc<float, VEC> {
 template <typename T>
 __global__ void __launch_bounds__(256)
 bn_stats_kernel(const T* __restrict__ x, long long rows, int C, double* __restrict__ sum,
-                double* __restrict__ sumsq) {
+                double* __restrict__ sumsq, long long ld = 0) {
+  // ld: row pitch in elements when this launch covers a column slice of a wider map (0: pitch = C)
   constexpr int VEC = Vec16<T>::N;
+  const long long pitch = ld ? ld : C;
   const int tpr = C / VEC;
   const int lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr;
@@ -413,17 +415,17 @@ bn_stats_kernel(const T* __restrict__ x, long long rows, int C, double* __restri
     // four independent 16-byte loads in flight per thread
     for (; r + 3 * step < rows; r += 4 * step) {
       Vec16<T> v0, v1, v2, v3;
-      v0.load(px + r * C);
-      v1.load(px + (r + step) * C);
-      v2.load(px + (r + 2 * step) * C);
-      v3.load(px + (r + 3 * step) * C);
+      v0.load(px + r * pitch);
+      v1.load(px + (r + step) * pitch);
+      v2.load(px + (r + 2 * step) * pitch);
+      v3.load(px + (r + 3 * step) * pitch);
       acc.add(v0); acc.add(v1); acc.add(v2); acc.add(v3);
       n += 4;
       if (n >= StatAcc<T, VEC>::kFlush - 3) { acc.flush(a0, a1); n = 0; }
     }
     for (; r < rows; r += step) {
       Vec16<T> v;
-      v.load(px + r * C);
+      v.load(px + r * pitch);
       acc.add(v);
       if (++n >= StatAcc<T, VEC>::kFlush - 3) { acc.flush(a0, a1); n = 0; }
     }
@@ -459,8 +461,9 @@ __global__ void __launch_bounds__(256)
 bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const float* __restrict__ beta,
                      uint16_t* __restrict__ s_out, float* __restrict__ a_out,
-                     int8_t* __restrict__ s8_out = nullptr) {
+                     int8_t* __restrict__ s8_out = nullptr, long long ld = 0) {
   constexpr int VEC = Vec16<T>::N;
+  const long long pitch = ld ? ld : C;     // row pitch of x and of every output (see bn_stats_kernel)
   const int tpr = C / VEC;
   const long long total = rows * tpr;
   // blockDim and the grid stride are multiples of tpr, so a thread keeps one channel group:
@@ -478,8 +481,8 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
    // two independent rows per iteration: both loads are issued before either is consumed
    Vec16<T> vv[2];
    const bool has2 = i0 + gstride < total;
-   vv[0].load(x + (i0 / tpr) * C + cl * VEC);
-   if (has2) vv[1].load(x + ((i0 + gstride) / tpr) * C + cl * VEC);
+   vv[0].load(x + (i0 / tpr) * pitch + cl * VEC);
+   if (has2) vv[1].load(x + ((i0 + gstride) / tpr) * pitch + cl * VEC);
 #pragma unroll
    for (int u = 0; u < 2; ++u) {
     if (u == 1 && !has2) break;
@@ -493,7 +496,7 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
       s[j] = pm1_bf16(a[j] >= 0.0f);
     }
     if (s_out) {
-      uint16_t* o = s_out + r * C + cl * VEC;
+      uint16_t* o = s_out + r * pitch + cl * VEC;
       if (VEC == 8) {
         *reinterpret_cast<uint4*>(o) =
             make_uint4(s[0] | (uint32_t(s[1]) << 16), s[2] | (uint32_t(s[3]) << 16),
@@ -514,12 +517,12 @@ bn_apply_sign_kernel(const T* __restrict__ x, long long rows, int C, const float
           w8[q] |= ((s[4 * q + e] & 0x8000u) ? 0xFFu : 0x01u) << (8 * e);
       }
       if (VEC == 8)
-        *reinterpret_cast<uint2*>(s8_out + r * C + cl * VEC) = make_uint2(w8[0], w8[(VEC / 4) - 1]);
+        *reinterpret_cast<uint2*>(s8_out + r * pitch + cl * VEC) = make_uint2(w8[0], w8[(VEC / 4) - 1]);
       else
-        *reinterpret_cast<uint32_t*>(s8_out + r * C + cl * VEC) = w8[0];
+        *reinterpret_cast<uint32_t*>(s8_out + r * pitch + cl * VEC) = w8[0];
     }
     if (a_out) {
-      float* o = a_out + r * C + cl * VEC;
+      float* o = a_out + r * pitch + cl * VEC;
 #pragma unroll
       for (int j = 0; j < VEC; j += 4)
         *reinterpret_cast<float4*>(o + j) = make_float4(a[j], a[j + 1], a[j + 2], a[j + 3]);
@@ -730,8 +733,9 @@ __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long long rows, int C,
                      const float* __restrict__ mean, const float* __restrict__ rstd,
                      const float* __restrict__ beta, int ste, double* __restrict__ sum_da,
-                     double* __restrict__ sum_dax) {
+                     double* __restrict__ sum_dax, long long ld = 0) {
   constexpr int VEC = 4;  // g is f32: 4 channels per 16 B
+  const long long pitch = ld ? ld : C;     // row pitch of g and x (see bn_stats_kernel)
   const int tpr = C / VEC;
   const int lanes = blockDim.x / tpr;
   const int cl = threadIdx.x % tpr;
@@ -755,8 +759,8 @@ bn_bwd_reduce_kernel(const float* __restrict__ g, const T* __restrict__ x, long 
       for (int u = 0; u < 4; ++u) {
         const long long r = r0 + u * step;
         if (r < rows) {
-          load4(g + r * C + cl * VEC, gg[u]);
-          load4(x + r * C + cl * VEC, xv[u]);
+          load4(g + r * pitch + cl * VEC, gg[u]);
+          load4(x + r * pitch + cl * VEC, xv[u]);
         } else {
 #pragma unroll
           for (int j = 0; j < 4; ++j) { gg[u][j] = 0.f; xv[u][j] = mu[j]; }   // contributes nothing
@@ -810,8 +814,10 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
                     const float* __restrict__ beta, const float* __restrict__ mean_da,
                     const float* __restrict__ mean_dax, int ste, int out_mode,
                     float* __restrict__ out_f32, uint16_t* __restrict__ out_hi,
-                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W) {
+                    uint16_t* __restrict__ out_lo, const uint8_t* __restrict__ arg, int H, int W,
+                    long long ld = 0) {
   constexpr int VEC = 4;
+  const long long pitch = ld ? ld : C;     // row pitch of g, x and the outputs (modes 0, 1; see bn_stats_kernel)
   const int tpr = C / VEC;
   const long long total = rows * tpr;
   const int PH = H / 2, PW = W / 2;
@@ -826,10 +832,10 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long r = i / tpr;
-    const float4 gv = *reinterpret_cast<const float4*>(g + r * C + cl * VEC);
+    const float4 gv = *reinterpret_cast<const float4*>(g + r * pitch + cl * VEC);
     const float gg[4] = {gv.x, gv.y, gv.z, gv.w};
     float xv[4];
-    load4(x + r * C + cl * VEC, xv);
+    load4(x + r * pitch + cl * VEC, xv);
     float dx[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
@@ -839,7 +845,7 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
       dx[j] = rs[j] * (da - mda[j] - xh * mdx[j]);
     }
     if (out_mode == 0) {
-      *reinterpret_cast<float4*>(out_f32 + r * C + cl * VEC) = make_float4(dx[0], dx[1], dx[2], dx[3]);
+      *reinterpret_cast<float4*>(out_f32 + r * pitch + cl * VEC) = make_float4(dx[0], dx[1], dx[2], dx[3]);
       continue;
     }
     uint16_t hi[VEC], lo[VEC];
@@ -849,9 +855,9 @@ bn_bwd_apply_kernel(const float* __restrict__ g, const T* __restrict__ x, long l
       lo[j] = f32_to_bf16_rn(dx[j] - bf16_to_f32(hi[j]));
     }
     if (out_mode == 1) {
-      *reinterpret_cast<uint2*>(out_hi + r * C + cl * VEC) =
+      *reinterpret_cast<uint2*>(out_hi + r * pitch + cl * VEC) =
           make_uint2(hi[0] | (uint32_t(hi[1]) << 16), hi[2] | (uint32_t(hi[3]) << 16));
-      *reinterpret_cast<uint2*>(out_lo + r * C + cl * VEC) =
+      *reinterpret_cast<uint2*>(out_lo + r * pitch + cl * VEC) =
           make_uint2(lo[0] | (uint32_t(lo[1]) << 16), lo[2] | (uint32_t(lo[3]) << 16));
     } else {
       const int pw = static_cast<int>(r % PW);
@@ -1121,32 +1127,47 @@ ZKB_API int zkb_conv_first_wgrad(const float* x, const float* dy, float* dw_k_co
   return ZKB_OK;
 }
 
-static int check_rows_c(const char* who, const void* x, long long rows, int C, int vec) {
+// wide != 0: maps wider than 256 vectors per row are allowed (the launcher walks column slices)
+static int check_rows_c(const char* who, const void* x, long long rows, int C, int vec, int wide = 0) {
   ZKB_REQUIRE(x, "%s: null pointer", who);
   ZKB_REQUIRE(rows >= 0 && C > 0, "%s: bad shape", who);
-  ZKB_REQUIRE(C % vec == 0 && C / vec <= 256 && 256 % (C / vec) == 0,
-              "%s: C=%d must be a multiple of %d with C/%d dividing 256", who, C, vec, vec);
+  ZKB_REQUIRE(C % vec == 0 && (wide || C / vec <= 256), "%s: C=%d must be a multiple of %d%s", who, C, vec,
+              wide ? "" : ", at most 256 vectors per row");
   ZKB_REQUIRE(ZKB_ALIGNED16(x), "%s: tensor must be 16-byte aligned", who);
   return ZKB_OK;
 }
 
+// Column slices of a [rows, C] map for the per-channel kernels: a thread owns one 16-byte vector of
+// channels, a block at most 256 of them, so wider maps (the 4096-unit dense layers of BinaryAlexNet)
+// are walked in slices of 256 vectors with the full row as pitch.
+static int slice_width(int C, int vec) { return C / vec <= 256 ? C : 256 * vec; }
+
+// Threads per block of the per-channel kernels: a thread keeps ONE 16-byte vector of channels for the
+// whole launch, so the block is a whole number of rows -- 256 threads when the vectors per row divide
+// 256 (every layer of BinaryNet), the largest multiple below otherwise (192 / 384 channels).
+static int row_block(int vectors_per_row) { return (256 / vectors_per_row) * vectors_per_row; }
+
 ZKB_API int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum,
                          double* sumsq, void* stream) {
   const int vec = x_is_i16 ? 8 : 4;
-  int rc = check_rows_c("bn_stats", x, rows, C, vec);
+  int rc = check_rows_c("bn_stats", x, rows, C, vec, 1);
   if (rc) return rc;
   ZKB_REQUIRE(sum && sumsq, "bn_stats: null accumulator");
   if (rows == 0) return ZKB_OK;
-  const int lanes = 256 / (C / vec);
-  const int grid = reduce_grid(rows, lanes);
   const size_t smem = 0;
-  if (x_is_i16)
-    bn_stats_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const int16_t*>(x), rows, C, sum, sumsq);
-  else
-    bn_stats_kernel<float><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const float*>(x), rows, C, sum, sumsq);
-  ZKB_LAUNCH_CHECK("bn_stats_kernel");
+  const int sw = slice_width(C, vec);
+  for (int c0 = 0; c0 < C; c0 += sw) {
+    const int cc = C - c0 < sw ? C - c0 : sw;
+    const int lanes = 256 / (cc / vec);
+    const int grid = reduce_grid(rows, lanes);
+    if (x_is_i16)
+      bn_stats_kernel<int16_t><<<grid, row_block(cc / vec), smem, static_cast<cudaStream_t>(stream)>>>(
+          static_cast<const int16_t*>(x) + c0, rows, cc, sum + c0, sumsq + c0, C);
+    else
+      bn_stats_kernel<float><<<grid, row_block(cc / vec), smem, static_cast<cudaStream_t>(stream)>>>(
+          static_cast<const float*>(x) + c0, rows, cc, sum + c0, sumsq + c0, C);
+    ZKB_LAUNCH_CHECK("bn_stats_kernel");
+  }
   return ZKB_OK;
 }
 
@@ -1197,21 +1218,26 @@ ZKB_API int zkb_bn_apply_sign(const void* x, int x_is_i16, long long rows, int C
                               const float* rstd, const float* beta, void* s_out_bf16, float* a_out,
                               void* s_out_i8, void* stream) {
   const int vec = x_is_i16 ? 8 : 4;
-  int rc = check_rows_c("bn_apply_sign", x, rows, C, vec);
+  int rc = check_rows_c("bn_apply_sign", x, rows, C, vec, 1);
   if (rc) return rc;
   ZKB_REQUIRE(mean && rstd && beta, "bn_apply_sign: null statistics");
   ZKB_REQUIRE(s_out_bf16 || a_out || s_out_i8, "bn_apply_sign: no output requested");
   if (rows == 0) return ZKB_OK;
-  const int grid = grid_for(rows * (C / vec), 256, 16);
-  if (x_is_i16)
-    bn_apply_sign_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const int16_t*>(x), rows, C, mean, rstd, beta,
-        static_cast<uint16_t*>(s_out_bf16), a_out, static_cast<int8_t*>(s_out_i8));
-  else
-    bn_apply_sign_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        static_cast<const float*>(x), rows, C, mean, rstd, beta, static_cast<uint16_t*>(s_out_bf16),
-        a_out, static_cast<int8_t*>(s_out_i8));
-  ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
+  const int sw = slice_width(C, vec);
+  for (int c0 = 0; c0 < C; c0 += sw) {
+    const int cc = C - c0 < sw ? C - c0 : sw;
+    const int grid = grid_for(rows * (cc / vec), 256, 16);
+    uint16_t* so = s_out_bf16 ? static_cast<uint16_t*>(s_out_bf16) + c0 : nullptr;
+    float* ao = a_out ? a_out + c0 : nullptr;
+    int8_t* s8 = s_out_i8 ? static_cast<int8_t*>(s_out_i8) + c0 : nullptr;
+    if (x_is_i16)
+      bn_apply_sign_kernel<int16_t><<<grid, row_block(cc / vec), 0, static_cast<cudaStream_t>(stream)>>>(
+          static_cast<const int16_t*>(x) + c0, rows, cc, mean + c0, rstd + c0, beta + c0, so, ao, s8, C);
+    else
+      bn_apply_sign_kernel<float><<<grid, row_block(cc / vec), 0, static_cast<cudaStream_t>(stream)>>>(
+          static_cast<const float*>(x) + c0, rows, cc, mean + c0, rstd + c0, beta + c0, so, ao, s8, C);
+    ZKB_LAUNCH_CHECK("bn_apply_sign_kernel");
+  }
   return ZKB_OK;
 }
 
@@ -1229,7 +1255,7 @@ ZKB_API int zkb_maxpool2_i16(const void* y, int B, int H, int W, int C, void* p_
   if (gmp > static_cast<long long>(zkb_sm_count()) * 12) gmp = static_cast<long long>(zkb_sm_count()) * 12;
   const int grid = gmp < 1 ? 1 : static_cast<int>(gmp);
   const size_t smem = 0;
-  maxpool2_i16_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
+  maxpool2_i16_kernel<<<grid, row_block(C / 8), smem, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const int16_t*>(y), B, H, W, C, static_cast<int16_t*>(p_out), arg_out, sum, sumsq);
   ZKB_LAUNCH_CHECK("maxpool2_i16_kernel");
   return ZKB_OK;
@@ -1250,20 +1276,26 @@ ZKB_API int zkb_softmax_ce(const float* logits, int ld, const int* labels, int B
 ZKB_API int zkb_bn_bwd_reduce(const float* g, const void* x, int x_is_i16, long long rows, int C,
                               const float* mean, const float* rstd, const float* beta, int ste,
                               double* sum_da, double* sum_dax, void* stream) {
-  int rc = check_rows_c("bn_bwd_reduce", g, rows, C, 4);
+  int rc = check_rows_c("bn_bwd_reduce", g, rows, C, 4, 1);
   if (rc) return rc;
   ZKB_REQUIRE(x && mean && rstd && beta && sum_da && sum_dax, "bn_bwd_reduce: null pointer");
   if (rows == 0) return ZKB_OK;
-  const int lanes = 256 / (C / 4);
-  const int grid = reduce_grid(rows, lanes);
   const size_t smem = 0;
-  if (x_is_i16)
-    bn_bwd_reduce_kernel<int16_t><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
-        g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, ste, sum_da, sum_dax);
-  else
-    bn_bwd_reduce_kernel<float><<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(
-        g, static_cast<const float*>(x), rows, C, mean, rstd, beta, ste, sum_da, sum_dax);
-  ZKB_LAUNCH_CHECK("bn_bwd_reduce_kernel");
+  const int sw = slice_width(C, 4);
+  for (int c0 = 0; c0 < C; c0 += sw) {
+    const int cc = C - c0 < sw ? C - c0 : sw;
+    const int lanes = 256 / (cc / 4);
+    const int grid = reduce_grid(rows, lanes);
+    if (x_is_i16)
+      bn_bwd_reduce_kernel<int16_t><<<grid, row_block(cc / 4), smem, static_cast<cudaStream_t>(stream)>>>(
+          g + c0, static_cast<const int16_t*>(x) + c0, rows, cc, mean + c0, rstd + c0, beta + c0, ste, sum_da + c0,
+          sum_dax + c0, C);
+    else
+      bn_bwd_reduce_kernel<float><<<grid, row_block(cc / 4), smem, static_cast<cudaStream_t>(stream)>>>(
+          g + c0, static_cast<const float*>(x) + c0, rows, cc, mean + c0, rstd + c0, beta + c0, ste, sum_da + c0,
+          sum_dax + c0, C);
+    ZKB_LAUNCH_CHECK("bn_bwd_reduce_kernel");
+  }
   return ZKB_OK;
 }
 
@@ -1283,7 +1315,7 @@ ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long l
                              const float* mean_da, const float* mean_dax, int ste, int out_mode,
                              float* out_f32, void* out_hi, void* out_lo, const uint8_t* arg, int H,
                              int W, void* stream) {
-  int rc = check_rows_c("bn_bwd_apply", g, rows, C, 4);
+  int rc = check_rows_c("bn_bwd_apply", g, rows, C, 4, out_mode != 2);
   if (rc) return rc;
   ZKB_REQUIRE(x && mean && rstd && beta && mean_da && mean_dax, "bn_bwd_apply: null pointer");
   ZKB_REQUIRE(out_mode >= 0 && out_mode <= 2, "bn_bwd_apply: out_mode must be 0, 1 or 2");
@@ -1295,16 +1327,23 @@ ZKB_API int zkb_bn_bwd_apply(const float* g, const void* x, int x_is_i16, long l
                 "bn_bwd_apply: rows is not a multiple of the pooled map size");
   }
   if (rows == 0) return ZKB_OK;
-  const int grid = grid_for(rows * (C / 4), 256, 16);
-  if (x_is_i16)
-    bn_bwd_apply_kernel<int16_t><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        g, static_cast<const int16_t*>(x), rows, C, mean, rstd, beta, mean_da, mean_dax, ste,
-        out_mode, out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W);
-  else
-    bn_bwd_apply_kernel<float><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        g, static_cast<const float*>(x), rows, C, mean, rstd, beta, mean_da, mean_dax, ste,
-        out_mode, out_f32, static_cast<uint16_t*>(out_hi), static_cast<uint16_t*>(out_lo), arg, H, W);
-  ZKB_LAUNCH_CHECK("bn_bwd_apply_kernel");
+  const int sw = slice_width(C, 4);      // (the pool scatter, out_mode 2, is one slice: checked above)
+  for (int c0 = 0; c0 < C; c0 += sw) {
+    const int cc = C - c0 < sw ? C - c0 : sw;
+    const int grid = grid_for(rows * (cc / 4), 256, 16);
+    float* of = out_f32 ? out_f32 + c0 : nullptr;
+    uint16_t* oh = out_hi ? static_cast<uint16_t*>(out_hi) + c0 : nullptr;
+    uint16_t* ol = out_lo ? static_cast<uint16_t*>(out_lo) + c0 : nullptr;
+    if (x_is_i16)
+      bn_bwd_apply_kernel<int16_t><<<grid, row_block(cc / 4), 0, static_cast<cudaStream_t>(stream)>>>(
+          g + c0, static_cast<const int16_t*>(x) + c0, rows, cc, mean + c0, rstd + c0, beta + c0, mean_da + c0,
+          mean_dax + c0, ste, out_mode, of, oh, ol, arg, H, W, C);
+    else
+      bn_bwd_apply_kernel<float><<<grid, row_block(cc / 4), 0, static_cast<cudaStream_t>(stream)>>>(
+          g + c0, static_cast<const float*>(x) + c0, rows, cc, mean + c0, rstd + c0, beta + c0, mean_da + c0,
+          mean_dax + c0, ste, out_mode, of, oh, ol, arg, H, W, C);
+    ZKB_LAUNCH_CHECK("bn_bwd_apply_kernel");
+  }
   return ZKB_OK;
 }
 

@@ -83,6 +83,8 @@ SIGNATURES = {
     "zkb_dense_f32_bwd": [P, P, P, I, P, P, P, I, I, I, P],
     "zkb_maxpool3s2_f32_fwd": [P, I, I, I, I, P, P, P],
     "zkb_maxpool3s2_f32_bwd": [P, P, I, I, I, I, P, P],
+    "zkb_maxpool3s2_fwd": [P, I, I, I, I, I, I, P, P, P],
+    "zkb_maxpool3s2_bwd": [P, P, I, I, I, I, I, P, P, P, P],
     "zkb_bconv2d_fwd_i8_pool": [P, P, P, P, I, I, I, I, I, I, P, P, P],
     "zkb_bconv2d_fwd_i8_s2": [P, P, P, I, I, I, I, I, I, P],
     "zkb_bconv2d_fwd_s2": [P, P, P, I, I, I, I, I, I, P],
