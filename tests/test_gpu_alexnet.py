@@ -174,3 +174,33 @@ def test_binary_alexnet_learns(native_lib):
         (first if s < 10 else last).append(eng.last_loss())
     assert np.isfinite(last).all()
     assert np.mean(last[-10:]) < 0.6 * np.mean(first), (np.mean(first), np.mean(last[-10:]))
+
+
+@pytest.mark.parametrize("B,NC,ld", [(300, 1000, 1024), (33, 65, 128), (256, 10, 64), (5, 1000, 1000)])
+def test_softmax_cross_entropy_narrow_and_wide_heads(native_lib, B, NC, ld):
+    """Thread-per-row (<= 64 classes) and warp-per-row forms: loss sum, accuracy with the first-maximum
+    argmax on tied rows, gradient incl. zeros in the padding columns."""
+    from zookeeper_b200 import native as zn
+
+    rng = np.random.default_rng(B + NC)
+    z = rng.normal(0, 2, (B, ld)).astype(np.float32)
+    lab = rng.integers(0, NC, (B,)).astype(np.int32)
+    z[0, :NC] = 0.5                                   # all tied: argmax is class 0
+    lab[0] = 0
+    z[1, :NC] = -1.0
+    z[1, NC - 1] = z[1, NC // 2] = 3.0                # two maxima: the first one counts
+    lab[1] = NC - 1
+    zt, lt = torch.as_tensor(z).cuda(), torch.as_tensor(lab).cuda()
+    d = torch.full((B, ld), 9.0, device="cuda")
+    loss = torch.zeros(1, dtype=torch.float64, device="cuda")
+    correct = torch.zeros(1, dtype=torch.int32, device="cuda")
+    zn.call("zkb_softmax_ce", zn.ptr(zt), ld, zn.ptr(lt), B, NC, 1.0 / B, zn.ptr(d), zn.ptr(loss), zn.ptr(correct), 0)
+    torch.cuda.synchronize()
+    z64 = torch.tensor(z[:, :NC].astype(np.float64), requires_grad=True)
+    ref = torch.nn.functional.cross_entropy(z64, torch.as_tensor(lab.astype(np.int64)), reduction="sum")
+    (ref / B).backward()
+    assert abs(loss.item() - ref.item()) <= 1e-5 * abs(ref.item())
+    first_max = np.argmax(z[:, :NC], axis=1)          # numpy returns the first maximum
+    assert correct.item() == int((first_max == lab).sum())
+    assert _rel(d[:, :NC].cpu().numpy(), z64.grad.numpy()) < 1e-5
+    assert bool((d[:, NC:] == 0).all())

@@ -712,6 +712,44 @@ softmax_ce_kernel(const float* __restrict__ logits, int ld, const int* __restric
   }
 }
 
+// The same for wide heads (the 1000-class zoo models): one warp per row, lanes strided over the
+// classes -- coalesced reads and gradient writes instead of one thread walking a 4 KB row.  argmax
+// keeps the first maximum (lowest index), as the thread-per-row form does.
+__global__ void __launch_bounds__(256)
+softmax_ce_wide_kernel(const float* __restrict__ logits, int ld, const int* __restrict__ labels, int B,
+                       int NC, float inv_global_batch, float* __restrict__ dlogits,
+                       double* __restrict__ loss_sum, int* __restrict__ correct) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (b >= B) return;                       // whole warps leave together
+  const float* z = logits + static_cast<long long>(b) * ld;
+  float mx = -INFINITY;
+  int am = 0x7FFFFFFF;
+  for (int k = lane; k < NC; k += 32) {
+    const float v = z[k];
+    if (v > mx) { mx = v; am = k; }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+    if (om > mx || (om == mx && oa < am)) { mx = om; am = oa; }
+  }
+  float se = 0.f;
+  for (int k = lane; k < NC; k += 32) se += expf(z[k] - mx);
+  for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+  const float lse = logf(se) + mx;
+  const int lab = labels[b];
+  if (dlogits) {
+    float* d = dlogits + static_cast<long long>(b) * ld;
+    for (int k = lane; k < ld; k += 32)
+      d[k] = k < NC ? (expf(z[k] - lse) - (k == lab ? 1.f : 0.f)) * inv_global_batch : 0.f;
+  }
+  if (lane == 0) {
+    atomicAdd(loss_sum, static_cast<double>(lse - z[lab]));
+    if (am == lab) atomicAdd(correct, 1);
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // BatchNorm backward.  g is the gradient w.r.t. sign(a) (ste != 0: masked by |a| <= 1) or w.r.t.
 // a itself (ste == 0, last layer).  Pass 1: per-channel sum(da), sum(da * xhat).
@@ -1267,8 +1305,12 @@ ZKB_API int zkb_softmax_ce(const float* logits, int ld, const int* labels, int B
   ZKB_REQUIRE(logits && labels && loss_sum && correct, "softmax_ce: null pointer");
   ZKB_REQUIRE(num_classes > 0 && ld >= num_classes, "softmax_ce: ld < num_classes");
   if (B == 0) return ZKB_OK;
-  softmax_ce_kernel<<<(B + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      logits, ld, labels, B, num_classes, inv_global_batch, dlogits, loss_sum, correct);
+  if (num_classes > 64)      // a warp per row
+    softmax_ce_wide_kernel<<<(B + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        logits, ld, labels, B, num_classes, inv_global_batch, dlogits, loss_sum, correct);
+  else
+    softmax_ce_kernel<<<(B + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        logits, ld, labels, B, num_classes, inv_global_batch, dlogits, loss_sum, correct);
   ZKB_LAUNCH_CHECK("softmax_ce_kernel");
   return ZKB_OK;
 }
