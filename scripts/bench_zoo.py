@@ -5,6 +5,9 @@ oracle/alexnet_oracle.py and oracle/bireal_oracle.py).  One GPU; synthetic uint8
 
   python scripts/bench_zoo.py --model bireal18|alexnet [--batch 256] [--steps 10] [--warmup 3]
                               [--breakdown] [--cpu-baseline]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+         scripts/bench_zoo.py --model ...        # data-parallel: --batch per GPU (weak scaling), gradients
+                                                 # summed with NCCL, BatchNorm statistics per replica
 
 A step = fused preprocessing (zkb_preprocess_u8: gather, random crop 256 -> 224, flip, u8 -> f32)
 -> forward -> loss -> full backward -> Adam (+ latent-weight clip).  Timed with CUDA events on the
@@ -37,10 +40,17 @@ ap.add_argument("--model", choices=("bireal18", "alexnet"), default="bireal18")
 ap.add_argument("--cpu-baseline", action="store_true")
 args = ap.parse_args()
 
-dev = torch.device("cuda", 0)
+world = int(os.environ.get("WORLD_SIZE", "1"))
+rank = int(os.environ.get("RANK", "0"))
+local = int(os.environ.get("LOCAL_RANK", "0"))
+dev = torch.device("cuda", local)
 torch.cuda.set_device(dev)
+if world > 1:
+    import torch.distributed as dist
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    dist.init_process_group("nccl", device_id=dev)
 B, O, S, NC = args.batch, args.image, args.image + 32, 1000
-rng = np.random.default_rng(0)
+rng = np.random.default_rng(0)          # the same initial weights on every replica
 
 
 def bireal_params(nc):
@@ -98,7 +108,7 @@ else:
     name = "BinaryAlexNet"
 
 n_pool = 2 * B
-g = torch.Generator(device="cpu").manual_seed(1234)
+g = torch.Generator(device="cpu").manual_seed(1234 + rank)
 pool = torch.randint(0, 256, (n_pool, S, S, 3), generator=g, dtype=torch.uint8).to(dev)
 labels = torch.randint(0, NC, (n_pool,), generator=g, dtype=torch.int64).to(dev)
 index = [torch.randperm(n_pool, generator=g)[:B].to(torch.int32).to(dev) for _ in range(4)]
@@ -108,13 +118,15 @@ stream = torch.cuda.current_stream().cuda_stream
 
 def step(k):
     zn.call("zkb_preprocess_u8", zn.ptr(pool), zn.ptr(labels), zn.ptr(index[k % 4]), 0, zn.ptr(eng.x), zn.ptr(lab_out),
-            0, B, S, S, 3, O, O, S, 1, 0, NC, 1234, k, 0, stream)
+            0, B, S, S, 3, O, O, S, 1, 0, NC, 1234 + rank, k, 0, stream)
     eng.train_step(eng.x, lab_out)
 
 
 for k in range(args.warmup):
     step(k)
 torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for k in range(args.steps):
@@ -123,16 +135,29 @@ e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / args.steps
 loss = eng.last_loss()
+in_sync = None
+if world > 1:
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    # every replica applied the same summed gradients to the same initial weights: the arenas must agree
+    arenas = [eng.params] if args.model == "alexnet" else [eng.body.params, eng.params]
+    chk = torch.stack([a.double().sum() for a in arenas] + [a.double().abs().sum() for a in arenas])
+    allc = [torch.zeros_like(chk) for _ in range(world)]
+    dist.all_gather(allc, chk)
+    in_sync = all(bool(torch.equal(allc[0], c)) for c in allc)
 
-line = {"metric": f"{name} train images/sec", "value": B / (ms * 1e-3), "unit": "images/s", "n_gpus": 1,
+line = {"metric": f"{name} train images/sec", "value": world * B / (ms * 1e-3), "unit": "images/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "dtype": "int8 / bf16 +-1 fwd (exact) / bf16x2 bwd (f32 acc) / f32 stem, shortcuts and elementwise", "data": "synthetic",
         "config": {"workload": f"{name} (larq-zoo, [EXT]) {O}x{O}x3 synthetic, {NC} classes, batch {B}/GPU",
-                   "global_batch": B, "parallelism": "dp1", "launch": "per-kernel launches, 1 stream"},
+                   "global_batch": world * B, "parallelism": f"dp{world}", "batchnorm": "per-replica",
+                   "launch": "per-kernel launches"},
+        "scaling": "weak", "replicas_in_sync": in_sync,
         "gpu_launches": (eng.launches_per_step + 1) * args.steps, "last_loss": loss,
         "work_per_image": {"binary_mac": bin_mac, "stem_float_mac": float_mac},
-        "binary_fwd_pops_if_all_time": 2 * bin_mac * B / (ms * 1e-3) / 1e15}
-if args.cpu_baseline:
+        "binary_fwd_pops_if_all_time": 2 * bin_mac * world * B / (ms * 1e-3) / 1e15}
+if args.cpu_baseline and rank == 0:
     nt = os.cpu_count() or 1
     torch.set_num_threads(nt)
     cb, csteps = 16, 2
@@ -152,9 +177,13 @@ if args.cpu_baseline:
     dt = (time.perf_counter() - t0) / csteps
     line["cpu_baseline"] = {"value": cb / dt, "unit": "images/s", "cores": nt, "kind": "port",
                             "sample": f"{csteps} forward+backward passes of batch {cb} of the torch-CPU fp32 restatement (no optimizer step), {nt} threads"}
-print(json.dumps(line))
+if rank == 0:
+    print(json.dumps(line), flush=True)
+if world > 1:
+    dist.barrier()
+    dist.destroy_process_group()
 
-if args.breakdown:
+if args.breakdown and world == 1:
     per = defaultdict(list)
     orig = call_host._call
 

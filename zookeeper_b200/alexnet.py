@@ -30,6 +30,7 @@ import numpy as np
 import torch
 
 from . import native as zn
+from .dataparallel import DataParallel
 
 BN_EPS = 1e-3
 FEATURES = (64, 192, 384, 384, 256)
@@ -51,10 +52,17 @@ class BinaryAlexNetEngine:
 
     def __init__(self, image_hw, batch_size: int, num_classes: int, features: Sequence[int] = FEATURES,
                  dense_units: int = 4096, learning_rate: float = 5e-3, bn_momentum: float = 0.9, beta_1: float = 0.9,
-                 beta_2: float = 0.999, epsilon: float = 1e-7, device: Optional[torch.device] = None):
+                 beta_2: float = 0.999, epsilon: float = 1e-7, device: Optional[torch.device] = None,
+                 data_parallel: Optional[DataParallel] = None):
         zn.load()
         if not torch.cuda.is_available():
             raise RuntimeError("BinaryAlexNetEngine needs a CUDA device (B200); there is no CPU fallback")
+        # one process per GPU: the batch shards by sample, BatchNorm statistics stay per replica, the
+        # flat gradient arena is summed over the replicas (the dense kernels -- 95 % of it -- while
+        # the conv layers are still in their backward pass)
+        self.dp = data_parallel if data_parallel is not None else DataParallel()
+        self.world = self.dp.world
+        self._side = None
         if len(features) != 5 or any(f % 64 for f in features):
             raise ValueError("features: five channel counts, multiples of 64")
         if dense_units % 128:
@@ -87,10 +95,19 @@ class BinaryAlexNetEngine:
         self.flat = flat
         cps = [s[2] if s[2] % 64 == 0 else _round_up(s[2], 64) for s in specs]
         k_sizes = [s[3] * s[3] * s[1] * s[2] for s in specs]
-        k_off = np.concatenate([[0], np.cumsum([_round_up(n, 4) for n in k_sizes])]).astype(np.int64)
+        # arena order [dense kernels | conv kernels | betas]: one clipped Adam launch over the kernels, one
+        # plain over the betas; the gradients that are complete FIRST in the backward pass (the dense
+        # kernels) are a prefix, so the early bucket of the gradient all-reduce is a plain slice
+        order = [5, 6, 7, 0, 1, 2, 3, 4]
+        k_off = np.zeros(len(specs), dtype=np.int64)
+        pos = 0
+        for i in order:
+            k_off[i] = pos
+            pos += _round_up(k_sizes[i], 4)
+        self.n_dense_kernel = int(k_off[0])
         b_off = np.concatenate([[0], np.cumsum(cps)]).astype(np.int64)
-        self.n_kernel, self.n_beta = int(k_off[-1]), int(b_off[-1])
-        n = self.n_kernel + self.n_beta                      # [kernels | betas]: one clipped Adam launch, one plain
+        self.n_kernel, self.n_beta = int(pos), int(b_off[-1])
+        n = self.n_kernel + self.n_beta
         self.params = torch.zeros(n, dtype=f32, device=dev)
         self.grads = torch.zeros(n, dtype=f32, device=dev)
         self.adam_m = torch.zeros(n, dtype=f32, device=dev)
@@ -232,8 +249,9 @@ class BinaryAlexNetEngine:
     def backward(self):
         B = self.B
         last = self.L[-1]
-        self._call("zkb_softmax_ce", zn.ptr(last.logits), last.cp, zn.ptr(self.labels), B, self.NC, 1.0 / B, zn.ptr(last.ds),
-                   self.acc[self.loss_off:].data_ptr(), zn.ptr(self.correct))
+        self._call("zkb_softmax_ce", zn.ptr(last.logits), last.cp, zn.ptr(self.labels), B, self.NC, 1.0 / (B * self.world),
+                   zn.ptr(last.ds), self.acc[self.loss_off:].data_ptr(), zn.ptr(self.correct))
+        self._pending = []
         for L in reversed(self.L):
             prev = self.L[L.idx - 1] if L.idx else None
             is_i16 = 0 if L.idx == 0 else 1
@@ -265,6 +283,30 @@ class BinaryAlexNetEngine:
             else:
                 self._call("zkb_bdense_dgrad", zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.w_dgrad), zn.ptr(prev.ds), B, L.cin, L.cp)
                 self._call("zkb_bdense_wgrad", zn.ptr(prev.s), zn.ptr(L.dy_hi), zn.ptr(L.dy_lo), zn.ptr(L.dkernel), L.cout, B, L.cin, L.cp, L.cout)
+                if L.idx == 5 and self.world > 1:
+                    # every dense kernel gradient has been enqueued: sum them over the replicas on a side
+                    # stream, next to the conv layers' backward
+                    main = torch.cuda.current_stream(self.device)
+                    if self._side is None:
+                        self._side = torch.cuda.Stream(self.device)
+                        self._ev = torch.cuda.Event()
+                    self._ev.record(main)
+                    self._side.wait_event(self._ev)
+                    with torch.cuda.stream(self._side):
+                        self._pending.append(self.dp.all_reduce_sum_async_(self.grads[:self.n_dense_kernel]))
+
+    def finish_gradient_reduce(self):
+        """Sum the rest of the gradient arena over the replicas and join the early bucket."""
+        if self.world == 1:
+            return
+        if self._pending:
+            self._pending.append(self.dp.all_reduce_sum_async_(self.grads[self.n_dense_kernel:]))
+        else:
+            self._pending.append(self.dp.all_reduce_sum_async_(self.grads))
+        for work in self._pending:
+            if work is not None:
+                work.wait()          # orders the current stream behind the collective; no host block
+        self._pending = []
 
     def _lr_t(self, t: int) -> float:
         f = np.float32
@@ -290,11 +332,13 @@ class BinaryAlexNetEngine:
         self.prepare_weights()
         self.forward(training=True)
         self.backward()
+        self.finish_gradient_reduce()
         if apply_update:
             self.optimizer_step()
         self.launches_per_step = self._n_launch
 
     def last_loss(self) -> float:
+        """Mean loss over THIS replica's samples of the last step."""
         return float(self.acc[self.loss_off].item()) / self.B
 
     def last_accuracy(self) -> float:

@@ -41,6 +41,7 @@ import numpy as np
 import torch
 
 from . import native as zn
+from .dataparallel import DataParallel
 
 BN_EPS = 1e-3
 
@@ -57,10 +58,15 @@ class BiRealUnitsEngine:
 
     def __init__(self, units, channels: int, hw, batch_size: int, num_classes: int,
                  learning_rate: float = 5e-3, bn_momentum: float = 0.99, beta_1: float = 0.9,
-                 beta_2: float = 0.999, epsilon: float = 1e-7, device: Optional[torch.device] = None):
+                 beta_2: float = 0.999, epsilon: float = 1e-7, device: Optional[torch.device] = None,
+                 data_parallel: Optional[DataParallel] = None):
         zn.load()
         if not torch.cuda.is_available():
             raise RuntimeError("BiRealUnitsEngine needs a CUDA device (B200); there is no CPU fallback")
+        # one process per GPU: the batch shards by sample, BatchNorm statistics stay per replica, the
+        # flat gradient arena (44 MB for Bi-Real-Net-18) is summed over the replicas after the backward
+        self.dp = data_parallel if data_parallel is not None else DataParallel()
+        self.world = self.dp.world
         self.plan = ["plain"] * units if isinstance(units, int) else [str(u) for u in units]
         if not self.plan or any(u not in ("plain", "down") for u in self.plan):
             raise ValueError('units: a positive count or a sequence of "plain" / "down"')
@@ -273,7 +279,7 @@ class BiRealUnitsEngine:
     def backward(self):
         B, NC = self.B, self.NC
         oh, ow = self.out_hw
-        self._call("zkb_softmax_ce", zn.ptr(self.logits), NC, zn.ptr(self.labels), B, NC, 1.0 / B, zn.ptr(self.dlogits),
+        self._call("zkb_softmax_ce", zn.ptr(self.logits), NC, zn.ptr(self.labels), B, NC, 1.0 / (B * self.world), zn.ptr(self.dlogits),
                    self.acc[self.loss_off:].data_ptr(), zn.ptr(self.correct))
         self._call("zkb_dense_f32_bwd", zn.ptr(self.pooled), zn.ptr(self.dense_w), zn.ptr(self.dlogits), NC, zn.ptr(self.dpooled),
                    zn.ptr(self.d_dense_w), zn.ptr(self.d_dense_b), B, self.out_c, NC)
@@ -334,11 +340,13 @@ class BiRealUnitsEngine:
         self.prepare_weights()
         self.forward(training=True)
         self.backward()
+        self.dp.all_reduce_sum_(self.grads)
         if apply_update:
             self.optimizer_step()
         self.launches_per_step = self._n_launch
 
     def last_loss(self) -> float:
+        """Mean loss over THIS replica's samples of the last step."""
         return float(self.acc[self.loss_off].item()) / self.B
 
     def last_accuracy(self) -> float:
@@ -461,6 +469,8 @@ class BiRealNetEngine:
         body.forward(training=True)
         body.backward()
         self.stem_backward()
+        body.dp.all_reduce_sum_(body.grads)
+        body.dp.all_reduce_sum_(self.grads)
         if apply_update:
             body.optimizer_step()
             body._call("zkb_adam_clip", zn.ptr(self.params), zn.ptr(self.grads), zn.ptr(self.adam_m), zn.ptr(self.adam_v),
