@@ -203,6 +203,10 @@ int zkb_bdense_wgrad(const void* act_pm1, const void* dy_hi, const void* dy_lo, 
  * + batch*(1-momentum), with the Bessel-corrected variance when bessel != 0 (TF fused 4-D kernel).
  * apply_sign: a = (x-mean)*rstd + beta; s = sign(a) as pm1 bf16 and/or int8 and/or a itself
  *             (any output pointer may be NULL).
+ * C: any multiple of one 16-byte vector (8 int16 / 4 f32 channels) for stats, apply_sign and the
+ * backward reduce / apply (f32 outputs or hi/lo): a block covers whole rows, maps wider than 256
+ * vectors (4096-unit dense layers) are walked in column slices.  zkb_maxpool2_i16 and the pool
+ * scatter of zkb_bn_bwd_apply (out_mode 2) take at most 256 vectors per row.
  * Replaces: tf.keras.layers.BatchNormalization(scale=False) examples/larq_experiment.py:70,75,79,
  *           84,88,93,96,98,100 and the ste_sign input quantizer of the following layer (:53). */
 int zkb_bn_stats(const void* x, int x_is_i16, long long rows, int C, double* sum, double* sumsq,

@@ -1,7 +1,9 @@
 """Generate tests/golden/*.npz from the CPU oracle (run from the repo root:
-``python -m oracle.make_golden``).  The vectors pin the oracle against drift -- they are NOT
-TensorFlow outputs (parity unpinned, see oracle/binarynet_oracle.py)."""
+``python -m oracle.make_golden`` for the BinaryNet / bit-level / preprocessing vectors,
+``python -m oracle.make_golden zoo`` for the two larq-zoo models).  The vectors pin the oracle against
+drift -- they are NOT TensorFlow outputs (parity unpinned, see oracle/binarynet_oracle.py)."""
 import os
+import sys
 
 import numpy as np
 import torch
@@ -60,5 +62,52 @@ def main():
     print("wrote", sorted(os.listdir(OUT)))
 
 
+def zoo_cases():
+    """(name, run) of the zoo-model steps the fixture holds; tests/test_oracle_zoo_golden.py replays them."""
+    from oracle import alexnet_oracle as A
+    from oracle import bireal_oracle as R
+
+    def alexnet():
+        hw, B, NC, dense, seed = (96, 96), 4, 10, 256, 1
+        p = A.init_params(NC, hw, dense_units=dense, seed=seed)
+        rng = np.random.default_rng(seed + 50)
+        img = rng.uniform(-1, 1, (B,) + hw + (3,)).astype(np.float32)
+        lab = rng.integers(0, NC, (B,)).astype(np.int64)
+        return A.forward_backward(p, img, lab, torch.float64, keep=True)
+
+    def bireal():
+        plan, hw, B, NC, seed = ("plain", "down", "plain"), (32, 32), 4, 10, 4
+        p = R.init_params(plan, 64, NC, seed=seed, stem_ksize=7)
+        rng = np.random.default_rng(seed + 100)
+        img = rng.uniform(-1, 1, (B,) + hw + (3,)).astype(np.float32)
+        lab = rng.integers(0, NC, (B,)).astype(np.int64)
+        return R.forward_backward(p, plan, img, lab, torch.float64, keep=True)
+
+    return (("alexnet", alexnet), ("bireal", bireal))
+
+
+def zoo_summary(r):
+    """What the fixture keeps of one step: loss, logits, every gradient's norm and sum, and the sum of
+    absolute values of every kept activation (exact for the integer maps)."""
+    out = {"loss": np.float64(r["loss"]), "logits": r["logits"].astype(np.float64)}
+    for k, g in r["grads"].items():
+        out[f"grad_norm_{k}"] = np.float64(np.linalg.norm(g))
+        out[f"grad_sum_{k}"] = np.float64(g.astype(np.float64).sum())
+    for k, a in r["acts"].items():
+        if np.ndim(a) > 1:
+            out[f"act_abs_sum_{k}"] = np.float64(np.abs(a.astype(np.float64)).sum())
+    return out
+
+
+def main_zoo():
+    os.makedirs(OUT, exist_ok=True)
+    out = {}
+    for name, run in zoo_cases():
+        for k, v in zoo_summary(run()).items():
+            out[f"{name}/{k}"] = v
+    np.savez_compressed(os.path.join(OUT, "zoo_steps.npz"), **out)
+    print("wrote zoo_steps.npz with", len(out), "entries")
+
+
 if __name__ == "__main__":
-    main()
+    main_zoo() if sys.argv[1:] == ["zoo"] else main()

@@ -61,6 +61,14 @@ def test_engine_refuses_to_run_without_cuda():
 
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         BiRealUnitsEngine(("plain", "down"), 128, (14, 14), 4, 10)
+    from zookeeper_b200.alexnet import BinaryAlexNetEngine
+    from zookeeper_b200.bireal import BiRealNetEngine, bireal18_plan
+
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        BiRealNetEngine(bireal18_plan(), (224, 224), 4, 1000)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        BinaryAlexNetEngine((224, 224), 4, 1000)
+    assert bireal18_plan().count("down") == 3 and len(bireal18_plan()) == 16
 
 
 def test_product_code_never_imports_the_oracle():
