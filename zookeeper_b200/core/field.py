@@ -27,6 +27,13 @@ def _annotation_for(owner: Type, name: str) -> Any:
     return utils.missing
 
 
+class _FieldNameError(ValueError, RuntimeError):
+    """The reference raises ``ValueError`` from ``__set_name__`` (zookeeper/core/field.py:81) and its
+    test expects the ``RuntimeError`` CPython < 3.12 wrapped such exceptions in (field_test.py:116-125);
+    CPython >= 3.12 re-raises the original with a note instead.  Being both keeps the caller-visible
+    behaviour on either side of that interpreter change."""
+
+
 class Field(Generic[C, F]):
     """A typed, configurable value.  ``default`` may be an immutable value or a function of zero
     arguments / of ``self`` that produces the default lazily (evaluated at most once per
@@ -101,7 +108,7 @@ class Field(Generic[C, F]):
         if self._registered:
             raise ValueError("This field has already been registered to a component.")
         if name.startswith("_"):
-            raise ValueError("Field names cannot start with underscores.")
+            raise _FieldNameError("Field names cannot start with underscores.")
 
     def _bind(self, owner: Type, name: str, annotation: Any) -> None:
         self.name, self.host_component_class, self.type = name, owner, annotation
