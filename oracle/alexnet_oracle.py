@@ -1,5 +1,5 @@
-"""CPU oracle for a BinaryAlexNet train step -- TEST INFRASTRUCTURE ONLY (imported by tests/ and the
-CPU-baseline leg of scripts/bench_alexnet.py only; the product path never imports it).
+"""CPU oracle for a BinaryAlexNet train step -- TEST INFRASTRUCTURE ONLY (imported by tests/ and, as the
+timed CPU baseline only, by scripts/bench_zoo.py --cpu-baseline; the product path never imports it).
 
 PARITY UNPINNED.  BASELINE.json configs[3] names larq-zoo's BinaryAlexNet, which a zookeeper experiment
 reaches through the same hook as the example's BinaryNet: a ``@factory`` model built from larq layers

@@ -1,5 +1,6 @@
 """CPU oracle for Bi-Real-Net style binary residual units -- TEST INFRASTRUCTURE ONLY
-(imported by tests/ only; the product path never imports it).
+(imported by tests/ and, as the timed CPU baseline only, by scripts/bench_zoo.py --cpu-baseline; the
+product path never imports it).
 
 PARITY UNPINNED.  The reference tree holds neither these operators nor a test for them:
 BASELINE.json configs[3] / [4] name larq-zoo models (BinaryAlexNet, Bi-Real-Net-18), which a
