@@ -29,8 +29,9 @@ down-sampling unit) one engine.  Channel counts are multiples of 64; layers whos
 not a multiple of 128 (the 64-channel stage) run the bf16 +-1 forward GEMM instead of the int8 one
 (same integers, half the tensor-pipe rate).
 
-What is NOT here: a Keras functional-API front end (the plan is a list of unit kinds).  The 1x1 float
-conv of the down-sampling shortcut runs on plain SIMT kernels, the stem conv on FP32 FMA kernels.
+The Keras-shaped handle (``compile`` / ``summary`` / ``fit``) is ``zookeeper_b200.tf.zoo.BiRealNet18``.
+What is NOT here: an inference path.  The 1x1 float conv of the down-sampling shortcut and the stem
+conv run on register-tiled FP32 FMA kernels, not on the tensor cores.
 """
 from __future__ import annotations
 
